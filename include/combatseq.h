@@ -1,0 +1,147 @@
+/*
+ * combatseq.h — C ABI of the B200-native ComBat-seq engine (libcombatseq.so).
+ *
+ * This is the drop-in boundary for the reference's one public entry point,
+ *     ComBat_seq(counts, batch, group, covar_mod, full_mod, shrink, shrink.disp, gene.subset.n)
+ * (/root/reference/ComBat_seq.R:22-23).  The reference has no FFI of its own: an R wrapper
+ * (combat-seq_b200/R/ComBat_seq.R) keeps as.matrix/as.factor/model.matrix and the confounding checks
+ * (ComBat_seq.R:25-31,53-94) and hands plain arrays to cbs_combat_seq() through a .Call shim
+ * (combat-seq_b200/R/r_shim.c).  In this repo the same entry points are bound with ctypes
+ * (combat-seq_b200/__init__.py).  See INTEGRATION.md.
+ *
+ * Conventions
+ *   - every matrix is COLUMN-MAJOR (R layout): element (g,s) of a G x N matrix is at g + s*G;
+ *   - plain pointers and sizes only, caller owns every host buffer, the library owns all device memory;
+ *   - every function returns CBS_OK (0) or a CBS_E* code and never throws; cbs_last_error() gives the text;
+ *   - there is NO CPU fallback: without a CUDA device every compute entry point returns CBS_ENOGPU.
+ */
+#ifndef COMBATSEQ_H
+#define COMBATSEQ_H
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define CBS_VERSION 100
+
+enum {
+    CBS_OK = 0,
+    CBS_EINVAL = 1,                 /* bad argument (message says which) */
+    CBS_ESINGLE_SAMPLE_BATCH = 2,   /* "ComBat-seq doesn't support 1 sample per batch yet"   ComBat_seq.R:30 */
+    CBS_ECONF_COVAR_BATCH = 3,      /* "The covariate is confounded with batch! ..."          ComBat_seq.R:86 */
+    CBS_ECONF_COVARS = 4,           /* "The covariates are confounded! ..."                   ComBat_seq.R:88 */
+    CBS_ECONF_COVAR_WITH_BATCH = 5, /* "At least one covariate is confounded with batch! ..." ComBat_seq.R:89 */
+    CBS_ECUDA = 6,                  /* CUDA runtime error */
+    CBS_ENCCL = 7,                  /* NCCL error / NCCL not loadable */
+    CBS_ENOGPU = 8,                 /* no CUDA device visible: the library has no CPU path */
+    CBS_ENOMEM = 9
+};
+
+/* Monte-Carlo weight mode (helper_seq.R:28-34) */
+enum {
+    CBS_MC_REFERENCE = 0,   /* weights are prod(dnbinom) in linear space: underflow to 0 and the
+                               sum(LH)==0 fallback happen exactly where they do in R */
+    CBS_MC_STABLE = 1       /* log-sum-exp weights (no underflow, no fallback); NOT reference behaviour */
+};
+
+/* stage indices of cbs_output.stage_ms */
+enum {
+    CBS_ST_H2D = 0, CBS_ST_PREP, CBS_ST_COMMON_DISP, CBS_ST_TAGWISE_DISP, CBS_ST_GLM, CBS_ST_MC,
+    CBS_ST_MATCH_QUANTILES, CBS_ST_D2H, CBS_ST_TOTAL, CBS_N_STAGES
+};
+
+int         cbs_version(void);
+int         cbs_device_count(void);           /* 0 when no CUDA device is usable */
+const char* cbs_last_error(void);             /* thread-local text of the last failure */
+int         cbs_shutdown(void);               /* release cached device buffers / communicators */
+uint64_t    cbs_kernel_launches(void);        /* kernels launched by this library since load */
+
+/* ---- multi-process gene sharding (one process per GPU, e.g. under torchrun) ------------------------
+ * Rank 0 calls cbs_comm_unique_id() and ships the 128 bytes to the other ranks by any means
+ * (bench.py uses torch.distributed.broadcast); every rank then calls cbs_comm_create().
+ * NCCL is dlopen'ed lazily, so single-GPU use needs no NCCL at all. */
+typedef struct cbs_comm cbs_comm;
+int cbs_comm_unique_id(void* id128);
+int cbs_comm_create(const void* id128, int rank, int world, int device, cbs_comm** out);
+int cbs_comm_destroy(cbs_comm* comm);
+
+/* ---- the whole ComBat_seq() numeric body (ComBat_seq.R:33-203) -------------------------------------- */
+typedef struct {
+    int32_t G0, N, B, p_mod;        /* genes, samples, batches, ncol(mod) incl. the intercept column      */
+    const double*  counts_f64;      /* G0 x N, integer-valued; exactly one of counts_f64/counts_i32 set   */
+    const int32_t* counts_i32;      /* G0 x N                                                             */
+    const int32_t* batch_idx;       /* N, 0-based level index of as.factor(batch)       ComBat_seq.R:28   */
+    const double*  mod;             /* N x p_mod, column 0 is the intercept             ComBat_seq.R:57-73 */
+    const uint8_t* use_fallback;    /* B, or NULL: library evaluates ComBat_seq.R:101 itself              */
+    int32_t shrink, shrink_disp;    /* ComBat_seq.R:141,162                                               */
+    int32_t gene_subset_n;          /* <= 0 means NULL (all genes)                      helper_seq.R:17    */
+    uint64_t seed;                  /* RNG seed for gene_subset_n sampling (Philox, not R's stream)       */
+    int32_t mc_mode;                /* CBS_MC_REFERENCE / CBS_MC_STABLE                                    */
+    int32_t device;                 /* CUDA device ordinal for single-process use; <0 = current           */
+    cbs_comm* comm;                 /* NULL = single GPU; else this process is one rank of a gene-sharded job */
+    int32_t counts_on_device;       /* non-zero: counts_i32 is a DEVICE pointer (kernel-only benchmarking) */
+} cbs_input;
+
+typedef struct {                    /* every pointer optional (NULL = not wanted); caller-allocated        */
+    double*  adjusted;              /* G0 x N (R double holding integers)            ComBat_seq.R:199-203  */
+    uint8_t* keep;                  /* G0, 1 = gene kept by the zero filter          ComBat_seq.R:33-37    */
+    double*  lib_size;              /* N                                             ComBat_seq.R:43       */
+    double*  disp_common;           /* B                                             ComBat_seq.R:100-107  */
+    double*  phi_hat;               /* G0 x B, rows of dropped genes = NaN           ComBat_seq.R:138      */
+    double*  gamma_hat;             /* G0 x B                                        ComBat_seq.R:136      */
+    double*  gamma_star;            /* G0 x B                                        ComBat_seq.R:157-170  */
+    double*  phi_star;              /* G0 x B  (phi_star_mat)                        ComBat_seq.R:159-170  */
+    double*  mu_hat;                /* G0 x N                                        ComBat_seq.R:137      */
+    double*  stage_ms;              /* CBS_N_STAGES host-side wall times per stage (ms)                    */
+    int64_t* n_mc_fallback;         /* B: genes that took the sum(LH)==0 fallback    helper_seq.R:30-31    */
+    int64_t  row_begin, row_end;    /* OUT: G0-row range this rank wrote (whole matrix when comm == NULL)  */
+    int32_t  adjusted_on_device;    /* non-zero: `adjusted` is a DEVICE pointer                            */
+} cbs_output;
+
+int cbs_combat_seq(const cbs_input* in, cbs_output* out);
+
+/* ---- per-subsystem entry points (host buffers in/out; used by the parity tests and kernel benches) --- */
+
+/* NB distribution primitives, elementwise over n values; replaces R's dnbinom/pnbinom/qnbinom as called at
+ * helper_seq.R:28,53,58.  logpmf = log dnbinom(x; mu, size), cdf = pnbinom(x; mu, size),
+ * quantile = qnbinom(p; mu, size) (R 3.5 semantics: smallest y with pnbinom(y) >= p*(1-64*DBL_EPSILON)). */
+int cbs_nb_logpmf(int64_t n, const double* x, const double* size, const double* mu, double* out);
+int cbs_nb_cdf(int64_t n, const double* x, const double* size, const double* mu, double* out);
+int cbs_nb_quantile(int64_t n, const double* p, const double* size, const double* mu, double* out);
+
+/* edgeR glmFit.default(y, design, dispersion, offset, prior.count) as called at ComBat_seq.R:130,134.
+ * counts G x n int32; design n x p; disp G x n_disp_cols with disp_cols[s] selecting the column for sample s
+ * (phi_matrix of ComBat_seq.R:122-125 without materialising it); offset = log(lib[s]) + gene_offset[g]
+ * (gene_offset may be NULL).  coef (G x p) comes from the prior.count refit, fitted (G x n) from the plain fit. */
+int cbs_glm_fit(int64_t G, int32_t n, const int32_t* counts, const double* design, int32_t p,
+                const double* disp, int32_t n_disp_cols, const int32_t* disp_cols,
+                const double* lib, const double* gene_offset, double prior_count,
+                double* coef, double* fitted);
+
+/* edgeR adjustedProfileLik(dispersion, y, design, offset) for D dispersion values per gene:
+ * apl is G x D; disp is G x D (per-gene) if disp_per_gene else D scalars.  Used by ComBat_seq.R:103-116. */
+int cbs_apl(int64_t G, int32_t n, const int32_t* counts, const double* design, int32_t p,
+            const double* lib, const double* disp, int32_t D, int32_t disp_per_gene, double* apl);
+
+/* estimateGLMCommonDisp(y, design, subset=nrow(y)) and estimateGLMTagwiseDisp(y, design, dispersion, prior.df=0)
+ * for one batch: counts G x n (the batch's columns), design n x p or NULL (intercept only). */
+int cbs_common_disp(int64_t G, int32_t n, const int32_t* counts, const double* design, int32_t p, double* common);
+int cbs_tagwise_disp(int64_t G, int32_t n, const int32_t* counts, const double* design, int32_t p,
+                     double common, double* tagwise);
+
+/* monte_carlo_int_NB(dat, mu, gamma, phi, gene.subset.n)  helper_seq.R:8-42 for one batch */
+int cbs_mc_int(int64_t G, int32_t n, const int32_t* counts, const double* mu, const double* gamma,
+               const double* phi, int32_t mc_mode, int32_t gene_subset_n, uint64_t seed,
+               double* gamma_star, double* phi_star, int64_t* n_fallback);
+
+/* match_quantiles(counts_sub, old_mu, old_phi, new_mu, new_phi)  helper_seq.R:46-64 for one batch */
+int cbs_match_quantiles(int64_t G, int32_t n, const int32_t* counts, const double* old_mu, const double* old_phi,
+                        const double* new_mu, const double* new_phi, double* adjusted);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* COMBATSEQ_H */
