@@ -1,0 +1,376 @@
+// glm.cuh — per-gene NB log-link GLM fitters, Cox-Reid adjusted profile likelihood and the spline maximiser,
+// as FP64 device functions (one gene per thread; every reduction over samples is sequential in sample order).
+//
+// Replaces, on the device, the edgeR routines the reference calls at
+//   /root/reference/ComBat_seq.R:103,105  estimateGLMCommonDisp   -> adjustedProfileLik  (apl_gene)
+//   /root/reference/ComBat_seq.R:115-116  estimateGLMTagwiseDisp  -> adjustedProfileLik + maximizeInterpolant
+//   /root/reference/ComBat_seq.R:130,134  glmFit / glmFit.default -> mglmOneWay | mglmLevenberg (+ predFC refit)
+// edgeR (pinned "edgeR 3.22.1", ComBat_seq.R:42) is a third-party dependency that is not under /root/reference;
+// the algorithms follow its published form: glm_one_group Newton iteration (maxit 50, tol 1e-10), the one-way
+// shortcut when #distinct design rows == ncol(design), glm_levenberg (null start, maxit 250, tol 1e-6, lambda
+// schedule x10 on Cholesky failure / x2 on deviance increase / /10 after a first-try success), the unit NB
+// deviance of nbdev.cpp, compute_apl + adj_coxreid (LDL' log-determinant), and interpolator::find_max on
+// the Forsythe-Malcolm-Moler spline.
+#pragma once
+#include <cuda_runtime.h>
+#include <cstdint>
+#include <cmath>
+
+namespace cbs {
+
+constexpr int PMAX = 32;                     // max design columns handled by the per-thread solvers
+constexpr int PTRI = PMAX * (PMAX + 1) / 2;  // packed lower triangle
+
+#define CBS_LOW_VALUE 1e-10
+#define CBS_SUPREMELY_LOW 1e-13
+#define CBS_RIDICULOUSLY_LOW 1e-100
+#define CBS_MILDLY_LOW 1e-8
+
+// A (sub)problem design: n samples, p columns.  Arrays live in global memory (read-only, tiny, L1-resident).
+struct DesignDev {
+    int n, p, oneway;
+    const int* col;        // [n] column of each sample in the G x N matrices; grouped by cell when oneway
+    const int* cell_start; // [p+1] sample ranges of the cells (oneway)
+    const double* minv;    // [p*p] column-major inverse of the distinct design rows: coef = minv * cellbeta
+    const int* rowptr;     // [n+1] CSR of the design rows (non-zeros, ascending column)
+    const int* cidx;
+    const double* cval;
+    const double* start;   // [p] least-squares solution of design * b = 1 (Levenberg null start direction)
+};
+
+// How y, offset and dispersion of gene g at sample-slot column c are obtained.
+struct RowSrc {
+    const int32_t* cnt;    // G x N column-major counts of the kept genes
+    long G;
+    const double* logoff;  // [N] log(lib.size)
+    const double* yadd;    // [N] prior count added to y (predFC), or nullptr
+    const double* phi;     // per-gene dispersion columns phi[g + phi_col[c]*G], or nullptr => phi_scalar
+    const int* phi_col;    // [N] dispersion column of each sample (batch index), nullptr => column 0
+    double phi_scalar;
+};
+
+struct Row {
+    const RowSrc& s; long g; double goff;
+    __device__ Row(const RowSrc& s_, long g_, double goff_) : s(s_), g(g_), goff(goff_) {}
+    __device__ __forceinline__ double y(int c) const {
+        const double v = (double)s.cnt[g + (long)c * s.G];
+        return s.yadd ? v + s.yadd[c] : v;
+    }
+    __device__ __forceinline__ double off(int c) const { return s.logoff[c] + goff; }
+    __device__ __forceinline__ double phi(int c) const {
+        return s.phi ? s.phi[g + (long)(s.phi_col ? s.phi_col[c] : 0) * s.G] : s.phi_scalar;
+    }
+};
+
+__device__ __forceinline__ int tri(int i, int j) { return i * (i + 1) / 2 + j; }   // i >= j
+
+// edgeR glm_one_group on samples [t0,t1) of the design's sample list
+__device__ inline double fit_one_group(const DesignDev& d, const Row& r, int t0, int t1, int maxit, double tol) {
+    bool nonzero = false;
+    double cur = 0;
+    for (int t = t0; t < t1; ++t) {
+        const int c = d.col[t];
+        const double y = r.y(c);
+        if (y > CBS_LOW_VALUE) { cur += y / exp(r.off(c)); nonzero = true; }
+    }
+    cur = log(cur / (double)(t1 - t0));
+    if (!nonzero) return -INFINITY;
+    for (int i = 0; i < maxit; ++i) {
+        double dl = 0, info = 0;
+        for (int t = t0; t < t1; ++t) {
+            const int c = d.col[t];
+            const double mu = exp(cur + r.off(c)), den = 1 + mu * r.phi(c);
+            dl += (r.y(c) - mu) / den;
+            info += mu / den;
+        }
+        const double step = dl / info;
+        cur += step;
+        if (fabs(step) < tol) break;
+    }
+    return cur;
+}
+
+// edgeR compute_unit_nb_deviance ("2/3" is an integer division, i.e. 0, in edgeR 3.22)
+__device__ __forceinline__ double unit_nb_deviance(double y, double mu, double phi) {
+    y += CBS_MILDLY_LOW; mu += CBS_MILDLY_LOW;
+    if (phi < 1e-4) {
+        const double resid = y - mu;
+        return 2 * (y * log(y / mu) - resid - 0.5 * resid * resid * phi * (1 + phi * (0.0 * resid - y)));
+    }
+    const double product = mu * phi;
+    if (product > 1e6) return 2 * ((y - mu) / mu - log(y / mu)) * mu / (1 + product);
+    const double invphi = 1 / phi;
+    return 2 * (y * log(y / mu) + (y + invphi) * log((mu + invphi) / (y + invphi)));
+}
+
+__device__ __forceinline__ double lin_pred(const DesignDev& d, const Row& r, int t, const double* beta) {
+    double eta = r.off(d.col[t]);
+    for (int k = d.rowptr[t]; k < d.rowptr[t + 1]; ++k) eta += d.cval[k] * beta[d.cidx[k]];
+    return eta;
+}
+
+// One sweep over the samples at coefficients beta: deviance, X'WX (packed lower) and X'z.
+__device__ inline double lev_sweep(const DesignDev& d, const Row& r, const double* beta, double* xtwx, double* dl) {
+    const int p = d.p;
+    for (int i = 0; i < p * (p + 1) / 2; ++i) xtwx[i] = 0;
+    for (int i = 0; i < p; ++i) dl[i] = 0;
+    double dev = 0;
+    for (int t = 0; t < d.n; ++t) {
+        const int c = d.col[t];
+        const double mu = exp(lin_pred(d, r, t, beta)), y = r.y(c), phi = r.phi(c);
+        dev += unit_nb_deviance(y, mu, phi);
+        const double den = 1 + mu * phi, W = mu / den, z = (y - mu) / den;
+        for (int k = d.rowptr[t]; k < d.rowptr[t + 1]; ++k) {
+            const int ik = d.cidx[k];
+            const double vk = d.cval[k];
+            dl[ik] += vk * z;
+            for (int k2 = d.rowptr[t]; k2 <= k; ++k2) xtwx[tri(ik, d.cidx[k2])] += vk * d.cval[k2] * W;
+        }
+    }
+    return dev;
+}
+
+// Cholesky of the packed lower triangle (in place); returns false when a pivot is <= 0 or NaN
+__device__ inline bool chol_packed(double* a, int p) {
+    for (int j = 0; j < p; ++j) {
+        double ajj = a[tri(j, j)];
+        for (int k = 0; k < j; ++k) ajj -= a[tri(j, k)] * a[tri(j, k)];
+        if (!(ajj > 0)) return false;
+        ajj = sqrt(ajj);
+        a[tri(j, j)] = ajj;
+        for (int c = j + 1; c < p; ++c) {
+            double v = a[tri(c, j)];
+            for (int k = 0; k < j; ++k) v -= a[tri(j, k)] * a[tri(c, k)];
+            a[tri(c, j)] = v / ajj;
+        }
+    }
+    return true;
+}
+__device__ inline void chol_solve_packed(const double* a, int p, double* b) {
+    for (int i = 0; i < p; ++i) { double s = b[i]; for (int k = 0; k < i; ++k) s -= a[tri(i, k)] * b[k]; b[i] = s / a[tri(i, i)]; }
+    for (int i = p - 1; i >= 0; --i) { double s = b[i]; for (int k = i + 1; k < p; ++k) s -= a[tri(k, i)] * b[k]; b[i] = s / a[tri(i, i)]; }
+}
+
+// edgeR glm_levenberg::fit with the "null" start.  beta (out, p).  Returns false when y is all zero (beta = NaN, mu = 0).
+__device__ inline bool fit_levenberg(const DesignDev& d, const Row& r, double* beta, int maxit = 250, double tolerance = 1e-6) {
+    const int p = d.p, pt = p * (p + 1) / 2;
+    double xtwx[PTRI], xtwx_new[PTRI], work[PTRI], dl[PMAX], dl_new[PMAX], dbeta[PMAX], beta_new[PMAX];
+    double ymax = 0, sum_exprs = 0, sum_weight = 0;
+    for (int t = 0; t < d.n; ++t) {
+        const int c = d.col[t];
+        const double y = r.y(c);
+        if (y > ymax) ymax = y;
+        const double curN = exp(r.off(c)), w = curN / (1 + r.phi(c) * curN);
+        sum_exprs += y * w / curN;
+        sum_weight += w;
+    }
+    if (ymax < CBS_LOW_VALUE) { for (int i = 0; i < p; ++i) beta[i] = nan(""); return false; }
+    const double c0 = log(sum_exprs / sum_weight);
+    for (int i = 0; i < p; ++i) beta[i] = d.start[i] * c0;
+    double dev = lev_sweep(d, r, beta, xtwx, dl);
+    double max_info = -1, lambda = 0;
+    int iter = 0;
+    while ((++iter) <= maxit) {
+        for (int i = 0; i < p; ++i) if (xtwx[tri(i, i)] > max_info) max_info = xtwx[tri(i, i)];
+        if (iter == 1) { lambda = max_info * 1e-6; if (lambda < 1e-13) lambda = 1e-13; }
+        int lev = 0;
+        bool low_dev = false, failed = false;
+        while (++lev) {
+            do {
+                for (int i = 0; i < pt; ++i) work[i] = xtwx[i];
+                for (int i = 0; i < p; ++i) { work[tri(i, i)] += lambda; dbeta[i] = dl[i]; }
+                if (chol_packed(work, p)) break;
+                lambda *= 10;
+                if (lambda <= 0) lambda = CBS_RIDICULOUSLY_LOW;
+            } while (1);
+            chol_solve_packed(work, p, dbeta);
+            for (int i = 0; i < p; ++i) beta_new[i] = beta[i] + dbeta[i];
+            const double dev_new = lev_sweep(d, r, beta_new, xtwx_new, dl_new);
+            if (dev_new / ymax < CBS_SUPREMELY_LOW) low_dev = true;
+            if (dev_new <= dev || low_dev) {
+                for (int i = 0; i < p; ++i) beta[i] = beta_new[i];
+                dev = dev_new;
+                break;
+            }
+            lambda *= 2;
+            if (lambda <= 0) lambda = CBS_RIDICULOUSLY_LOW;
+            if (lambda / max_info > 1 / CBS_SUPREMELY_LOW) { failed = true; break; }
+        }
+        if (failed || low_dev) break;
+        double divergence = 0;
+        for (int i = 0; i < p; ++i) divergence += dl[i] * dbeta[i];
+        if (divergence < tolerance) break;
+        if (lev == 1) lambda /= 10;
+        for (int i = 0; i < pt; ++i) xtwx[i] = xtwx_new[i];     // information at the accepted coefficients
+        for (int i = 0; i < p; ++i) dl[i] = dl_new[i];
+    }
+    return true;
+}
+
+// glmFit.default's plain fit of one gene: coefficients beta[p]; cellbeta[p] additionally for one-way designs.
+// Returns the mode used so that the caller can form fitted values with fitted_at().
+__device__ inline void fit_gene(const DesignDev& d, const Row& r, double* beta, double* cellbeta) {
+    if (d.oneway) {
+        for (int l = 0; l < d.p; ++l) {
+            const double b = fit_one_group(d, r, d.cell_start[l], d.cell_start[l + 1], 50, 1e-10);
+            cellbeta[l] = fmax(b, -1e8);                        // mglmOneWay: pmax(beta, -1e8)
+        }
+        for (int k = 0; k < d.p; ++k) {
+            double s = 0;
+            for (int l = 0; l < d.p; ++l) s += d.minv[k + l * d.p] * cellbeta[l];
+            beta[k] = s;
+        }
+    } else {
+        fit_levenberg(d, r, beta);
+    }
+}
+
+// LAPACK dsytf2 (uplo = 'L', Bunch-Kaufman) on a packed lower triangle; the diagonal of D is left on the diagonal
+__device__ inline void sytf2_packed(double* a, int n) {
+    const double alpha = (1. + sqrt(17.)) / 8.;
+    int k = 0;
+    while (k < n) {
+        int kstep = 1, kp = k, imax = k;
+        const double absakk = fabs(a[tri(k, k)]);
+        double colmax = 0;
+        for (int i = k + 1; i < n; ++i) if (fabs(a[tri(i, k)]) > colmax) { colmax = fabs(a[tri(i, k)]); imax = i; }
+        if (fmax(absakk, colmax) == 0 || isnan(absakk)) { kp = k; }
+        else {
+            if (absakk >= alpha * colmax) kp = k;
+            else {
+                double rowmax = 0;
+                for (int j = k; j < imax; ++j) rowmax = fmax(rowmax, fabs(a[tri(imax, j)]));
+                for (int i = imax + 1; i < n; ++i) rowmax = fmax(rowmax, fabs(a[tri(i, imax)]));
+                if (absakk >= alpha * colmax * (colmax / rowmax)) kp = k;
+                else if (fabs(a[tri(imax, imax)]) >= alpha * rowmax) kp = imax;
+                else { kp = imax; kstep = 2; }
+            }
+            const int kk = k + kstep - 1;
+            if (kp != kk) {
+                for (int i = kp + 1; i < n; ++i) { const double t = a[tri(i, kk)]; a[tri(i, kk)] = a[tri(i, kp)]; a[tri(i, kp)] = t; }
+                for (int j = kk + 1; j < kp; ++j) { const double t = a[tri(j, kk)]; a[tri(j, kk)] = a[tri(kp, j)]; a[tri(kp, j)] = t; }
+                { const double t = a[tri(kk, kk)]; a[tri(kk, kk)] = a[tri(kp, kp)]; a[tri(kp, kp)] = t; }
+                if (kstep == 2) { const double t = a[tri(k + 1, k)]; a[tri(k + 1, k)] = a[tri(kp, k)]; a[tri(kp, k)] = t; }
+            }
+            if (kstep == 1) {
+                if (k < n - 1) {
+                    const double d11 = 1. / a[tri(k, k)];
+                    for (int j = k + 1; j < n; ++j) {
+                        const double t = -d11 * a[tri(j, k)];
+                        for (int i = j; i < n; ++i) a[tri(i, j)] += a[tri(i, k)] * t;
+                    }
+                    for (int i = k + 1; i < n; ++i) a[tri(i, k)] *= d11;
+                }
+            } else if (k < n - 2) {
+                double d21 = a[tri(k + 1, k)];
+                const double d11 = a[tri(k + 1, k + 1)] / d21, d22 = a[tri(k, k)] / d21;
+                const double t = 1. / (d11 * d22 - 1.);
+                d21 = t / d21;
+                for (int j = k + 2; j < n; ++j) {
+                    const double wk = d21 * (d11 * a[tri(j, k)] - a[tri(j, k + 1)]);
+                    const double wkp1 = d21 * (d22 * a[tri(j, k + 1)] - a[tri(j, k)]);
+                    for (int i = j; i < n; ++i) a[tri(i, j)] -= a[tri(i, k)] * wk + a[tri(i, k + 1)] * wkp1;
+                    a[tri(j, k)] = wk; a[tri(j, k + 1)] = wkp1;
+                }
+            }
+        }
+        k += kstep;
+    }
+}
+
+// edgeR adjustedProfileLik for one gene at the dispersion carried by `r`: fit, NB log-likelihood, Cox-Reid term.
+__device__ inline double apl_gene(const DesignDev& d, const Row& r) {
+    double beta[PMAX], cellbeta[PMAX], wm[PTRI];
+    const int p = d.p;
+    fit_gene(d, r, beta, cellbeta);
+    for (int i = 0; i < p * (p + 1) / 2; ++i) wm[i] = 0;
+    double sum_loglik = 0, sumw = 0;
+    int l = 0;
+    for (int t = 0; t < d.n; ++t) {
+        const int c = d.col[t];
+        double mu;
+        if (d.oneway) { while (t >= d.cell_start[l + 1]) ++l; mu = exp(cellbeta[l] + r.off(c)); }
+        else mu = isnan(beta[0]) ? 0.0 : exp(lin_pred(d, r, t, beta));
+        if (mu == 0) continue;
+        const double y = r.y(c), phi = r.phi(c);
+        double loglik;
+        if (phi > 0) {
+            const double rr = 1 / phi, logmur = log(mu + rr);
+            loglik = y * log(mu) - y * logmur + rr * log(rr) - rr * logmur + lgamma(y + rr) - lgamma(y + 1) - lgamma(rr);
+        } else {
+            loglik = y * log(mu) - mu - lgamma(y + 1);
+        }
+        const double W = mu / (1 + phi * mu);
+        sum_loglik += loglik;
+        sumw += W;
+        if (p > 1)
+            for (int k = d.rowptr[t]; k < d.rowptr[t + 1]; ++k)
+                for (int k2 = d.rowptr[t]; k2 <= k; ++k2) wm[tri(d.cidx[k], d.cidx[k2])] += d.cval[k] * d.cval[k2] * W;
+    }
+    double adj;
+    if (p == 1) adj = log(fabs(sumw)) / 2;
+    else {
+        sytf2_packed(wm, p);
+        const double log_low = log(CBS_LOW_VALUE);
+        double sld = 0;
+        for (int i = 0; i < p; ++i) {
+            const double v = wm[tri(i, i)];
+            sld += (v < CBS_LOW_VALUE || !isfinite(v)) ? log_low : log(v);
+        }
+        adj = sld * 0.5;
+    }
+    return sum_loglik - adj;
+}
+
+// R's fmm_spline (n >= 4 here) and edgeR interpolator::find_max: abscissa of the spline maximum
+template <int NP>
+__device__ inline double maximize_interpolant(const double* x, const double* y) {
+    double b[NP], c[NP], dd[NP];
+    double maxed = -1; int at = -1;
+    for (int i = 0; i < NP; ++i) if (at < 0 || y[i] > maxed) { maxed = y[i]; at = i; }
+    double x_max = x[at];
+    const int nm1 = NP - 1;
+    dd[0] = x[1] - x[0];
+    c[1] = (y[1] - y[0]) / dd[0];
+    for (int i = 1; i < nm1; i++) {
+        dd[i] = x[i + 1] - x[i];
+        b[i] = 2.0 * (dd[i - 1] + dd[i]);
+        c[i + 1] = (y[i + 1] - y[i]) / dd[i];
+        c[i] = c[i + 1] - c[i];
+    }
+    b[0] = -dd[0]; b[nm1] = -dd[NP - 2];
+    c[0] = c[2] / (x[3] - x[1]) - c[1] / (x[2] - x[0]);
+    c[nm1] = c[NP - 2] / (x[nm1] - x[NP - 3]) - c[NP - 3] / (x[NP - 2] - x[NP - 4]);
+    c[0] = c[0] * dd[0] * dd[0] / (x[3] - x[0]);
+    c[nm1] = -c[nm1] * dd[NP - 2] * dd[NP - 2] / (x[nm1] - x[NP - 4]);
+    for (int i = 1; i <= nm1; i++) { const double t = dd[i - 1] / b[i - 1]; b[i] = b[i] - t * dd[i - 1]; c[i] = c[i] - t * c[i - 1]; }
+    c[nm1] = c[nm1] / b[nm1];
+    for (int i = NP - 2; i >= 0; i--) c[i] = (c[i] - dd[i] * c[i + 1]) / b[i];
+    b[nm1] = (y[nm1] - y[NP - 2]) / dd[NP - 2] + dd[NP - 2] * (c[NP - 2] + 2.0 * c[nm1]);
+    for (int i = 0; i < nm1; i++) {
+        b[i] = (y[i + 1] - y[i]) / dd[i] - dd[i] * (c[i + 1] + 2.0 * c[i]);
+        dd[i] = (c[i + 1] - c[i]) / dd[i];
+        c[i] = 3.0 * c[i];
+    }
+    c[nm1] = 3.0 * c[nm1];
+    dd[nm1] = dd[NP - 2];
+#pragma unroll
+    for (int side = 0; side < 2; ++side) {
+        const int k = (side == 0) ? at - 1 : at;
+        if (k < 0 || k >= NP - 1) continue;
+        const double width = x[k + 1] - x[k];
+        const double A = 3 * dd[k], B = 2 * c[k], C = b[k];
+        double back = B * B - 4 * A * C;
+        if (back < 0) continue;
+        const double front = -B / (2 * A);
+        back = sqrt(back) / (2 * A);
+        const double sol = front - back;
+        if (sol > 0 && sol < width) {
+            const double temp = ((dd[k] * sol + c[k]) * sol + b[k]) * sol + y[k];
+            if (temp > maxed) { maxed = temp; x_max = sol + x[k]; }
+        }
+    }
+    return x_max;
+}
+
+}  // namespace cbs

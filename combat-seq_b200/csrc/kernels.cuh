@@ -1,0 +1,227 @@
+// kernels.cuh — sm_100a kernels of the ComBat-seq engine other than the Monte-Carlo integration (mc.cuh).
+// Data layout: every per-gene matrix is column-major with the gene index fastest (R layout), so one thread per
+// gene (consecutive threads = consecutive genes) gives fully coalesced loads and stores.
+#pragma once
+#include "nbmath.cuh"
+#include "glm.cuh"
+
+namespace cbs {
+
+// ---- a1: zero filter (ComBat_seq.R:33-37): keep[g] = every batch has a non-zero count in row g ----------
+template <class T>
+__global__ void k_keep_mask(const T* __restrict__ counts, long G0, int N, const int* __restrict__ batch_idx, int B,
+                            unsigned char* __restrict__ keep) {
+    const long g = (long)blockIdx.x * blockDim.x + threadIdx.x;
+    if (g >= G0) return;
+    unsigned long long seen_lo = 0, seen_hi = 0;   // up to 128 batches as a bit set
+    for (int s = 0; s < N; ++s) {
+        const T v = counts[g + (long)s * G0];
+        if (v != (T)0) { const int b = batch_idx[s]; if (b < 64) seen_lo |= 1ull << b; else seen_hi |= 1ull << (b - 64); }
+    }
+    const int cnt = __popcll(seen_lo) + __popcll(seen_hi);
+    keep[g] = (cnt == B) ? 1 : 0;
+}
+
+// ---- a1/a2: compaction to int32 + exact integer column sums (DGEList lib.size, ComBat_seq.R:43) -----------
+// grid: (ceil(G/256), N).  cnt is G x N column-major over the kept genes.
+template <class T>
+__global__ void k_compact_colsum(const T* __restrict__ counts, long G0, const int* __restrict__ keep_idx, long G,
+                                 int32_t* __restrict__ cnt, unsigned long long* __restrict__ colsum) {
+    const long i = (long)blockIdx.x * blockDim.x + threadIdx.x;
+    const int s = blockIdx.y;
+    long long v = 0;
+    if (i < G) {
+        v = (long long)counts[keep_idx[i] + (long)s * G0];
+        cnt[i + (long)s * G] = (int32_t)v;
+    }
+    // integer sums are exact and order-independent, so atomics keep the result deterministic
+    for (int o = 16; o > 0; o >>= 1) v += __shfl_down_sync(0xffffffffu, v, o);
+    __shared__ long long part[32];
+    const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
+    if (lane == 0) part[wid] = v;
+    __syncthreads();
+    if (wid == 0) {
+        v = (lane < (int)(blockDim.x >> 5)) ? part[lane] : 0;
+        for (int o = 16; o > 0; o >>= 1) v += __shfl_down_sync(0xffffffffu, v, o);
+        if (lane == 0 && v != 0) atomicAdd(&colsum[s], (unsigned long long)v);
+    }
+}
+
+// per-batch row sums of the kept genes: sel[b*G+g] = rowSums(counts[g, batch b]) >= 5  (edgeR min.row.sum)
+__global__ void k_rowsum_sel(const int32_t* __restrict__ cnt, long G, int N, const int* __restrict__ batch_idx, int B,
+                             unsigned char* __restrict__ sel) {
+    const long g = (long)blockIdx.x * blockDim.x + threadIdx.x;
+    const int b = blockIdx.y;
+    if (g >= G) return;
+    long long rs = 0;
+    for (int s = 0; s < N; ++s) if (batch_idx[s] == b) rs += cnt[g + (long)s * G];
+    sel[(long)b * G + g] = (rs >= 5) ? 1 : 0;
+}
+
+// ---- a5/a6: adjusted profile likelihood, one thread per (gene, evaluation) -------------------------------
+constexpr int APL_MAX_EVALS = 96;
+struct AplLaunch {
+    int n_evals;
+    int design[APL_MAX_EVALS];   // which DesignDev (batch) each evaluation uses
+    double phi[APL_MAX_EVALS];   // scalar dispersion of the evaluation (ignored when phi_gene != nullptr)
+};
+// apl[e*G + g]; sel[design*G + g] == 0 genes are skipped (apl = 0).  phi_gene (optional): G x n_evals per-gene dispersions.
+__global__ void __launch_bounds__(128)
+k_apl(const int32_t* __restrict__ cnt, long G, long g0, long g1, const double* __restrict__ logoff,
+      const DesignDev* __restrict__ designs, const unsigned char* __restrict__ sel, const double* __restrict__ phi_gene,
+      AplLaunch L, double* __restrict__ apl) {
+    const long g = g0 + (long)blockIdx.x * blockDim.x + threadIdx.x;
+    const int e = blockIdx.y;
+    if (g >= g1) return;
+    const int di = L.design[e];
+    if (sel && !sel[(long)di * G + g]) { apl[(long)e * G + g] = 0.0; return; }
+    const DesignDev d = designs[di];
+    RowSrc src{cnt, G, logoff, nullptr, nullptr, nullptr, phi_gene ? phi_gene[(long)e * G + g] : L.phi[e]};
+    Row r(src, g, 0.0);
+    apl[(long)e * G + g] = apl_gene(d, r);
+}
+
+// deterministic chunked sums: partial[e*nchunk + chunk] = sum of apl[e*G + g] over the selected genes of the chunk
+constexpr int APL_CHUNK = 1024;
+__global__ void __launch_bounds__(256)
+k_chunk_sum(const double* __restrict__ apl, long G, const unsigned char* __restrict__ sel, AplLaunch L,
+            long chunk0, double* __restrict__ partial, long nchunk_total) {
+    const long chunk = chunk0 + blockIdx.x;
+    const int e = blockIdx.y;
+    const long base = chunk * APL_CHUNK;
+    const unsigned char* s = sel ? sel + (long)L.design[e] * G : nullptr;
+    double v = 0;
+    for (int k = 0; k < APL_CHUNK / 256; ++k) {
+        const long g = base + threadIdx.x + k * 256;
+        if (g < G && (!s || s[g])) v += apl[(long)e * G + g];
+    }
+    __shared__ double sh[256];
+    sh[threadIdx.x] = v;
+    __syncthreads();
+    for (int o = 128; o > 0; o >>= 1) {
+        if ((int)threadIdx.x < o) sh[threadIdx.x] += sh[threadIdx.x + o];
+        __syncthreads();
+    }
+    if (threadIdx.x == 0) partial[(long)e * nchunk_total + chunk] = sh[0];
+}
+
+// a6: spline maximisation over the 11-point grid; apl is laid out [k*G + g] for this batch
+__global__ void k_tagwise_max(const double* __restrict__ apl, long G, long g0, long g1, const unsigned char* __restrict__ sel,
+                              double common, double* __restrict__ phi_out) {
+    const long g = g0 + (long)blockIdx.x * blockDim.x + threadIdx.x;
+    if (g >= g1) return;
+    if (sel && !sel[g]) { phi_out[g] = common; return; }
+    double x[11], y[11];
+#pragma unroll
+    for (int k = 0; k < 11; ++k) { x[k] = -6.0 + k * (12.0 / 10); y[k] = apl[(long)k * G + g]; }
+    const double dmax = maximize_interpolant<11>(x, y);
+    phi_out[g] = common * pow(2.0, dmax);
+}
+
+__global__ void k_fill(double* __restrict__ p, long n, double v) {
+    const long i = (long)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i < n) p[i] = v;
+}
+
+// ---- a8-a10: glmFit.default, one thread per gene --------------------------------------------------------
+// mode 0: plain fit, gene offset = goff_in[g] (or 0)            -> coef (optional), fitted (optional)
+// mode 1: predFC fit (y + yadd, gene offset = log(exp(goff_in[g]) + 2*prior/mean(lib))) -> coef
+// alpha_w (optional, length n_alpha): additionally write alpha[g] = sum_b alpha_w[b] * coef[g,b]   (ComBat_seq.R:131)
+__global__ void __launch_bounds__(128)
+k_glm_fit(const int32_t* __restrict__ cnt, long G, long g0, long g1, const double* __restrict__ logoff,
+          const double* __restrict__ yadd, double two_prior_over_meanlib, const double* __restrict__ phi,
+          const int* __restrict__ phi_col, const DesignDev* __restrict__ design, const double* __restrict__ goff_in,
+          int mode, double* __restrict__ coef, double* __restrict__ fitted, const double* __restrict__ alpha_w,
+          int n_alpha, double* __restrict__ alpha_out) {
+    const long g = g0 + (long)blockIdx.x * blockDim.x + threadIdx.x;
+    if (g >= g1) return;
+    const DesignDev d = *design;
+    double goff = goff_in ? goff_in[g] : 0.0;
+    if (mode == 1) goff = log(exp(goff) + two_prior_over_meanlib);
+    RowSrc src{cnt, G, logoff, mode == 1 ? yadd : nullptr, phi, phi_col, 0.0};
+    Row r(src, g, goff);
+    double beta[PMAX], cellbeta[PMAX];
+    fit_gene(d, r, beta, cellbeta);
+    if (coef) for (int k = 0; k < d.p; ++k) coef[g + (long)k * G] = beta[k];
+    if (alpha_out) {
+        double a = 0;
+        for (int b = 0; b < n_alpha; ++b) a += beta[b] * alpha_w[b];
+        alpha_out[g] = a;
+    }
+    if (fitted) {
+        if (d.oneway) {
+            for (int l = 0; l < d.p; ++l)
+                for (int t = d.cell_start[l]; t < d.cell_start[l + 1]; ++t) {
+                    const int c = d.col[t];
+                    fitted[g + (long)c * G] = exp(cellbeta[l] + r.off(c));
+                }
+        } else {
+            const bool dead = isnan(beta[0]);
+            for (int t = 0; t < d.n; ++t) fitted[g + (long)d.col[t] * G] = dead ? 0.0 : exp(lin_pred(d, r, t, beta));
+        }
+    }
+}
+
+// ---- a12/a13: batch-free parameters + match_quantiles (helper_seq.R:46-64), one thread per element -------
+__global__ void k_phi_star_mean(const double* __restrict__ phi_star_mat, long G, int B, double* __restrict__ phi_star) {
+    const long g = (long)blockIdx.x * blockDim.x + threadIdx.x;
+    if (g >= G) return;
+    double s = 0;
+    for (int b = 0; b < B; ++b) s += phi_star_mat[g + (long)b * G];
+    phi_star[g] = s / B;                                    // rowMeans  ComBat_seq.R:178
+}
+
+__device__ __forceinline__ double match_one(double x, double old_mu, double old_phi, double new_mu, double new_phi) {
+    if (x <= 1) return x;                                   // helper_seq.R:50-51
+    const double tmp_p = pnbinom_mu(x - 1, 1.0 / old_phi, old_mu);
+    if (fabs(tmp_p - 1) < 1e-4) return x;                   // helper_seq.R:54-56
+    return 1 + qnbinom_mu(tmp_p, 1.0 / new_phi, new_mu);    // helper_seq.R:58
+}
+
+// grid: (ceil(G/128), N).  out is G0-row column-major; row of kept gene i is keep_idx[i] (or i when keep_idx == nullptr)
+__global__ void __launch_bounds__(128)
+k_match_quantiles(const int32_t* __restrict__ cnt, long G, long g0, long g1, const double* __restrict__ mu_hat,
+                  const int* __restrict__ batch_idx, const double* __restrict__ phi_hat,
+                  const double* __restrict__ gamma_star, const double* __restrict__ phi_star,
+                  const int* __restrict__ keep_idx, long G0, double* __restrict__ out) {
+    const long g = g0 + (long)blockIdx.x * blockDim.x + threadIdx.x;
+    const int s = blockIdx.y;
+    if (g >= g1) return;
+    const int b = batch_idx[s];
+    const double x = (double)cnt[g + (long)s * G];
+    const double old_mu = mu_hat[g + (long)s * G];
+    const double new_mu = exp(log(old_mu) - gamma_star[g + (long)b * G]);     // ComBat_seq.R:176
+    const double v = match_one(x, old_mu, phi_hat[g + (long)b * G], new_mu, phi_star[g]);
+    out[(keep_idx ? (long)keep_idx[g] : g) + (long)s * G0] = v;
+}
+
+// generic per-batch form used by cbs_match_quantiles (explicit new_mu)
+__global__ void __launch_bounds__(128)
+k_match_quantiles_plain(const int32_t* __restrict__ cnt, long G, int n, const double* __restrict__ old_mu,
+                        const double* __restrict__ old_phi, const double* __restrict__ new_mu,
+                        const double* __restrict__ new_phi, double* __restrict__ out) {
+    const long g = (long)blockIdx.x * blockDim.x + threadIdx.x;
+    const int s = blockIdx.y;
+    if (g >= G) return;
+    const long k = g + (long)s * G;
+    out[k] = match_one((double)cnt[k], old_mu[k], old_phi[g], new_mu[k], new_phi[g]);
+}
+
+// a14: output pre-fill with the original counts as doubles (rows of filtered genes pass through; ComBat_seq.R:202)
+template <class T>
+__global__ void k_counts_to_f64(const T* __restrict__ counts, long n, double* __restrict__ out) {
+    const long i = (long)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i < n) out[i] = (double)counts[i];
+}
+
+// ---- elementwise NB primitives (cbs_nb_logpmf / cbs_nb_cdf / cbs_nb_quantile) ----------------------------
+__global__ void k_nb_elementwise(int what, long n, const double* __restrict__ a, const double* __restrict__ size,
+                                 const double* __restrict__ mu, double* __restrict__ out) {
+    const long i = (long)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    if (what == 0) out[i] = dnbinom_mu<true>(a[i], size[i], mu[i]);
+    else if (what == 1) out[i] = pnbinom_mu(a[i], size[i], mu[i]);
+    else out[i] = qnbinom_mu(a[i], size[i], mu[i]);
+}
+
+}  // namespace cbs

@@ -1,0 +1,286 @@
+// nbmath.cuh — FP64 device functions for the negative-binomial distribution.
+//
+// Replaces, on the device, the R nmath routines that the reference calls as
+//   dnbinom(x, mu=, size=)  /root/reference/helper_seq.R:28
+//   pnbinom(q, mu=, size=)  /root/reference/helper_seq.R:53
+//   qnbinom(p, mu=, size=)  /root/reference/helper_seq.R:58
+// R/nmath is a third-party dependency that is not under /root/reference; the algorithms follow its published
+// form: Loader's saddle-point pmf (stirlerr / bd0), the TOMS 708 continued fraction for the regularised
+// incomplete beta function, Wichura's AS 241 inverse normal and qnbinom's Cornish-Fisher start + discrete
+// search with the p*(1-64*eps) fuzz.  Everything is evaluated on the FP64 pipe.
+#pragma once
+#include <cuda_runtime.h>
+#include <cfloat>
+#include <cmath>
+
+namespace cbs {
+
+#define CBS_LN_SQRT_2PI 0.918938533204672741780329736406
+#define CBS_LN_2PI      1.837877066409345483560659472811
+#define CBS_2PI         6.283185307179586476925286766559
+
+// stirlerr(k/2), k = 0..30:  log(n!) - log(sqrt(2 pi n) (n/e)^n), generated with mpmath at 40 digits
+__device__ __constant__ double c_sferr_halves[31] = {
+    0.0,
+    0.1534264097200273452913839, 0.08106146679532725821967026, 0.0548141210519176538961387,
+    0.04134069595540929409382208, 0.03316287351993628748511051, 0.02767792568499833914878929,
+    0.02374616365629749597133028, 0.02079067210376509311152277, 0.01848845053267318523077936,
+    0.01664469118982119216319487, 0.01513497322191737887351384, 0.01387612882307074799874573,
+    0.01281046524292022692425066, 0.01189670994589177009505572, 0.01110455975820691732663076,
+    0.01041126526197209649747857, 0.009799416126158803298390373, 0.009255462182712732917728637,
+    0.008768700134139385462955047, 0.008330563433362871256469319, 0.007934114564314020547249562,
+    0.007573675487951840794972024, 0.007244554301320383179546197, 0.006942840107209529865664153,
+    0.006665247032707682442356181, 0.006408994188004207068439631, 0.006171712263039457647534605,
+    0.005951370112758847735624416, 0.005746216513010115682026102, 0.00555473355196280137103869};
+
+// Stirling-series remainder of log(n!)
+__device__ __forceinline__ double stirlerr(double n) {
+    const double S0 = 0.083333333333333333333, S1 = 0.00277777777777777777778, S2 = 0.00079365079365079365079365,
+                 S3 = 0.000595238095238095238095238, S4 = 0.0008417508417508417508417508;
+    if (n <= 15.0) {
+        const double nn = n + n;
+        if (nn == (double)(int)nn) return c_sferr_halves[(int)nn];
+        return lgamma(n + 1.0) - (n + 0.5) * log(n) + n - CBS_LN_SQRT_2PI;
+    }
+    const double nn = n * n;
+    if (n > 500) return (S0 - S1 / nn) / n;
+    if (n > 80) return (S0 - (S1 - S2 / nn) / nn) / n;
+    if (n > 35) return (S0 - (S1 - (S2 - S3 / nn) / nn) / nn) / n;
+    return (S0 - (S1 - (S2 - (S3 - S4 / nn) / nn) / nn) / nn) / n;
+}
+
+// bd0(x, np) = x log(x/np) + np - x, without cancellation when x ~ np
+__device__ __forceinline__ double bd0(double x, double np) {
+    if (!isfinite(x) || !isfinite(np) || np == 0.0) return nan("");
+    if (fabs(x - np) < 0.1 * (x + np)) {
+        double v = (x - np) / (x + np);
+        double s = (x - np) * v;
+        if (fabs(s) < DBL_MIN) return s;
+        double ej = 2 * x * v;
+        v = v * v;
+        for (int j = 1; j < 1000; j++) {
+            ej *= v;
+            const double s1 = s + ej / ((j << 1) + 1);
+            if (s1 == s) return s1;
+            s = s1;
+        }
+    }
+    return x * log(x / np) + np - x;
+}
+
+// binomial pmf kernel of Loader's algorithm, linear (log_p = false) or log scale
+template <bool LOG>
+__device__ __forceinline__ double dbinom_raw(double x, double n, double p, double q) {
+    if (p == 0) return (x == 0) ? (LOG ? 0.0 : 1.0) : (LOG ? -INFINITY : 0.0);
+    if (q == 0) return (x == n) ? (LOG ? 0.0 : 1.0) : (LOG ? -INFINITY : 0.0);
+    double lc;
+    if (x == 0) {
+        if (n == 0) return LOG ? 0.0 : 1.0;
+        lc = (p < 0.1) ? -bd0(n, n * q) - n * p : n * log(q);
+        return LOG ? lc : exp(lc);
+    }
+    if (x == n) {
+        lc = (q < 0.1) ? -bd0(n, n * p) - n * q : n * log(p);
+        return LOG ? lc : exp(lc);
+    }
+    if (x < 0 || x > n) return LOG ? -INFINITY : 0.0;
+    lc = stirlerr(n) - stirlerr(x) - stirlerr(n - x) - bd0(x, n * p) - bd0(n - x, n * q);
+    const double lf = CBS_LN_2PI + log(x) + log1p(-x / n);
+    return LOG ? (lc - 0.5 * lf) : exp(lc - 0.5 * lf);
+}
+
+// dnbinom(x; mu, size) for integer-valued x >= 0 (helper_seq.R:28), linear or log scale
+template <bool LOG>
+__device__ __forceinline__ double dnbinom_mu(double x, double size, double mu) {
+    if (isnan(x) || isnan(size) || isnan(mu)) return x + size + mu;
+    if (mu < 0 || size < 0) return nan("");
+    if (x < 0 || !isfinite(x)) return LOG ? -INFINITY : 0.0;
+    if (x == 0 && size == 0) return LOG ? 0.0 : 1.0;
+    if (!isfinite(size)) {  // Poisson limit
+        if (mu == 0) return (x == 0) ? (LOG ? 0.0 : 1.0) : (LOG ? -INFINITY : 0.0);
+        if (x == 0) return LOG ? -mu : exp(-mu);
+        const double l = -stirlerr(x) - bd0(x, mu) - 0.5 * log(CBS_2PI * x);
+        return LOG ? l : exp(l);
+    }
+    if (x == 0) {
+        const double l = size * (size < mu ? log(size / (size + mu)) : log1p(-mu / (size + mu)));
+        return LOG ? l : exp(l);
+    }
+    if (x < 1e-10 * size) {
+        const double p = (size < mu ? log(size / (1 + size / mu)) : log(mu / (1 + mu / size)));
+        const double l = x * p - mu - lgamma(x + 1) + log1p(x * (x - 1) / (2 * size));
+        return LOG ? l : exp(l);
+    }
+    const double p = size / (size + x);
+    const double ans = dbinom_raw<LOG>(size, x + size, size / (size + mu), mu / (size + mu));
+    return LOG ? (log(p) + ans) : (p * ans);
+}
+
+// x^a y^b / B(a,b) in saddle-point form (valid for all a, b > 0)
+__device__ __forceinline__ double brcomp(double a, double b, double x, double y) {
+    if (x == 0 || y == 0) return 0.0;
+    const double n = a + b;
+    const double lc = stirlerr(n) - stirlerr(a) - stirlerr(b) - bd0(a, n * x) - bd0(b, n * y);
+    return sqrt(a * b / (n * CBS_2PI)) * exp(lc);
+}
+
+// TOMS 708 continued fraction for I_x(a,b), lambda = (a+b)y - b >= 0
+__device__ __forceinline__ double bfrac(double a, double b, double x, double y, double lambda, double eps) {
+    const double brc = brcomp(a, b, x, y);
+    if (brc == 0.) return 0.;
+    const double c = lambda + 1., c0 = b / a, c1 = 1. / a + 1., yp1 = y + 1.;
+    double n = 0., p = 1., s = a + 1., an = 0., bn = 1., anp1 = 1., bnp1 = c / c1, r = c1 / c;
+    do {
+        n += 1.;
+        double t = n / a;
+        const double w = n * (b - n) * x;
+        double e = a / s;
+        const double alpha = p * (p + c0) * e * e * (w * x);
+        e = (t + 1.) / (c1 + t + t);
+        const double beta = n + w / s + e * (c + n * yp1);
+        p = t + 1.;
+        s += 2.;
+        t = alpha * an + beta * anp1; an = anp1; anp1 = t;
+        t = alpha * bn + beta * bnp1; bn = bnp1; bnp1 = t;
+        const double r0 = r;
+        r = anp1 / bnp1;
+        if (fabs(r - r0) <= eps * r) break;
+        an /= bnp1; bn /= bnp1; anp1 = r; bnp1 = 1.;
+    } while (n < 10000);
+    return brc * r;
+}
+
+// regularised incomplete beta I_x(a,b) (w) and its complement (w1); y = 1 - x is passed separately
+__device__ __forceinline__ void bratio(double a, double b, double x, double y, double* w, double* w1) {
+    if (isnan(a) || isnan(b) || isnan(x) || isnan(y) || a < 0 || b < 0 || x < 0 || x > 1) { *w = *w1 = nan(""); return; }
+    if (x == 0) { *w = 0; *w1 = 1; return; }
+    if (y == 0) { *w = 1; *w1 = 0; return; }
+    if (a == 0) { *w = 1; *w1 = 0; return; }
+    if (b == 0) { *w = 0; *w1 = 1; return; }
+    const double eps = 2 * DBL_EPSILON;
+    const double lambda = (a > b) ? (a + b) * y - b : a - (a + b) * x;
+    if (lambda >= 0) {
+        *w = bfrac(a, b, x, y, lambda, eps);
+        *w1 = 0.5 - *w + 0.5;
+    } else {
+        *w1 = bfrac(b, a, y, x, -lambda, eps);
+        *w = 0.5 - *w1 + 0.5;
+    }
+}
+
+// pnbinom(q; mu, size), lower tail (helper_seq.R:53)
+__device__ __forceinline__ double pnbinom_mu(double x, double size, double mu) {
+    if (isnan(x) || isnan(size) || isnan(mu)) return x + size + mu;
+    if (!isfinite(mu) || size < 0 || mu < 0) return nan("");
+    if (size == 0) return (x >= 0) ? 1.0 : 0.0;
+    if (x < 0) return 0.0;
+    if (!isfinite(x)) return 1.0;
+    x = floor(x + 1e-7);
+    double w, wc;
+    bratio(size, x + 1, size / (size + mu), mu / (size + mu), &w, &wc);
+    return w;
+}
+
+// pnbinom(q; size, prob), lower tail
+__device__ __forceinline__ double pnbinom_prob(double x, double size, double prob) {
+    if (isnan(x) || isnan(size) || isnan(prob)) return x + size + prob;
+    if (!isfinite(size) || !isfinite(prob) || size < 0 || prob <= 0 || prob > 1) return nan("");
+    if (size == 0) return (x >= 0) ? 1.0 : 0.0;
+    if (x < 0) return 0.0;
+    if (!isfinite(x)) return 1.0;
+    x = floor(x + 1e-7);
+    double w, wc;
+    bratio(size, x + 1, prob, 0.5 - prob + 0.5, &w, &wc);
+    return w;
+}
+
+// standard normal quantile, AS 241 (PPND16)
+__device__ __forceinline__ double qnorm01(double p) {
+    if (isnan(p)) return p;
+    if (p <= 0) return (p == 0) ? -INFINITY : nan("");
+    if (p >= 1) return (p == 1) ? INFINITY : nan("");
+    const double q = p - 0.5;
+    double r, val;
+    if (fabs(q) <= .425) {
+        r = .180625 - q * q;
+        val = q * (((((((r * 2509.0809287301226727 + 33430.575583588128105) * r + 67265.770927008700853) * r
+                        + 45921.953931549871457) * r + 13731.693765509461125) * r + 1971.5909503065514427) * r
+                        + 133.14166789178437745) * r + 3.387132872796366608)
+            / (((((((r * 5226.495278852854561 + 28729.085735721942674) * r + 39307.89580009271061) * r
+                        + 21213.794301586595867) * r + 5394.1960214247511077) * r + 687.1870074920579083) * r
+                        + 42.313330701600911252) * r + 1.);
+        return val;
+    }
+    r = (q < 0) ? p : (0.5 - p + 0.5);
+    r = sqrt(-log(r));
+    if (r <= 5.) {
+        r += -1.6;
+        val = (((((((r * 7.7454501427834140764e-4 + .0227238449892691845833) * r + .24178072517745061177) * r
+                      + 1.27045825245236838258) * r + 3.64784832476320460504) * r + 5.7694972214606914055) * r
+                      + 4.6303378461565452959) * r + 1.42343711074968357734)
+            / (((((((r * 1.05075007164441684324e-9 + 5.475938084995344946e-4) * r + .0151986665636164571966) * r
+                      + .14810397642748007459) * r + .68976733498510000455) * r + 1.6763848301838038494) * r
+                      + 2.05319162663775882187) * r + 1.);
+    } else {
+        r += -5.;
+        val = (((((((r * 2.01033439929228813265e-7 + 2.71155556874348757815e-5) * r + .0012426609473880784386) * r
+                      + .026532189526576123093) * r + .29656057182850489123) * r + 1.7848265399172913358) * r
+                      + 5.4637849111641143699) * r + 6.6579046435011037772)
+            / (((((((r * 2.04426310338993978564e-15 + 1.4215117583164458887e-7) * r + 1.8463183175100546818e-5) * r
+                      + 7.868691311456132591e-4) * r + .0148753612908506148525) * r + .13692988092273580531) * r
+                      + .59983220655588793769) * r + 1.);
+    }
+    return (q < 0.0) ? -val : val;
+}
+
+// discrete search on the incr-grid: returns y with F(y) >= p and F(y - incr) < p (or y == 0); *z = F(y)
+__device__ __forceinline__ double qnb_search(double y, double* z, double p, double n, double pr, double incr) {
+    if (*z >= p) {
+        for (;;) {
+            double newz;
+            if (y == 0 || (newz = pnbinom_prob(y - incr, n, pr)) < p) return y;
+            y = fmax(0.0, y - incr);
+            *z = newz;
+        }
+    } else {
+        for (;;) {
+            y = y + incr;
+            if ((*z = pnbinom_prob(y, n, pr)) >= p) return y;
+        }
+    }
+}
+
+// qnbinom(p; size, prob): smallest integer y >= 0 with pnbinom(y) >= p*(1-64*DBL_EPSILON)
+__device__ __forceinline__ double qnbinom_prob(double p, double size, double prob) {
+    if (isnan(p) || isnan(size) || isnan(prob)) return p + size + prob;
+    if (prob == 0 && size == 0) return 0;
+    if (prob <= 0 || prob > 1 || size < 0) return nan("");
+    if (prob == 1 || size == 0) return 0;
+    if (p < 0 || p > 1) return nan("");
+    if (p == 0) return 0;
+    if (p == 1) return INFINITY;
+    const double Q = 1.0 / prob, P = (1.0 - prob) * Q, mu = size * P, sigma = sqrt(size * P * Q);
+    const double gamma = (Q + P) / sigma;
+    if (p + 1.01 * DBL_EPSILON >= 1.) return INFINITY;
+    double z = qnorm01(p);
+    double y = nearbyint(mu + sigma * (z + gamma * (z * z - 1) / 6));
+    if (!(y >= 0)) y = 0;      // Cornish-Fisher can undershoot 0 for very skewed distributions; F(y<0) = 0 anyway
+    z = pnbinom_prob(y, size, prob);
+    p *= 1 - 64 * DBL_EPSILON;
+    if (y < 1e5) return qnb_search(y, &z, p, size, prob, 1);
+    double incr = floor(y * 0.001), oldincr;
+    do {
+        oldincr = incr;
+        y = qnb_search(y, &z, p, size, prob, incr);
+        incr = fmax(1.0, floor(incr / 100));
+    } while (oldincr > 1 && incr > y * 1e-15);
+    return y;
+}
+
+// qnbinom(p; mu, size) (helper_seq.R:58)
+__device__ __forceinline__ double qnbinom_mu(double p, double size, double mu) {
+    if (!isfinite(size)) return nan("");
+    return qnbinom_prob(p, size, size / (size + mu));
+}
+
+}  // namespace cbs

@@ -1,0 +1,163 @@
+// stages.inl — internal device-level stage drivers shared by the per-subsystem entry points and cbs_combat_seq().
+// Included by combatseq.cu inside no namespace; everything here is static.
+
+namespace cbs {
+
+struct AplJob { int design; double phi; };
+
+// gene shard [g0,g1) of rank r: contiguous blocks rounded to the APL reduction chunk so that the chunk partial
+// sums (and therefore disp_common and everything downstream) are identical for every GPU count.
+static void shard_range(long G, int rank, int world, long* g0, long* g1) {
+    long per = (G + world - 1) / world;
+    per = (per + APL_CHUNK - 1) / APL_CHUNK * APL_CHUNK;
+    *g0 = std::min(G, (long)rank * per);
+    *g1 = std::min(G, (long)(rank + 1) * per);
+}
+
+// APL of genes [g0,g1) for every job -> d_apl[job*G + g]
+static void launch_apl(const int32_t* cnt, long G, long g0, long g1, const double* logoff, const DesignDev* designs,
+                       const unsigned char* sel, const double* phi_gene, const std::vector<AplJob>& jobs, double* d_apl,
+                       cudaStream_t st) {
+    if (g1 <= g0) return;
+    for (size_t e0 = 0; e0 < jobs.size(); e0 += APL_MAX_EVALS) {
+        AplLaunch L;
+        L.n_evals = (int)std::min<size_t>(APL_MAX_EVALS, jobs.size() - e0);
+        for (int e = 0; e < L.n_evals; ++e) { L.design[e] = jobs[e0 + e].design; L.phi[e] = jobs[e0 + e].phi; }
+        dim3 grid((unsigned)((g1 - g0 + 127) / 128), (unsigned)L.n_evals);
+        CBS_LAUNCH(k_apl, grid, 128, 0, st, cnt, G, g0, g1, logoff, designs, sel,
+                   phi_gene ? phi_gene + e0 * G : nullptr, L, d_apl + e0 * G);
+    }
+}
+
+// per-job sum over the selected genes, deterministic: chunk partials on the device (tree order inside a chunk),
+// all-reduced across ranks (each rank owns disjoint chunks, the others contribute exact zeros) and added on the
+// host in chunk order.
+static void apl_sums(const double* d_apl, long G, long g0, long g1, const unsigned char* sel,
+                     const std::vector<AplJob>& jobs, cbs_comm* comm, cudaStream_t st, std::vector<double>& sums) {
+    const long nchunk = (G + APL_CHUNK - 1) / APL_CHUNK;
+    const size_t nj = jobs.size();
+    double* d_part = g_dev.get<double>("apl_partial", nj * nchunk);
+    CBS_CUDA(cudaMemsetAsync(d_part, 0, nj * nchunk * sizeof(double), st));
+    const long c0 = g0 / APL_CHUNK, c1 = (g1 + APL_CHUNK - 1) / APL_CHUNK;
+    if (c1 > c0)
+        for (size_t e0 = 0; e0 < nj; e0 += APL_MAX_EVALS) {
+            AplLaunch L;
+            L.n_evals = (int)std::min<size_t>(APL_MAX_EVALS, nj - e0);
+            for (int e = 0; e < L.n_evals; ++e) { L.design[e] = jobs[e0 + e].design; L.phi[e] = jobs[e0 + e].phi; }
+            dim3 grid((unsigned)(c1 - c0), (unsigned)L.n_evals);
+            CBS_LAUNCH(k_chunk_sum, grid, 256, 0, st, d_apl + e0 * G, G, sel, L, c0, d_part + e0 * nchunk, nchunk);
+        }
+    if (comm && comm->world > 1)
+        CBS_NCCL(nccl_api()->AllReduce(d_part, d_part, nj * nchunk, NCCL_FLOAT64, NCCL_SUM, comm->nccl, st));
+    std::vector<double> h(nj * nchunk);
+    CBS_CUDA(cudaMemcpyAsync(h.data(), d_part, h.size() * sizeof(double), cudaMemcpyDeviceToHost, st));
+    CBS_CUDA(cudaStreamSynchronize(st));
+    sums.assign(nj, 0.0);
+    for (size_t e = 0; e < nj; ++e) { double s = 0; for (long c = 0; c < nchunk; ++c) s += h[e * nchunk + c]; sums[e] = s; }
+}
+
+// estimateGLMCommonDisp for several (batch) designs at once: the Brent searches advance in lock-step, one APL
+// launch per step evaluates every unfinished batch at its current delta.  designs[b] is batch b's DesignDev,
+// sel[b*G+g] its rowSums>=5 mask.  Returns NaN for a batch whose design has p >= n (edgeR: warning + NA).
+static void run_common_disp(const int32_t* cnt, long G, long g0, long g1, const double* logoff, const DesignSet& ds,
+                            const unsigned char* sel, cbs_comm* comm, cudaStream_t st, std::vector<double>& common,
+                            int* n_steps) {
+    const int nb = (int)ds.h_array.size();
+    common.assign(nb, std::nan(""));
+    std::vector<BrentFmin> br(nb);
+    std::vector<char> active(nb, 0);
+    for (int b = 0; b < nb; ++b)
+        if (ds.h_array[b].p < ds.h_array[b].n) { br[b].init(0.0, std::pow(4.0, 0.25), 1e-5); active[b] = 1; }
+    double* d_apl = g_dev.get<double>("apl_common", (size_t)nb * G);
+    int steps = 0;
+    for (;;) {
+        std::vector<AplJob> jobs;
+        std::vector<int> who;
+        for (int b = 0; b < nb; ++b)
+            if (active[b] && !br[b].done) { const double x = br[b].query(); jobs.push_back({b, x * x * x * x}); who.push_back(b); }
+        if (jobs.empty()) break;
+        launch_apl(cnt, G, g0, g1, logoff, ds.d_array, sel, nullptr, jobs, d_apl, st);
+        std::vector<double> sums;
+        apl_sums(d_apl, G, g0, g1, sel, jobs, comm, st, sums);
+        for (size_t k = 0; k < who.size(); ++k) br[who[k]].feed(-sums[k]);     // optimize(maximum = TRUE)
+        ++steps;
+    }
+    for (int b = 0; b < nb; ++b) if (active[b]) { const double x = br[b].result(); common[b] = x * x * x * x; }
+    if (n_steps) *n_steps = steps;
+}
+
+// estimateGLMTagwiseDisp(prior.df = 0) for the batches with do_batch[b] != 0: phi_hat[g + b*G] for g in [g0,g1).
+// Batches with do_batch[b] == 0 get rep(common[b]) (ComBat_seq.R:113).
+static void run_tagwise_disp(const int32_t* cnt, long G, long g0, long g1, const double* logoff, const DesignSet& ds,
+                             const unsigned char* sel, const std::vector<double>& common, const std::vector<char>& do_batch,
+                             cudaStream_t st, double* d_phi_hat) {
+    const int nb = (int)ds.h_array.size();
+    if (g1 <= g0) return;
+    std::vector<AplJob> jobs;
+    std::vector<int> job0(nb, -1);
+    for (int b = 0; b < nb; ++b) {
+        if (!do_batch[b]) continue;
+        job0[b] = (int)jobs.size();
+        for (int k = 0; k < 11; ++k) jobs.push_back({b, common[b] * std::pow(2.0, -6.0 + k * (12.0 / 10))});
+    }
+    double* d_apl = jobs.empty() ? nullptr : g_dev.get<double>("apl_grid", jobs.size() * (size_t)G);
+    if (!jobs.empty()) launch_apl(cnt, G, g0, g1, logoff, ds.d_array, sel, nullptr, jobs, d_apl, st);
+    for (int b = 0; b < nb; ++b) {
+        if (do_batch[b]) {
+            CBS_LAUNCH(k_tagwise_max, grid1(g1 - g0, 128), 128, 0, st, d_apl + (size_t)job0[b] * G, G, g0, g1,
+                       sel ? sel + (size_t)b * G : nullptr, common[b], d_phi_hat + (size_t)b * G);
+        } else {
+            CBS_LAUNCH(k_fill, grid1(g1 - g0, 256), 256, 0, st, d_phi_hat + (size_t)b * G + g0, g1 - g0, common[b]);
+        }
+    }
+}
+
+// glmFit.default(prior.count) on genes [g0,g1): coef (G x p, may be null) from the prior-count refit when
+// prior_count > 0 else from the plain fit; fitted (G x N, may be null) from the plain fit; alpha (G, may be null)
+// = sum_b alpha_w[b] * coef[g,b].  d_lib is the per-sample library size on the device (N); h_lib the host copy.
+static void run_glm_fit(const int32_t* cnt, long G, long g0, long g1, int N, const double* d_logoff,
+                        const std::vector<double>& h_lib, const double* d_phi, const int* d_phi_col,
+                        const DesignDev* d_design, const double* d_goff, double prior_count, double* d_coef,
+                        double* d_fitted, const double* d_alpha_w, int n_alpha, double* d_alpha, cudaStream_t st) {
+    if (g1 <= g0) return;
+    const dim3 grid = grid1(g1 - g0, 128);
+    double two_prior = 0;
+    const double* d_yadd = nullptr;
+    if (prior_count > 0) {
+        double meanlib = 0;
+        for (int s = 0; s < N; ++s) meanlib += h_lib[s];
+        meanlib /= N;
+        std::vector<double> yadd(N);
+        for (int s = 0; s < N; ++s) yadd[s] = prior_count * h_lib[s] / meanlib;     // add_prior.cpp
+        d_yadd = upload(g_dev, "glm_yadd", yadd.data(), (size_t)N, st);
+        two_prior = 2 * prior_count / meanlib;
+    }
+    if (d_fitted || (prior_count <= 0 && (d_coef || d_alpha)))
+        CBS_LAUNCH(k_glm_fit, grid, 128, 0, st, cnt, G, g0, g1, d_logoff, (const double*)nullptr, 0.0, d_phi, d_phi_col,
+                   d_design, d_goff, 0, prior_count > 0 ? (double*)nullptr : d_coef, d_fitted, d_alpha_w, n_alpha,
+                   prior_count > 0 ? (double*)nullptr : d_alpha);
+    if (prior_count > 0 && (d_coef || d_alpha))
+        CBS_LAUNCH(k_glm_fit, grid, 128, 0, st, cnt, G, g0, g1, d_logoff, d_yadd, two_prior, d_phi, d_phi_col, d_design,
+                   d_goff, 1, d_coef, (double*)nullptr, d_alpha_w, n_alpha, d_alpha);
+}
+
+// monte_carlo_int_NB for one batch, targets [i0,i1); sources are all G genes.  d_cols: the batch's columns (n).
+static void run_mc_batch(const int32_t* cnt, long G, int n, const int* d_cols, long i0, long i1, const double* d_mu_hat,
+                         const double* d_gamma, const double* d_phi, int mc_mode, int subset_n, uint64_t seed,
+                         double* d_gamma_star, double* d_phi_star, unsigned long long* d_nfb, cudaStream_t st) {
+    double* A = g_dev.get<double>("mc_A", (size_t)n * G);
+    double* cj = g_dev.get<double>("mc_cj", (size_t)G);
+    double* rj = g_dev.get<double>("mc_rj", (size_t)G);
+    double* lgr = g_dev.get<double>("mc_lgr", (size_t)G);
+    double* di = g_dev.get<double>("mc_di", (size_t)G);
+    CBS_LAUNCH(k_mc_prep_src, grid1(G, 128), 128, 0, st, d_mu_hat, G, n, d_cols, d_phi, A, cj, rj, lgr);
+    CBS_LAUNCH(k_mc_prep_tgt, grid1(G, 128), 128, 0, st, cnt, G, n, d_cols, di);
+    if (i1 <= i0) return;
+    if (subset_n >= G - 1) subset_n = 0;      // sample(1:(G-1), G-1) is a permutation of all other genes
+    const size_t smem = (size_t)MC_TI * n * sizeof(double);
+    const unsigned nblk = (unsigned)((i1 - i0 + MC_TI - 1) / MC_TI);
+    CBS_LAUNCH(k_mc_direct, dim3(nblk), 256, smem, st, cnt, G, n, d_cols, i0, i1, A, cj, rj, lgr, di, d_gamma, d_phi,
+               mc_mode == CBS_MC_STABLE ? 1 : 0, subset_n, seed, d_gamma_star, d_phi_star, d_nfb);
+}
+
+}  // namespace cbs

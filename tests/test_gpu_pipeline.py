@@ -1,0 +1,119 @@
+"""-m gpu: the CUDA pipeline (through the C ABI) against the CPU oracle on the same seeded inputs.
+
+Bars (BASELINE.json north_star): adjusted counts >= 99.99 % exact with every flip listed; gamma_hat / phi_hat
+within 1e-6 relative, stated form |a-b| <= 1e-6*|b| + 1e-9.
+"""
+import numpy as np
+import pytest
+
+from conftest import rel_err
+
+pytestmark = pytest.mark.gpu
+
+
+def run_both(pkg, oracle, case, **extra):
+    kw = case.kwargs(); kw.update(extra)
+    res = pkg.ComBat_seq(case.counts, case.batch, return_details=True, verbose=False, **kw)
+    d = res["design"]
+    ref = oracle.combat_seq(case.counts.astype(np.float64), d.batch_idx, d.mod, shrink=kw["shrink"],
+                            shrink_disp=kw["shrink_disp"], gene_subset_n=0, nthreads=oracle.max_threads(),
+                            mc_mode=1 if extra.get("mc_mode") == "stable" else 0)
+    return res, ref
+
+
+def check_parity(res, ref, min_exact=0.9999, check_star=True):
+    assert np.array_equal(res["keep"], ref["keep"])
+    assert np.array_equal(res["lib_size"], ref["lib_size"])
+    assert rel_err(res["disp_common"], ref["disp_common"]) <= 1.0
+    assert rel_err(res["phi_hat"], ref["phi_hat"]) <= 1.0
+    assert rel_err(res["gamma_hat"], ref["gamma_hat"]) <= 1.0
+    assert rel_err(res["mu_hat"], ref["mu_hat"], rtol=1e-6, atol=1e-9) <= 1.0
+    if check_star:
+        assert rel_err(res["gamma_star"], ref["gamma_star"]) <= 1.0
+        assert rel_err(res["phi_star"], ref["phi_star"]) <= 1.0
+    a, b = np.asarray(res["adjusted"]), ref["adjusted"]
+    flips = np.argwhere(a != b)
+    exact = 1.0 - flips.shape[0] / a.size
+    for g, s in flips[:20]:
+        print("flip g=%d s=%d ref=%g got=%g" % (g, s, b[g, s], a[g, s]))
+    assert exact >= min_exact, "exact-match %.6f" % exact
+    return exact
+
+
+@pytest.mark.parametrize("name", ["C1", "C1g", "C1c"])
+def test_readme_examples(pkg, oracle, synth, name):
+    case = synth.CASES[name](G=50)
+    res, ref = run_both(pkg, oracle, case)
+    assert check_parity(res, ref) == 1.0
+
+
+def test_c2_small(pkg, oracle, synth):
+    res, ref = run_both(pkg, oracle, synth.c2(G=3000))
+    check_parity(res, ref)
+    assert (res["keep"] == 0).any(), "the zero filter should drop some genes"
+    dropped = res["keep"] == 0
+    assert np.array_equal(np.asarray(res["adjusted"])[dropped], synth.c2(G=3000).counts[dropped])
+
+
+@pytest.mark.parametrize("crossed", [False, True])
+def test_c3_small(pkg, oracle, synth, crossed):
+    res, ref = run_both(pkg, oracle, synth.c3(G=2000, crossed=crossed))
+    check_parity(res, ref)
+
+
+def test_c4_small_shrink(pkg, oracle, synth):
+    case = synth.c4(G=600, n=6)
+    res, ref = run_both(pkg, oracle, case)
+    check_parity(res, ref)
+    assert np.array_equal(res["n_mc_fallback"], ref["n_mc_fallback"])
+    # shrink.disp = FALSE  =>  phi_star_mat == phi_hat  (ComBat_seq.R:162-165)
+    assert np.array_equal(res["phi_star"], res["phi_hat"], equal_nan=True)
+
+
+def test_c5_small_shrink_disp(pkg, oracle, synth):
+    case = synth.c5(G=500, n=5, B=3)
+    res, ref = run_both(pkg, oracle, case)
+    check_parity(res, ref)
+
+
+def test_mc_underflow_fallback(pkg, oracle, synth):
+    # n_b = 300 samples: prod(dnbinom) underflows for (almost) every pair -> helper_seq.R:30-31 fallback
+    case = synth.c4(G=150, n=300)
+    res, ref = run_both(pkg, oracle, case)
+    assert ref["n_mc_fallback"].sum() > 0
+    assert np.array_equal(res["n_mc_fallback"], ref["n_mc_fallback"])
+    check_parity(res, ref)
+
+
+def test_mc_stable_mode(pkg, oracle, synth):
+    case = synth.c4(G=400, n=30)
+    res, ref = run_both(pkg, oracle, case, mc_mode="stable")
+    assert res["n_mc_fallback"].sum() == 0
+    check_parity(res, ref)
+
+
+def test_int32_and_float_inputs_agree(pkg, synth):
+    case = synth.c2(G=1000)
+    a = pkg.ComBat_seq(case.counts.astype(np.int32), case.batch, group=case.group, verbose=False)
+    b = pkg.ComBat_seq(case.counts.astype(np.float64), case.batch, group=case.group, verbose=False)
+    assert np.array_equal(a, b)
+
+
+def test_identity_when_no_batch_effect_parameters(pkg):
+    # match_quantiles is the identity when new == old distribution (needs the 64*eps fuzz of qnbinom)
+    rng = np.random.default_rng(0)
+    G, n = 2000, 6
+    mu = np.exp(rng.normal(4, 1.5, (G, n)))
+    phi = rng.uniform(0.01, 1.0, G)
+    x = rng.poisson(mu).astype(np.int32)
+    out = pkg._lib.match_quantiles(x, mu, phi, mu, phi)
+    assert np.array_equal(out, x.astype(np.float64))
+
+
+def test_error_strings(pkg):
+    rng = np.random.default_rng(0)
+    counts = rng.negative_binomial(10, 0.1, size=(20, 6))
+    with pytest.raises(ValueError, match="doesn't support 1 sample per batch"):
+        pkg.ComBat_seq(counts, [1, 1, 1, 2, 2, 3], verbose=False)
+    with pytest.raises(ValueError, match="The covariate is confounded with batch"):
+        pkg.ComBat_seq(counts, [1, 1, 1, 2, 2, 2], group=[0, 0, 0, 1, 1, 1], verbose=False)
