@@ -25,7 +25,7 @@ STAGES = ("h2d", "prep", "common_disp", "tagwise_disp", "glm", "mc", "match_quan
 EXPORTS = ("cbs_version", "cbs_device_count", "cbs_last_error", "cbs_shutdown", "cbs_kernel_launches",
            "cbs_comm_unique_id", "cbs_comm_create", "cbs_comm_destroy", "cbs_combat_seq", "cbs_nb_logpmf",
            "cbs_nb_cdf", "cbs_nb_quantile", "cbs_glm_fit", "cbs_apl", "cbs_common_disp", "cbs_tagwise_disp",
-           "cbs_mc_int", "cbs_match_quantiles")
+           "cbs_mc_int", "cbs_match_quantiles", "cbs_profile_enable", "cbs_profile_dump", "cbs_fp64_peak")
 
 
 class CbsInput(C.Structure):
@@ -81,6 +81,27 @@ def device_count():
 
 def kernel_launches():
     return int(lib().cbs_kernel_launches())
+
+
+def profile_enable(on=True):
+    check(lib().cbs_profile_enable(int(on)))
+
+
+def profile_dump():
+    """{kernel name: (total device ms, launches)} since profile_enable(True)."""
+    buf = C.create_string_buffer(1 << 16)
+    check(lib().cbs_profile_dump(buf, C.c_size_t(len(buf))))
+    out = {}
+    for line in buf.value.decode().splitlines():
+        name, ms, n = line.rsplit(" ", 2)
+        out[name] = (float(ms), int(n))
+    return out
+
+
+def fp64_peak_tflops():
+    v = C.c_double(0)
+    check(lib().cbs_fp64_peak(C.byref(v)))
+    return v.value
 
 
 def _d(a):
@@ -194,7 +215,7 @@ def comm_destroy(h):
 # ---- the whole pipeline ------------------------------------------------------------------------------------------
 def combat_seq_raw(counts, batch_idx, mod, shrink=False, shrink_disp=False, gene_subset_n=0, seed=0,
                    mc_mode=CBS_MC_REFERENCE, use_fallback=None, device=-1, comm=None, want=("adjusted",),
-                   counts_dev_ptr=None, adjusted_dev_ptr=None, shape=None):
+                   counts_dev_ptr=None, adjusted_dev_ptr=None, shape=None, adjusted_out=None):
     """cbs_combat_seq().  `want` selects the optional outputs; returns a dict.  counts may be float64 or int32
     (column-major is used as is; anything else is copied).  counts_dev_ptr/adjusted_dev_ptr (+ shape) run the
     device-resident variant used by bench.py's kernel-only timing."""
@@ -229,7 +250,11 @@ def combat_seq_raw(counts, batch_idx, mod, shrink=False, shrink_disp=False, gene
         if k in shapes:
             if k == "adjusted" and adjusted_dev_ptr is not None:
                 continue
-            res[k] = np.empty(shapes[k], order="F")
+            if k == "adjusted" and adjusted_out is not None:
+                assert adjusted_out.flags.f_contiguous and adjusted_out.dtype == np.float64 and adjusted_out.shape == (G0, N)
+                res[k] = adjusted_out
+            else:
+                res[k] = np.empty(shapes[k], order="F")
             setattr(out, k, res[k].ctypes.data_as(C.c_void_p) if k == "adjusted" else _p(res[k]))
     if adjusted_dev_ptr is not None:
         out.adjusted = C.c_void_p(adjusted_dev_ptr); out.adjusted_on_device = 1
@@ -242,3 +267,8 @@ def combat_seq_raw(counts, batch_idx, mod, shrink=False, shrink_disp=False, gene
     res["stage_ms"] = dict(zip(STAGES, stage.tolist()))
     res["row_begin"], res["row_end"] = int(out.row_begin), int(out.row_end)
     return res
+
+
+def combat_seq_into(counts, batch_idx, mod, adjusted_out, **kw):
+    """cbs_combat_seq() writing the adjusted matrix into a caller-owned column-major float64 buffer (e.g. pinned)."""
+    return combat_seq_raw(counts, batch_idx, mod, want=("adjusted",), adjusted_out=adjusted_out, **kw)

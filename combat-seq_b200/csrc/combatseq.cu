@@ -170,5 +170,6 @@ int cbs_comm_destroy(cbs_comm* c) {
 
 }  // extern "C"
 
+#include "profile.inl"
 #include "api_subsystems.inl"
 #include "api_pipeline.inl"

@@ -40,10 +40,16 @@ struct CbsError { int code; };   // thrown inside the library only; every extern
 // every kernel launch goes through this macro so that cbs_kernel_launches() is the library's own count
 #define CBS_LAUNCH(kernel, grid, block, smem, stream, ...)                                          \
     do {                                                                                            \
+        cudaEvent_t pe_ = cbs::prof_begin(#kernel, (stream));                                       \
         kernel<<<(grid), (block), (smem), (stream)>>>(__VA_ARGS__);                                 \
+        cbs::prof_end(pe_, (stream));                                                               \
         cbs::g_launches.fetch_add(1, std::memory_order_relaxed);                                    \
         CBS_CUDA(cudaGetLastError());                                                               \
     } while (0)
+
+// optional per-kernel device timing (cbs_profile_enable): events on the launching stream around each launch
+cudaEvent_t prof_begin(const char* name, cudaStream_t st);   // nullptr when profiling is off
+void prof_end(cudaEvent_t begin, cudaStream_t st);
 
 // Grow-only cache of named device buffers (per process, current device).  Released by cbs_shutdown().
 class DevCache {

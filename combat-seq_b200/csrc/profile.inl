@@ -1,0 +1,108 @@
+// profile.inl — measurement hooks: per-kernel CUDA-event timing and the FP64 FMA peak microbenchmark.
+namespace cbs {
+
+struct ProfRec { std::string name; cudaEvent_t e0, e1; };
+static bool g_prof_on = false;
+static std::vector<ProfRec> g_prof_pending;
+static std::map<std::string, std::pair<double, long>> g_prof_acc;     // name -> (total ms, launches)
+static std::vector<cudaEvent_t> g_prof_pool;
+
+static cudaEvent_t prof_event() {
+    if (!g_prof_pool.empty()) { cudaEvent_t e = g_prof_pool.back(); g_prof_pool.pop_back(); return e; }
+    cudaEvent_t e = nullptr;
+    cudaEventCreate(&e);
+    return e;
+}
+cudaEvent_t prof_begin(const char* name, cudaStream_t st) {
+    if (!g_prof_on) return nullptr;
+    ProfRec r{name, prof_event(), prof_event()};
+    cudaEventRecord(r.e0, st);
+    g_prof_pending.push_back(r);
+    return r.e0;
+}
+void prof_end(cudaEvent_t begin, cudaStream_t st) {
+    if (!begin) return;
+    cudaEventRecord(g_prof_pending.back().e1, st);
+}
+static void prof_collect() {
+    if (g_prof_pending.empty()) return;
+    cudaDeviceSynchronize();
+    for (auto& r : g_prof_pending) {
+        float ms = 0;
+        if (cudaEventElapsedTime(&ms, r.e0, r.e1) == cudaSuccess) {
+            auto& a = g_prof_acc[r.name];
+            a.first += ms; a.second += 1;
+        }
+        g_prof_pool.push_back(r.e0); g_prof_pool.push_back(r.e1);
+    }
+    g_prof_pending.clear();
+    cudaGetLastError();
+}
+
+// 8 independent FMA chains per thread, 4096 FMAs per chain
+__global__ void __launch_bounds__(256) k_fp64_peak(double* out, double a, double b) {
+    double x0 = threadIdx.x, x1 = x0 + 1, x2 = x0 + 2, x3 = x0 + 3, x4 = x0 + 4, x5 = x0 + 5, x6 = x0 + 6, x7 = x0 + 7;
+#pragma unroll 1
+    for (int i = 0; i < 512; ++i) {
+#pragma unroll
+        for (int k = 0; k < 8; ++k) {
+            x0 = fma(x0, a, b); x1 = fma(x1, a, b); x2 = fma(x2, a, b); x3 = fma(x3, a, b);
+            x4 = fma(x4, a, b); x5 = fma(x5, a, b); x6 = fma(x6, a, b); x7 = fma(x7, a, b);
+        }
+    }
+    const double s = x0 + x1 + x2 + x3 + x4 + x5 + x6 + x7;
+    if (s == 123.456) out[0] = s;
+}
+
+}  // namespace cbs
+
+extern "C" {
+
+int cbs_profile_enable(int on) {
+    std::lock_guard<std::mutex> lock_(g_mutex);
+    if (on) { prof_collect(); g_prof_acc.clear(); }
+    else prof_collect();
+    g_prof_on = on != 0;
+    return CBS_OK;
+}
+int cbs_profile_dump(char* buf, size_t len) {
+    std::lock_guard<std::mutex> lock_(g_mutex);
+    if (!buf || len == 0) return fail(CBS_EINVAL, "null buffer");
+    prof_collect();
+    std::string s;
+    char line[256];
+    for (auto& kv : g_prof_acc) {
+        snprintf(line, sizeof line, "%s %.6f %ld\n", kv.first.c_str(), kv.second.first, kv.second.second);
+        s += line;
+    }
+    snprintf(buf, len, "%s", s.c_str());
+    return CBS_OK;
+}
+int cbs_fp64_peak(double* tflops) {
+    CBS_NEED_GPU();
+    if (!tflops) return fail(CBS_EINVAL, "null pointer");
+    CBS_ENTRY_BEGIN
+    int dev = 0, sms = 0;
+    CBS_CUDA(cudaGetDevice(&dev));
+    CBS_CUDA(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev));
+    double* d = g_dev.get<double>("fp64_peak", 8);
+    const int blocks = sms * 32;
+    cudaEvent_t e0, e1;
+    CBS_CUDA(cudaEventCreate(&e0)); CBS_CUDA(cudaEventCreate(&e1));
+    double best = 0;
+    for (int rep = 0; rep < 6; ++rep) {
+        CBS_CUDA(cudaEventRecord(e0, 0));
+        CBS_LAUNCH(k_fp64_peak, dim3(blocks), 256, 0, 0, d, 0.999999, 1e-6);
+        CBS_CUDA(cudaEventRecord(e1, 0));
+        CBS_CUDA(cudaEventSynchronize(e1));
+        float ms = 0;
+        CBS_CUDA(cudaEventElapsedTime(&ms, e0, e1));
+        const double flop = 2.0 * 8 * 8 * 512 * 256.0 * blocks;
+        if (rep > 0) best = std::max(best, flop / (ms * 1e-3) / 1e12);
+    }
+    cudaEventDestroy(e0); cudaEventDestroy(e1);
+    *tflops = best;
+    CBS_ENTRY_END
+}
+
+}  // extern "C"

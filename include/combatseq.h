@@ -59,6 +59,15 @@ const char* cbs_last_error(void);             /* thread-local text of the last f
 int         cbs_shutdown(void);               /* release cached device buffers / communicators */
 uint64_t    cbs_kernel_launches(void);        /* kernels launched by this library since load */
 
+/* ---- measurement hooks (bench.py) ---------------------------------------------------------------------
+ * cbs_profile_enable(1) clears the accumulators and brackets every kernel launch with CUDA events on the
+ * launching stream; cbs_profile_dump() writes one "kernel_name total_ms launches" line per kernel.
+ * cbs_fp64_peak() runs a dependent-chain-free DFMA microbenchmark and returns the achieved FP64 TFLOP/s
+ * (2 flop per FMA): the roofline denominator of the FP64-pipe-bound kernels (MEASURED_PEAKS.json has none). */
+int         cbs_profile_enable(int on);
+int         cbs_profile_dump(char* buf, size_t len);
+int         cbs_fp64_peak(double* tflops);
+
 /* ---- multi-process gene sharding (one process per GPU, e.g. under torchrun) ------------------------
  * Rank 0 calls cbs_comm_unique_id() and ships the 128 bytes to the other ranks by any means
  * (bench.py uses torch.distributed.broadcast); every rank then calls cbs_comm_create().

@@ -207,8 +207,10 @@ def combat_seq(counts, batch_idx, mod, shrink=False, shrink_disp=False, gene_sub
         setattr(out, k, _p(res[k]))
     out.keep = res["keep"].ctypes.data_as(u8p)
     out.n_mc_fallback = res["n_mc_fallback"].ctypes.data_as(i64p)
-    out.stage_ms = None
+    stage = np.zeros(9); out.stage_ms = _p(stage)
     rc = lib().ref_combat_seq(C.byref(inp), C.byref(out), C.c_int(nthreads), C.c_int(mc_target_stride))
     if rc != 0:
         raise OracleError(rc, lib().ref_last_error().decode())
+    res["stage_ms"] = dict(zip(("h2d", "prep", "common_disp", "tagwise_disp", "glm", "mc", "match_quantiles", "d2h", "total"),
+                               stage.tolist()))
     return res

@@ -15,6 +15,7 @@
 #include <limits>
 #include <algorithm>
 #include <random>
+#include <chrono>
 #ifdef _OPENMP
 #include <omp.h>
 #endif
@@ -65,7 +66,10 @@ static void mc_int_ref(long G, int n, const double* dat, const double* mu, const
                 }
                 double lh = (double)LH;
                 if (std::isnan(lh)) lh = 0;             // LH[is.nan(LH)] = 0  helper_seq.R:29
-                sumLH += lh; sumG += (long double)gamma[j] * lh; sumP += (long double)phi[j] * lh;
+                // gamma_sub*LH and phi_sub*LH are double vector products in R (they round in the denormal range
+                // when LH has underflowed gradually); only sum() accumulates in long double  (helper_seq.R:33)
+                const double gl = gamma[j] * lh, pl = phi[j] * lh;
+                sumLH += lh; sumG += gl; sumP += pl;
             } else {
                 double L = 0;
                 for (int s = 0; s < n; ++s) {
@@ -83,7 +87,8 @@ static void mc_int_ref(long G, int n, const double* dat, const double* mu, const
                     const long j = src.empty() ? jj : src[jj];
                     if (j == i || logw[jj] == -INFINITY) continue;
                     double w = std::exp(logw[jj] - smax);
-                    sumLH += w; sumG += (long double)gamma[j] * w; sumP += (long double)phi[j] * w;
+                    const double gl = gamma[j] * w, pl = phi[j] * w;
+                    sumLH += w; sumG += gl; sumP += pl;
                 }
         }
         double s = (double)sumLH;
@@ -126,6 +131,11 @@ const char* ref_last_error(void) { return g_err; }
 // unshrunk estimate): used ONLY by bench.py's bounded CPU baseline, never by parity tests.
 int ref_combat_seq(const cbs_input* in, cbs_output* out, int nthreads, int mc_target_stride) {
     const long G0 = in->G0; const int N = in->N, B = in->B, p_mod = in->p_mod;
+    double stage[CBS_N_STAGES] = {0};
+    auto clk = [] { return std::chrono::duration<double, std::milli>(std::chrono::steady_clock::now().time_since_epoch()).count(); };
+    const double t_begin = clk();
+    double t_last = t_begin;
+    auto lap = [&](int which) { const double t = clk(); stage[which] += t - t_last; t_last = t; };
     if (G0 <= 0 || N <= 0 || B <= 0 || p_mod < 1) return fail(CBS_EINVAL, "bad dimensions");
     if (B < 2) return fail(CBS_EINVAL, "ComBat-seq needs at least 2 batches");
     // ---- Preparation (ComBat_seq.R:25-51) ----
@@ -172,6 +182,7 @@ int ref_combat_seq(const cbs_input* in, cbs_output* out, int nthreads, int mc_ta
             return fail(CBS_ECONF_COVAR_WITH_BATCH, "At least one covariate is confounded with batch! Please remove confounded covariates and rerun ComBat-Seq");
         }
     }
+    lap(CBS_ST_PREP);
     // ---- dispersions within each batch (ComBat_seq.R:97-125) ----
     std::vector<double> disp_common(B), phi_hat((size_t)G * B);
     for (int b = 0; b < B; ++b) {
@@ -194,6 +205,7 @@ int ref_combat_seq(const cbs_input* in, cbs_output* out, int nthreads, int mc_ta
         }
     }
     if (out->disp_common) std::copy(disp_common.begin(), disp_common.end(), out->disp_common);
+    lap(CBS_ST_TAGWISE_DISP);      // common + tagwise together
     // phi_matrix (ComBat_seq.R:122-125)
     std::vector<double> phi_matrix((size_t)G * N);
     for (int s = 0; s < N; ++s) for (long i = 0; i < G; ++i) phi_matrix[i + (size_t)s * G] = phi_hat[i + (size_t)in->batch_idx[s] * G];
@@ -210,6 +222,7 @@ int ref_combat_seq(const cbs_input* in, cbs_output* out, int nthreads, int mc_ta
     Bcast o2{new_offset.data(), G, N, 3};
     glm_fit(counts.data(), G, N, design.data(), p, dm, o2, 1e-4, coef2.data(), mu_hat.data(), nthreads);
     const double* gamma_hat = coef2.data();   // first B columns
+    lap(CBS_ST_GLM);
     // ---- Monte-Carlo EB (ComBat_seq.R:141-170) ----
     std::vector<double> gamma_star(gamma_hat, gamma_hat + (size_t)G * B), phi_star_mat(phi_hat);
     if (in->shrink) {
@@ -231,6 +244,7 @@ int ref_combat_seq(const cbs_input* in, cbs_output* out, int nthreads, int mc_ta
         }
         if (!in->shrink_disp) phi_star_mat = phi_hat;     // ComBat_seq.R:162-165
     }
+    lap(CBS_ST_MC);
     // ---- batch-free distribution + match_quantiles (ComBat_seq.R:173-193) ----
     std::vector<double> phi_star(G), adjust((size_t)G * N);
     for (long i = 0; i < G; ++i) { double s = 0; for (int b = 0; b < B; ++b) s += phi_star_mat[i + (size_t)b * G]; phi_star[i] = s / B; }
@@ -248,6 +262,7 @@ int ref_combat_seq(const cbs_input* in, cbs_output* out, int nthreads, int mc_ta
         match_quantiles_ref(G, nb, yb.data(), omu.data(), phi_hat.data() + (size_t)b * G, nmu.data(), phi_star.data(), res.data(), nthreads);
         for (int t = 0; t < nb; ++t) { const int s = batches_ind[b][t]; for (long i = 0; i < G; ++i) adjust[i + (size_t)s * G] = res[i + (size_t)t * G]; }
     }
+    lap(CBS_ST_MATCH_QUANTILES);
     // ---- outputs (ComBat_seq.R:198-203) ----
     if (out->adjusted) {
         std::copy(countsOri.begin(), countsOri.end(), out->adjusted);
@@ -264,6 +279,9 @@ int ref_combat_seq(const cbs_input* in, cbs_output* out, int nthreads, int mc_ta
     scatter(out->phi_star, phi_star_mat.data(), B);
     scatter(out->mu_hat, mu_hat.data(), N);
     out->row_begin = 0; out->row_end = G0;
+    lap(CBS_ST_D2H);
+    stage[CBS_ST_TOTAL] = clk() - t_begin;
+    if (out->stage_ms) std::copy(stage, stage + CBS_N_STAGES, out->stage_ms);
     return CBS_OK;
 }
 
