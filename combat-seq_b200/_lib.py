@@ -25,7 +25,8 @@ STAGES = ("h2d", "prep", "common_disp", "tagwise_disp", "glm", "mc", "match_quan
 EXPORTS = ("cbs_version", "cbs_device_count", "cbs_last_error", "cbs_shutdown", "cbs_kernel_launches",
            "cbs_comm_unique_id", "cbs_comm_create", "cbs_comm_destroy", "cbs_combat_seq", "cbs_nb_logpmf",
            "cbs_nb_cdf", "cbs_nb_quantile", "cbs_glm_fit", "cbs_apl", "cbs_common_disp", "cbs_tagwise_disp",
-           "cbs_mc_int", "cbs_match_quantiles", "cbs_profile_enable", "cbs_profile_dump", "cbs_fp64_peak")
+           "cbs_mc_int", "cbs_match_quantiles", "cbs_profile_enable", "cbs_profile_dump", "cbs_fp64_peak",
+           "cbs_fp64_mma_peak", "cbs_set_tuning", "cbs_get_diag")
 
 
 class CbsInput(C.Structure):
@@ -101,6 +102,22 @@ def profile_dump():
 def fp64_peak_tflops():
     v = C.c_double(0)
     check(lib().cbs_fp64_peak(C.byref(v)))
+    return v.value
+
+
+def fp64_mma_peak_tflops():
+    v = C.c_double(0)
+    check(lib().cbs_fp64_mma_peak(C.byref(v)))
+    return v.value
+
+
+def set_tuning(key, value):
+    check(lib().cbs_set_tuning(key.encode(), C.c_double(value)))
+
+
+def get_diag(key):
+    v = C.c_double(0)
+    check(lib().cbs_get_diag(key.encode(), C.byref(v)))
     return v.value
 
 

@@ -7,6 +7,7 @@
 #include "host_design.hpp"
 #include "kernels.cuh"
 #include "mc.cuh"
+#include "mc_gemm.cuh"
 #include <dlfcn.h>
 #include <chrono>
 #include <mutex>
@@ -19,6 +20,13 @@ std::atomic<uint64_t> g_launches{0};
 static std::mutex g_mutex;          // one call at a time per process (the R caller is single-threaded anyway)
 static DevCache g_dev;
 static PinCache g_pin;
+
+// ---- tuning knobs (cbs_set_tuning) ----------------------------------------------------------------------------
+static int g_mc_algo = 0;            // 0 = auto (tensor-core contraction when gene.subset.n is NULL), 1 = direct, 2 = contraction
+static double g_mc_tail_tol = 1e-8;  // largest accepted Chebyshev tail estimate (log-likelihood units)
+static double g_last_mc_tail = 0;    // diagnostics: largest tail estimate of the last Monte-Carlo stage
+static int g_last_mc_kc = 0;         // diagnostics: Chebyshev terms used by the last contraction launch
+
 
 static double now_ms() {
     using namespace std::chrono;

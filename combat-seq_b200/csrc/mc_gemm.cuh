@@ -1,0 +1,373 @@
+// mc_gemm.cuh — Monte-Carlo empirical-Bayes integration as one FP64 tensor-core contraction with a fused
+// weighted-sum epilogue (the "flash-attention with an NB score" form of monte_carlo_int_NB).
+//
+// Replaces monte_carlo_int_NB (/root/reference/helper_seq.R:8-42) for gene.subset.n = NULL.  For target gene i and
+// source gene j of one batch (n samples, r_j = 1/phi_j):
+//
+//   log LH_ij = sum_s log dnbinom(x_is; mu_js, r_j)                                              helper_seq.R:28
+//             = sum_s x_is * A_js                      A_js = log(mu_js / (r_j + mu_js))          (bilinear)
+//             + sum_s [lgamma(x_is + r_j) - lgamma(x_is + 1)]                                     (not separable)
+//             + c_j                                    c_j  = r_j sum_s log(r_j/(r_j+mu_js)) - n lgamma(r_j)
+//
+// The only non-separable term depends on j through the scalar r_j alone, so for every target i the function
+//   F_i(r) = sum_{s : x_is >= c} [lgamma(x_is + r) - lgamma(x_is + 1)]
+// is a smooth function of one variable.  In u = log(r + c) its singularities sit at Im u = +-pi whatever x >= c
+// is, so a Chebyshev series in u over the batch's range of r converges geometrically (about 24-30 terms for
+// 1e-13 over a 4096-fold range of r): F_i(r_j) = sum_k C_ik T_k(t_j).  Counts below the shift c are handled
+// exactly with a one-hot table, lgamma(v + r_j) - lgamma(v + 1) for v = 0..c-1 times the number of samples of
+// gene i that equal v.  All of it is one inner product of length KT = n + Kc + c + 1:
+//
+//   P_i = [ x_i1 .. x_in | C_i0 .. C_i,Kc-1 | #{x_is = 0} .. #{x_is = c-1} | 1   ]
+//   Q_j = [ A_j1 .. A_jn | T_0(t_j) ..      | lgamma(v + r_j) - lgamma(v+1) | c_j ]          log LH_ij = P_i . Q_j
+//
+// k_mc_gemm evaluates P Q^T tile by tile on the FP64 tensor pipe (mma.sync m8n8k4 f64 -> DMMA.8x8x4; tcgen05 has
+// no FP64 path), streams the tiles into shared memory with 1-D TMA bulk copies (cp.async.bulk + mbarrier), and
+// folds the weights w = exp(log LH) into running sums (sum w, sum w gamma_j, sum w phi_j) in registers, so the
+// G x G likelihood matrix never exists.  Per (i, j) pair that is 2*KT flop instead of n lgamma evaluations.
+// Truncation error of the series is monitored (tail coefficients) and reported; see DESIGN.md for the tolerance.
+#pragma once
+#include <cuda_runtime.h>
+#include <cstdint>
+#include <cmath>
+#include "mc.cuh"
+
+namespace cbs {
+
+constexpr int MCG_TILE = 128;        // CTA tile: 128 targets x 128 sources
+constexpr int MCG_KC = 8;            // k-chunk (doubles) per pipeline stage
+constexpr int MCG_STAGES = 4;
+constexpr int MCG_MAX_KC = 64;       // max Chebyshev terms
+constexpr int MCG_SHIFT = 4;         // c: counts below c use the one-hot table
+constexpr int MCG_THREADS = 256;
+
+struct McgShape {
+    int n;          // samples in the batch
+    int Kc;         // Chebyshev terms
+    int KT;         // n + Kc + MCG_SHIFT + 1
+    int KTP;        // KT rounded up to a multiple of MCG_KC
+    long rows;      // matrix rows, G rounded up to a multiple of MCG_TILE
+    double ulo, uhi;   // range of u = log(r + c)
+};
+
+// Storage of P and Q: chunk-major, [kc][row][8] doubles with an XOR swizzle of the in-chunk column so that the
+// m8n8k4 fragment loads (8 rows x 4 columns per warp) are shared-memory bank-conflict free at a dense row stride
+// of 8 doubles, and so that one (tile, chunk) block of 128 rows is 8 KB contiguous in global memory = one bulk copy.
+__host__ __device__ __forceinline__ size_t mcg_index(long rows, long row, int k) {
+    const int kc = k >> 3, kk = (k & 7) ^ ((int)((row >> 1) & 1) << 2);
+    return ((size_t)kc * rows + row) * 8 + kk;
+}
+
+// lgamma(x + r) - lgamma(x + 1) for integer-valued x >= 0, r > 0, without cancellation for large x
+__device__ __forceinline__ double lgamma_diff(double x, double r) {
+    if (x < 15.0) return lgamma(x + r) - lgamma(x + 1.0);
+    const double z1 = x + r, z2 = x + 1.0, d = r - 1.0;
+    const double i1 = 1.0 / z1, i2 = 1.0 / z2, q1 = i1 * i1, q2 = i2 * i2;
+    const double s1 = i1 * (0.083333333333333333 + q1 * (-0.0027777777777777778 + q1 * (0.00079365079365079365 +
+                      q1 * (-0.00059523809523809524 + q1 * 0.00084175084175084175))));
+    const double s2 = i2 * (0.083333333333333333 + q2 * (-0.0027777777777777778 + q2 * (0.00079365079365079365 +
+                      q2 * (-0.00059523809523809524 + q2 * 0.00084175084175084175))));
+    return (x + 0.5) * log1p(d / z2) + d * (log(z1) - 1.0) + (s1 - s2);
+}
+
+// ---- range of r = 1/phi over the genes, per batch: out[2b] = min phi, out[2b+1] = max phi ----------------
+__global__ void __launch_bounds__(256)
+k_mcg_phi_range(const double* __restrict__ phi, long G, double* __restrict__ out) {
+    const int b = blockIdx.x;
+    double lo = INFINITY, hi = -INFINITY;
+    for (long g = threadIdx.x; g < G; g += blockDim.x) {
+        const double v = phi[g + (long)b * G];
+        if (v == v) { lo = fmin(lo, v); hi = fmax(hi, v); }
+    }
+    __shared__ double slo[256], shi[256];
+    slo[threadIdx.x] = lo; shi[threadIdx.x] = hi;
+    __syncthreads();
+    for (int o = 128; o > 0; o >>= 1) {
+        if ((int)threadIdx.x < o) { slo[threadIdx.x] = fmin(slo[threadIdx.x], slo[threadIdx.x + o]); shi[threadIdx.x] = fmax(shi[threadIdx.x], shi[threadIdx.x + o]); }
+        __syncthreads();
+    }
+    if (threadIdx.x == 0) { out[2 * b] = slo[0]; out[2 * b + 1] = shi[0]; }
+}
+
+// ---- source side: row j of Q -------------------------------------------------------------------------------
+// cols[t] = global column of the batch's t-th sample; phi, gamma = this batch's columns of phi_hat / gamma_hat.
+// Rows j >= G are padding: zeros with c_j = MC_LOG_ZERO, so their weight is exactly 0.
+__global__ void __launch_bounds__(128)
+k_mcg_prep_src(const double* __restrict__ mu_hat, long G, const int* __restrict__ cols, const double* __restrict__ phi,
+               McgShape sh, double* __restrict__ Q) {
+    const long j = (long)blockIdx.x * blockDim.x + threadIdx.x;
+    if (j >= sh.rows) return;
+    const int n = sh.n, Kc = sh.Kc;
+    if (j >= G) {
+        for (int k = 0; k < sh.KTP; ++k) Q[mcg_index(sh.rows, j, k)] = (k == sh.KT - 1) ? MC_LOG_ZERO : 0.0;
+        return;
+    }
+    const double r = 1.0 / phi[j];
+    double c = 0;
+    for (int t = 0; t < n; ++t) {
+        const double mu = mu_hat[j + (long)cols[t] * G];
+        double a, l;
+        if (mu == 0) { a = MC_LOG_ZERO; l = 0; }
+        else {
+            a = (mu < r) ? log(mu / (r + mu)) : log1p(-r / (r + mu));
+            l = (r < mu) ? log(r / (r + mu)) : log1p(-mu / (r + mu));
+        }
+        Q[mcg_index(sh.rows, j, t)] = a;
+        c += r * l;
+    }
+    const double u = log(r + (double)MCG_SHIFT);
+    double tt = (sh.uhi > sh.ulo) ? (2.0 * u - (sh.ulo + sh.uhi)) / (sh.uhi - sh.ulo) : 0.0;
+    tt = fmin(1.0, fmax(-1.0, tt));
+    double t0 = 1.0, t1 = tt;
+    for (int k = 0; k < Kc; ++k) {
+        Q[mcg_index(sh.rows, j, n + k)] = t0;
+        const double t2 = 2.0 * tt * t1 - t0;
+        t0 = t1; t1 = t2;
+    }
+    for (int v = 0; v < MCG_SHIFT; ++v) Q[mcg_index(sh.rows, j, n + Kc + v)] = lgamma(v + r) - lgamma(v + 1.0);
+    Q[mcg_index(sh.rows, j, sh.KT - 1)] = c - n * lgamma(r);
+    for (int k = sh.KT; k < sh.KTP; ++k) Q[mcg_index(sh.rows, j, k)] = 0.0;
+}
+
+// ---- target side, step 1: F_i at the Chebyshev nodes.  grid (ceil(G/128), Kc); Fnode is [m*G + i] ----------
+__global__ void __launch_bounds__(128)
+k_mcg_prep_nodes(const int32_t* __restrict__ cnt, long G, const int* __restrict__ cols, McgShape sh,
+                 double* __restrict__ Fnode) {
+    const long i = (long)blockIdx.x * blockDim.x + threadIdx.x;
+    const int m = blockIdx.y;
+    if (i >= G) return;
+    const double tn = cospi((m + 0.5) / sh.Kc);
+    const double r = exp(0.5 * (sh.ulo + sh.uhi) + 0.5 * (sh.uhi - sh.ulo) * tn) - (double)MCG_SHIFT;
+    double f = 0;
+    for (int t = 0; t < sh.n; ++t) {
+        const int x = cnt[i + (long)cols[t] * G];
+        if (x >= MCG_SHIFT) f += lgamma_diff((double)x, r);
+    }
+    Fnode[(long)m * G + i] = f;
+}
+
+// ---- target side, step 2: row i of P (counts, Chebyshev coefficients by DCT, one-hot counts, 1) ------------
+// dct is the Kc x Kc table dct[k*Kc + m] = (k ? 2 : 1)/Kc * cos(pi k (m + 1/2)/Kc).  tail_bits: atomicMax of the
+// bit pattern of |C_{Kc-1}| + |C_{Kc-2}| (non-negative doubles order like their bit patterns).
+__global__ void __launch_bounds__(128)
+k_mcg_prep_tgt(const int32_t* __restrict__ cnt, long G, const int* __restrict__ cols, McgShape sh,
+               const double* __restrict__ Fnode, const double* __restrict__ dct, double* __restrict__ P,
+               unsigned long long* __restrict__ tail_bits) {
+    const long i = (long)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= sh.rows) return;
+    const int n = sh.n, Kc = sh.Kc;
+    if (i >= G) {
+        for (int k = 0; k < sh.KTP; ++k) P[mcg_index(sh.rows, i, k)] = 0.0;
+        return;
+    }
+    int hot[MCG_SHIFT];
+#pragma unroll
+    for (int v = 0; v < MCG_SHIFT; ++v) hot[v] = 0;
+    for (int t = 0; t < n; ++t) {
+        const int x = cnt[i + (long)cols[t] * G];
+        P[mcg_index(sh.rows, i, t)] = (double)x;
+#pragma unroll
+        for (int v = 0; v < MCG_SHIFT; ++v) hot[v] += (x == v);
+    }
+    double f[MCG_MAX_KC];
+    for (int m = 0; m < Kc; ++m) f[m] = Fnode[(long)m * G + i];
+    double tail = 0;
+    for (int k = 0; k < Kc; ++k) {
+        double c = 0;
+        for (int m = 0; m < Kc; ++m) c += dct[k * Kc + m] * f[m];
+        P[mcg_index(sh.rows, i, n + k)] = c;
+        if (Kc >= 4 && k >= Kc - 2) tail += fabs(c);
+    }
+#pragma unroll
+    for (int v = 0; v < MCG_SHIFT; ++v) P[mcg_index(sh.rows, i, n + Kc + v)] = (double)hot[v];
+    P[mcg_index(sh.rows, i, sh.KT - 1)] = 1.0;
+    for (int k = sh.KT; k < sh.KTP; ++k) P[mcg_index(sh.rows, i, k)] = 0.0;
+    if (tail > 0) atomicMax(tail_bits, (unsigned long long)__double_as_longlong(tail));
+}
+
+// ---- PTX helpers: mbarrier + 1-D TMA bulk copy (global -> shared) and the FP64 tensor-core MMA ---------------
+__device__ __forceinline__ uint32_t smem_u32(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
+__device__ __forceinline__ void mbar_init(uint64_t* bar, int count) {
+    asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(smem_u32(bar)), "r"(count));
+}
+__device__ __forceinline__ void mbar_expect_tx(uint64_t* bar, uint32_t bytes) {
+    asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(smem_u32(bar)), "r"(bytes) : "memory");
+}
+__device__ __forceinline__ void mbar_wait(uint64_t* bar, uint32_t parity) {
+    asm volatile(
+        "{\n\t.reg .pred p;\n\t"
+        "WAIT_%=:\n\t"
+        "mbarrier.try_wait.parity.shared::cta.b64 p, [%0], %1;\n\t"
+        "@p bra DONE_%=;\n\t"
+        "bra WAIT_%=;\n\t"
+        "DONE_%=:\n\t}" ::"r"(smem_u32(bar)), "r"(parity) : "memory");
+}
+__device__ __forceinline__ void bulk_g2s(void* dst, const void* src, uint32_t bytes, uint64_t* bar) {
+    asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];"
+                 ::"r"(smem_u32(dst)), "l"(src), "r"(bytes), "r"(smem_u32(bar)) : "memory");
+}
+__device__ __forceinline__ void dmma884(double& c0, double& c1, double a, double b) {
+    asm volatile("mma.sync.aligned.m8n8k4.row.col.f64.f64.f64.f64 {%0,%1}, {%2}, {%3}, {%0,%1};"
+                 : "+d"(c0), "+d"(c1) : "d"(a), "d"(b));
+}
+
+// weight accumulation with the cheap rejections first (the overwhelming majority of pairs has weight 0)
+template <int STABLE>
+__device__ __forceinline__ void mcg_add(McAcc& a, double L, double g, double p) {
+    if (!STABLE) {
+        if (L > -746.0) {                              // exp(L) == 0 below -745.14 (denormal minimum / 2)
+            const double w = exp(L);
+            a.sw += w; a.sg += w * g; a.sp += w * p;
+        }
+    } else {
+        if (L > a.m && L > -1e29) {                    // -1e30 stands for log(0): an impossible source, weight 0
+            const double sc = exp(a.m - L);            // exp(-inf) = 0 on the first hit
+            a.sw = a.sw * sc + 1.0; a.sg = a.sg * sc + g; a.sp = a.sp * sc + p; a.m = L;
+        } else if (L > a.m - 100.0) {                  // below that the relative contribution is < 4e-44
+            const double w = exp(L - a.m);
+            a.sw += w; a.sg += w * g; a.sp += w * p;
+        }
+    }
+}
+
+constexpr size_t MCG_SMEM_STAGE = 2 * MCG_TILE * MCG_KC * sizeof(double);                         // P + Q chunk
+constexpr size_t MCG_SMEM_GP = 2 * MCG_TILE * 2 * sizeof(double);                                 // 2 buffers
+constexpr size_t MCG_SMEM_BYTES = MCG_STAGES * MCG_SMEM_STAGE + MCG_SMEM_GP + MCG_STAGES * sizeof(uint64_t) + 64;
+
+// One CTA = one 128-target tile x one split of the source tiles.  8 warps as 4 (targets) x 2 (sources); warp tile
+// 32 x 64 = 4 x 8 DMMA tiles.  part[(split*rows + i)] receives the partial sums of target row i.
+template <int STABLE>
+__global__ void __launch_bounds__(MCG_THREADS, 1)
+k_mc_gemm(const double* __restrict__ P, const double* __restrict__ Q, const double2* __restrict__ gp, McgShape sh,
+          long tile0, McAcc* __restrict__ part) {
+    extern __shared__ __align__(128) unsigned char smem_raw[];
+    double* stage_base = reinterpret_cast<double*>(smem_raw);
+    double2* gp_s = reinterpret_cast<double2*>(smem_raw + MCG_STAGES * MCG_SMEM_STAGE);
+    uint64_t* bars = reinterpret_cast<uint64_t*>(smem_raw + MCG_STAGES * MCG_SMEM_STAGE + MCG_SMEM_GP);
+
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    const int wi = warp & 3, wj = warp >> 2;
+    const long itile = tile0 + blockIdx.x;
+    const long NJ = sh.rows / MCG_TILE;
+    const long jt0 = NJ * blockIdx.y / gridDim.y, jt1 = NJ * (blockIdx.y + 1) / gridDim.y;
+    const int NKC = sh.KTP / MCG_KC;
+    const long total = (jt1 - jt0) * NKC;
+
+    if (tid == 0) {
+        for (int s = 0; s < MCG_STAGES; ++s) mbar_init(&bars[s], 1);
+        asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+    }
+    __syncthreads();
+
+    auto issue = [&](long it) {
+        const long jl = it / NKC;
+        const int kc = (int)(it - jl * NKC), st = (int)(it % MCG_STAGES);
+        double* ps = stage_base + (size_t)st * (2 * MCG_TILE * MCG_KC);
+        double* qs = ps + MCG_TILE * MCG_KC;
+        const uint32_t chunk_bytes = MCG_TILE * MCG_KC * sizeof(double);
+        mbar_expect_tx(&bars[st], 2 * chunk_bytes + (kc == 0 ? (uint32_t)(MCG_TILE * sizeof(double2)) : 0u));
+        bulk_g2s(ps, P + ((size_t)kc * sh.rows + itile * MCG_TILE) * MCG_KC, chunk_bytes, &bars[st]);
+        bulk_g2s(qs, Q + ((size_t)kc * sh.rows + (jt0 + jl) * MCG_TILE) * MCG_KC, chunk_bytes, &bars[st]);
+        if (kc == 0) bulk_g2s(gp_s + (jl & 1) * MCG_TILE, gp + (jt0 + jl) * MCG_TILE, MCG_TILE * sizeof(double2), &bars[st]);
+    };
+    if (tid == 0)
+        for (long it = 0; it < MCG_STAGES && it < total; ++it) issue(it);
+
+    double acc[4][8][2];
+#pragma unroll
+    for (int mt = 0; mt < 4; ++mt)
+#pragma unroll
+        for (int nt = 0; nt < 8; ++nt) acc[mt][nt][0] = acc[mt][nt][1] = 0.0;
+    McAcc racc[4];
+#pragma unroll
+    for (int mt = 0; mt < 4; ++mt) { racc[mt].m = STABLE ? -INFINITY : 0.0; racc[mt].sw = racc[mt].sg = racc[mt].sp = 0.0; }
+
+    // fragment addressing: row = lane/4 within an 8-row MMA tile, column = lane%4 within a 4-wide k-step
+    const int frow = lane >> 2, fcol = lane & 3;
+    const int swz = ((frow >> 1) & 1) << 2;                 // tile bases are multiples of 8, so bit 1 of the row is frow's
+    const int a_off = (wi * 32 + frow) * MCG_KC, b_off = (wj * 64 + frow) * MCG_KC;
+
+    for (long it = 0; it < total; ++it) {
+        const int st = (int)(it % MCG_STAGES);
+        const uint32_t parity = (uint32_t)((it / MCG_STAGES) & 1);
+        mbar_wait(&bars[st], parity);
+        const double* ps = stage_base + (size_t)st * (2 * MCG_TILE * MCG_KC);
+        const double* qs = ps + MCG_TILE * MCG_KC;
+#pragma unroll
+        for (int ks = 0; ks < 2; ++ks) {
+            const int col = (ks * 4 + fcol) ^ swz;
+            double a[4], b[8];
+#pragma unroll
+            for (int mt = 0; mt < 4; ++mt) a[mt] = ps[a_off + mt * 8 * MCG_KC + col];
+#pragma unroll
+            for (int nt = 0; nt < 8; ++nt) b[nt] = qs[b_off + nt * 8 * MCG_KC + col];
+#pragma unroll
+            for (int mt = 0; mt < 4; ++mt)
+#pragma unroll
+                for (int nt = 0; nt < 8; ++nt) dmma884(acc[mt][nt][0], acc[mt][nt][1], a[mt], b[nt]);
+        }
+        __syncthreads();                                    // every warp is done with stage st
+        if (tid == 0 && it + MCG_STAGES < total) issue(it + MCG_STAGES);
+
+        const long jl = it / NKC;
+        if (it - jl * NKC == NKC - 1) {                     // last k-chunk of source tile jl: fold the weights in
+            const long jt = jt0 + jl;
+            const double2* g2 = gp_s + (jl & 1) * MCG_TILE;
+            const bool diag = (jt == itile);
+#pragma unroll
+            for (int nt = 0; nt < 8; ++nt) {
+#pragma unroll
+                for (int e = 0; e < 2; ++e) {
+                    const int jc = wj * 64 + nt * 8 + 2 * fcol + e;
+                    const double2 gpj = g2[jc];
+#pragma unroll
+                    for (int mt = 0; mt < 4; ++mt) {
+                        const double L = acc[mt][nt][e];
+                        acc[mt][nt][e] = 0.0;
+                        if (diag && jc == wi * 32 + mt * 8 + frow) continue;      // mu[-i,]   helper_seq.R:11-14
+                        mcg_add<STABLE>(racc[mt], L, gpj.x, gpj.y);
+                    }
+                }
+            }
+        }
+    }
+    // reduce over the 4 lanes that share a row, then over the two source-side warps
+    __syncthreads();
+    McAcc* red = reinterpret_cast<McAcc*>(smem_raw);        // [2][128], aliases the (now idle) stage buffers
+#pragma unroll
+    for (int mt = 0; mt < 4; ++mt) {
+        McAcc a = racc[mt];
+        for (int o = 1; o <= 2; o <<= 1) { const McAcc b = mc_shfl_xor(a, o); mc_merge(a, b, STABLE); }
+        if (fcol == 0) red[wj * MCG_TILE + wi * 32 + mt * 8 + frow] = a;
+    }
+    __syncthreads();
+    if (tid < MCG_TILE) {
+        McAcc a = red[tid];
+        mc_merge(a, red[MCG_TILE + tid], STABLE);
+        part[(size_t)blockIdx.y * sh.rows + itile * MCG_TILE + tid] = a;
+    }
+}
+
+// merge the source-split partials of targets [i0, i1) in split order and apply helper_seq.R:30-33
+__global__ void __launch_bounds__(128)
+k_mcg_finalize(const McAcc* __restrict__ part, long rows, int nsplit, long i0, long i1, int stable,
+               const double* __restrict__ gamma, const double* __restrict__ phi, double* __restrict__ gamma_star,
+               double* __restrict__ phi_star, unsigned long long* __restrict__ n_fallback) {
+    const long i = i0 + (long)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= i1) return;
+    McAcc a = part[i];
+    for (int s = 1; s < nsplit; ++s) mc_merge(a, part[(size_t)s * rows + i], stable);
+    if (a.sw == 0 || !(a.sw == a.sw)) {
+        gamma_star[i] = gamma[i]; phi_star[i] = phi[i];
+        atomicAdd(n_fallback, 1ull);
+    } else {
+        gamma_star[i] = a.sg / a.sw; phi_star[i] = a.sp / a.sw;
+    }
+}
+
+__global__ void k_mcg_pack_gp(const double* __restrict__ gamma, const double* __restrict__ phi, long G, long rows,
+                              double2* __restrict__ gp) {
+    const long j = (long)blockIdx.x * blockDim.x + threadIdx.x;
+    if (j < rows) gp[j] = (j < G) ? make_double2(gamma[j], phi[j]) : make_double2(0.0, 0.0);
+}
+
+}  // namespace cbs

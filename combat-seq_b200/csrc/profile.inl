@@ -54,9 +54,68 @@ __global__ void __launch_bounds__(256) k_fp64_peak(double* out, double a, double
     if (s == 123.456) out[0] = s;
 }
 
+// 16 independent DMMA.8x8x4 accumulator tiles per warp, 256 rounds
+__global__ void __launch_bounds__(256) k_fp64_mma_peak(double* out, double a, double b) {
+    double c[16][2];
+#pragma unroll
+    for (int t = 0; t < 16; ++t) { c[t][0] = threadIdx.x; c[t][1] = t; }
+#pragma unroll 1
+    for (int i = 0; i < 256; ++i) {
+#pragma unroll
+        for (int t = 0; t < 16; ++t) dmma884(c[t][0], c[t][1], a, b);
+    }
+    double s = 0;
+#pragma unroll
+    for (int t = 0; t < 16; ++t) s += c[t][0] + c[t][1];
+    if (s == 123.456) out[0] = s;
+}
+
 }  // namespace cbs
 
 extern "C" {
+
+int cbs_set_tuning(const char* key, double value) {
+    std::lock_guard<std::mutex> lock_(g_mutex);
+    if (!key) return fail(CBS_EINVAL, "null key");
+    if (!strcmp(key, "mc_algo")) { if (value < 0 || value > 2) return fail(CBS_EINVAL, "mc_algo must be 0, 1 or 2"); g_mc_algo = (int)value; return CBS_OK; }
+    if (!strcmp(key, "mc_tail_tol")) { g_mc_tail_tol = value; return CBS_OK; }
+    return fail(CBS_EINVAL, "unknown tuning key '%s'", key);
+}
+int cbs_get_diag(const char* key, double* value) {
+    std::lock_guard<std::mutex> lock_(g_mutex);
+    if (!key || !value) return fail(CBS_EINVAL, "null pointer");
+    if (!strcmp(key, "mc_tail")) { *value = g_last_mc_tail; return CBS_OK; }
+    if (!strcmp(key, "mc_terms")) { *value = g_last_mc_kc; return CBS_OK; }
+    if (!strcmp(key, "reset")) { g_last_mc_tail = 0; g_last_mc_kc = 0; *value = 0; return CBS_OK; }
+    return fail(CBS_EINVAL, "unknown diagnostics key '%s'", key);
+}
+
+int cbs_fp64_mma_peak(double* tflops) {
+    CBS_NEED_GPU();
+    if (!tflops) return fail(CBS_EINVAL, "null pointer");
+    CBS_ENTRY_BEGIN
+    int dev = 0, sms = 0;
+    CBS_CUDA(cudaGetDevice(&dev));
+    CBS_CUDA(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev));
+    double* d = g_dev.get<double>("fp64_peak", 8);
+    const int blocks = sms * 16;
+    cudaEvent_t e0, e1;
+    CBS_CUDA(cudaEventCreate(&e0)); CBS_CUDA(cudaEventCreate(&e1));
+    double best = 0;
+    for (int rep = 0; rep < 6; ++rep) {
+        CBS_CUDA(cudaEventRecord(e0, 0));
+        CBS_LAUNCH(k_fp64_mma_peak, dim3(blocks), 256, 0, 0, d, 0.999999, 1e-6);
+        CBS_CUDA(cudaEventRecord(e1, 0));
+        CBS_CUDA(cudaEventSynchronize(e1));
+        float ms = 0;
+        CBS_CUDA(cudaEventElapsedTime(&ms, e0, e1));
+        const double flop = 2.0 * 256 /*fma per mma*/ * 16 * 256 * 8 /*warps*/ * (double)blocks;
+        if (rep > 0) best = std::max(best, flop / (ms * 1e-3) / 1e12);
+    }
+    cudaEventDestroy(e0); cudaEventDestroy(e1);
+    *tflops = best;
+    CBS_ENTRY_END
+}
 
 int cbs_profile_enable(int on) {
     std::lock_guard<std::mutex> lock_(g_mutex);

@@ -141,8 +141,21 @@ static void run_glm_fit(const int32_t* cnt, long G, long g0, long g1, int N, con
                    d_goff, 1, d_coef, (double*)nullptr, d_alpha_w, n_alpha, d_alpha);
 }
 
-// monte_carlo_int_NB for one batch, targets [i0,i1); sources are all G genes.  d_cols: the batch's columns (n).
-static void run_mc_batch(const int32_t* cnt, long G, int n, const int* d_cols, long i0, long i1, const double* d_mu_hat,
+// number of Chebyshev terms for the range h = (uhi - ulo)/2 of u = log(r + c): the series of lgamma(x + e^u - c)
+// converges like rho^-K with rho fixed by the singularities at Im u = +-pi above the end points of the interval.
+static int mcg_terms(double h) {
+    if (h < 1e-3) return 8;
+    const double wr = 1.0, wi = M_PI / h;                     // w = 1 + i pi/h
+    const double ar = wr * wr - wi * wi - 1.0, ai = 2 * wr * wi;   // w^2 - 1
+    const double mod = std::sqrt(std::hypot(ar, ai)), arg = 0.5 * std::atan2(ai, ar);
+    const double rho = std::hypot(wr + mod * std::cos(arg), wi + mod * std::sin(arg));
+    int K = (int)std::ceil(std::log(1e14) / std::log(rho)) + 4;
+    K = (K + 1) & ~1;
+    return std::max(8, K);
+}
+
+// monte_carlo_int_NB for one batch by the direct pairwise kernel (every lgamma evaluated)
+static void run_mc_batch_direct(const int32_t* cnt, long G, int n, const int* d_cols, long i0, long i1, const double* d_mu_hat,
                          const double* d_gamma, const double* d_phi, int mc_mode, int subset_n, uint64_t seed,
                          double* d_gamma_star, double* d_phi_star, unsigned long long* d_nfb, cudaStream_t st) {
     double* A = g_dev.get<double>("mc_A", (size_t)n * G);
@@ -158,6 +171,90 @@ static void run_mc_batch(const int32_t* cnt, long G, int n, const int* d_cols, l
     const unsigned nblk = (unsigned)((i1 - i0 + MC_TI - 1) / MC_TI);
     CBS_LAUNCH(k_mc_direct, dim3(nblk), 256, smem, st, cnt, G, n, d_cols, i0, i1, A, cj, rj, lgr, di, d_gamma, d_phi,
                mc_mode == CBS_MC_STABLE ? 1 : 0, subset_n, seed, d_gamma_star, d_phi_star, d_nfb);
+}
+
+// monte_carlo_int_NB for one batch as P Q^T on the FP64 tensor pipe (mc_gemm.cuh).  Returns false (nothing
+// written) when the batch's dispersion range needs more Chebyshev terms than the kernel supports.
+// *tail_out receives the series' tail estimate (synchronises the stream).
+static bool run_mc_batch_gemm(const int32_t* cnt, long G, int n, const int* d_cols, long i0, long i1, const double* d_mu_hat,
+                              const double* d_gamma, const double* d_phi, int mc_mode, double* d_gamma_star,
+                              double* d_phi_star, unsigned long long* d_nfb, cudaStream_t st, double* tail_out) {
+    double* d_rng = g_dev.get<double>("mcg_range", 2);
+    CBS_LAUNCH(k_mcg_phi_range, dim3(1), 256, 0, st, d_phi, G, d_rng);
+    double rng[2];
+    CBS_CUDA(cudaMemcpyAsync(rng, d_rng, sizeof rng, cudaMemcpyDeviceToHost, st));
+    CBS_CUDA(cudaStreamSynchronize(st));
+    if (!(rng[0] > 0) || !std::isfinite(rng[1])) return false;
+    McgShape sh;
+    sh.n = n;
+    sh.ulo = std::log(1.0 / rng[1] + MCG_SHIFT);
+    sh.uhi = std::log(1.0 / rng[0] + MCG_SHIFT);
+    if (sh.uhi - sh.ulo < 0.02) { const double mid = 0.5 * (sh.ulo + sh.uhi); sh.ulo = mid - 0.01; sh.uhi = mid + 0.01; }
+    sh.Kc = mcg_terms(0.5 * (sh.uhi - sh.ulo));
+    if (sh.Kc > MCG_MAX_KC) return false;
+    sh.KT = n + sh.Kc + MCG_SHIFT + 1;
+    sh.KTP = std::max((sh.KT + MCG_KC - 1) / MCG_KC * MCG_KC, (MCG_STAGES + 1) * MCG_KC);
+    sh.rows = (G + MCG_TILE - 1) / MCG_TILE * MCG_TILE;
+    g_last_mc_kc = sh.Kc;
+    std::vector<double> dct((size_t)sh.Kc * sh.Kc);
+    for (int k = 0; k < sh.Kc; ++k)
+        for (int m = 0; m < sh.Kc; ++m) dct[(size_t)k * sh.Kc + m] = (k ? 2.0 : 1.0) / sh.Kc * std::cos(M_PI * k * (m + 0.5) / sh.Kc);
+    double* d_dct = upload(g_dev, "mcg_dct", dct.data(), dct.size(), st);
+    double* P = g_dev.get<double>("mcg_P", (size_t)sh.KTP * sh.rows);
+    double* Q = g_dev.get<double>("mcg_Q", (size_t)sh.KTP * sh.rows);
+    double* Fn = g_dev.get<double>("mcg_Fnode", (size_t)sh.Kc * G);
+    double2* gp = (double2*)g_dev.get<double>("mcg_gp", (size_t)2 * sh.rows);
+    unsigned long long* d_tail = g_dev.get<unsigned long long>("mcg_tail", 1);
+    CBS_CUDA(cudaMemsetAsync(d_tail, 0, sizeof(unsigned long long), st));
+    CBS_LAUNCH(k_mcg_prep_src, grid1(sh.rows, 128), 128, 0, st, d_mu_hat, G, d_cols, d_phi, sh, Q);
+    CBS_LAUNCH(k_mcg_prep_nodes, dim3((unsigned)((G + 127) / 128), (unsigned)sh.Kc), 128, 0, st, cnt, G, d_cols, sh, Fn);
+    CBS_LAUNCH(k_mcg_prep_tgt, grid1(sh.rows, 128), 128, 0, st, cnt, G, d_cols, sh, Fn, d_dct, P, d_tail);
+    CBS_LAUNCH(k_mcg_pack_gp, grid1(sh.rows, 256), 256, 0, st, d_gamma, d_phi, G, sh.rows, gp);
+    if (i1 > i0) {
+        const long tile0 = i0 / MCG_TILE, ntiles = (i1 - i0 + MCG_TILE - 1) / MCG_TILE, NJ = sh.rows / MCG_TILE;
+        int sms = 148;
+        { int dev = 0; cudaGetDevice(&dev); cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev); }
+        long nsplit = (8L * sms + ntiles - 1) / ntiles;
+        nsplit = std::max(1L, std::min(nsplit, std::min(32L, std::max(1L, NJ / 4))));
+        McAcc* part = (McAcc*)g_dev.get<double>("mcg_part", (size_t)nsplit * sh.rows * (sizeof(McAcc) / sizeof(double)));
+        static bool attr_set = false;
+        if (!attr_set) {
+            CBS_CUDA(cudaFuncSetAttribute(k_mc_gemm<0>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)MCG_SMEM_BYTES));
+            CBS_CUDA(cudaFuncSetAttribute(k_mc_gemm<1>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)MCG_SMEM_BYTES));
+            attr_set = true;
+        }
+        const dim3 grid((unsigned)ntiles, (unsigned)nsplit);
+        if (mc_mode == CBS_MC_STABLE)
+            CBS_LAUNCH(k_mc_gemm<1>, grid, MCG_THREADS, MCG_SMEM_BYTES, st, P, Q, gp, sh, tile0, part);
+        else
+            CBS_LAUNCH(k_mc_gemm<0>, grid, MCG_THREADS, MCG_SMEM_BYTES, st, P, Q, gp, sh, tile0, part);
+        CBS_LAUNCH(k_mcg_finalize, grid1(i1 - i0, 128), 128, 0, st, part, sh.rows, (int)nsplit, i0, i1,
+                   mc_mode == CBS_MC_STABLE ? 1 : 0, d_gamma, d_phi, d_gamma_star, d_phi_star, d_nfb);
+    }
+    unsigned long long tb = 0;
+    CBS_CUDA(cudaMemcpyAsync(&tb, d_tail, sizeof tb, cudaMemcpyDeviceToHost, st));
+    CBS_CUDA(cudaStreamSynchronize(st));
+    double tail; memcpy(&tail, &tb, sizeof tail);
+    *tail_out = tail;
+    return true;
+}
+
+// monte_carlo_int_NB for one batch, targets [i0,i1); sources are all G genes.  d_cols: the batch's columns (n).
+// d_nfb must be zero on entry.
+static void run_mc_batch(const int32_t* cnt, long G, int n, const int* d_cols, long i0, long i1, const double* d_mu_hat,
+                         const double* d_gamma, const double* d_phi, int mc_mode, int subset_n, uint64_t seed,
+                         double* d_gamma_star, double* d_phi_star, unsigned long long* d_nfb, cudaStream_t st) {
+    if (subset_n >= G - 1) subset_n = 0;
+    const bool want_gemm = subset_n <= 0 && g_mc_algo != 1 && G >= 2;
+    if (want_gemm) {
+        double tail = 0;
+        if (run_mc_batch_gemm(cnt, G, n, d_cols, i0, i1, d_mu_hat, d_gamma, d_phi, mc_mode, d_gamma_star, d_phi_star, d_nfb, st, &tail)) {
+            g_last_mc_tail = std::max(g_last_mc_tail, tail);
+            if (tail <= g_mc_tail_tol || g_mc_algo == 2) return;
+            CBS_CUDA(cudaMemsetAsync(d_nfb, 0, sizeof(unsigned long long), st));     // series not converged: redo exactly
+        }
+    }
+    run_mc_batch_direct(cnt, G, n, d_cols, i0, i1, d_mu_hat, d_gamma, d_phi, mc_mode, subset_n, seed, d_gamma_star, d_phi_star, d_nfb, st);
 }
 
 }  // namespace cbs

@@ -67,6 +67,18 @@ uint64_t    cbs_kernel_launches(void);        /* kernels launched by this librar
 int         cbs_profile_enable(int on);
 int         cbs_profile_dump(char* buf, size_t len);
 int         cbs_fp64_peak(double* tflops);
+int         cbs_fp64_mma_peak(double* tflops);   /* same for the FP64 tensor pipe (mma.sync m8n8k4 f64, DMMA) */
+
+/* ---- tuning knobs and diagnostics ---------------------------------------------------------------------------
+ * Defaults reproduce the reference; none of them changes what is computed beyond the stated tolerance.
+ *   "mc_algo"      0 = auto, 1 = direct pairwise kernel (every lgamma evaluated), 2 = FP64 tensor-core
+ *                  contraction with the Chebyshev expansion of the lgamma term
+ *   "mc_tail_tol"  largest accepted Chebyshev tail estimate in log-likelihood units (default 1e-8); a batch that
+ *                  exceeds it is redone with the direct kernel when mc_algo = 0
+ * cbs_get_diag keys: "mc_tail" (largest tail estimate since the last reset), "mc_terms" (Chebyshev terms of the
+ * last contraction launch); cbs_get_diag("reset", &x) clears them. */
+int         cbs_set_tuning(const char* key, double value);
+int         cbs_get_diag(const char* key, double* value);
 
 /* ---- multi-process gene sharding (one process per GPU, e.g. under torchrun) ------------------------
  * Rank 0 calls cbs_comm_unique_id() and ships the 128 bytes to the other ranks by any means
