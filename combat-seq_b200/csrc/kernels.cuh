@@ -171,13 +171,6 @@ __global__ void k_phi_star_mean(const double* __restrict__ phi_star_mat, long G,
     phi_star[g] = s / B;                                    // rowMeans  ComBat_seq.R:178
 }
 
-__device__ __forceinline__ double match_one(double x, double old_mu, double old_phi, double new_mu, double new_phi) {
-    if (x <= 1) return x;                                   // helper_seq.R:50-51
-    const double tmp_p = pnbinom_mu(x - 1, 1.0 / old_phi, old_mu);
-    if (fabs(tmp_p - 1) < 1e-4) return x;                   // helper_seq.R:54-56
-    return 1 + qnbinom_mu(tmp_p, 1.0 / new_phi, new_mu);    // helper_seq.R:58
-}
-
 // grid: (ceil(G/128), N).  out is G0-row column-major; row of kept gene i is keep_idx[i] (or i when keep_idx == nullptr)
 __global__ void __launch_bounds__(128)
 k_match_quantiles(const int32_t* __restrict__ cnt, long G, long g0, long g1, const double* __restrict__ mu_hat,
@@ -191,7 +184,7 @@ k_match_quantiles(const int32_t* __restrict__ cnt, long G, long g0, long g1, con
     const double x = (double)cnt[g + (long)s * G];
     const double old_mu = mu_hat[g + (long)s * G];
     const double new_mu = exp(log(old_mu) - gamma_star[g + (long)b * G]);     // ComBat_seq.R:176
-    const double v = match_one(x, old_mu, phi_hat[g + (long)b * G], new_mu, phi_star[g]);
+    const double v = match_one_fast(x, old_mu, phi_hat[g + (long)b * G], new_mu, phi_star[g]);
     out[(keep_idx ? (long)keep_idx[g] : g) + (long)s * G0] = v;
 }
 
@@ -204,7 +197,7 @@ k_match_quantiles_plain(const int32_t* __restrict__ cnt, long G, int n, const do
     const int s = blockIdx.y;
     if (g >= G) return;
     const long k = g + (long)s * G;
-    out[k] = match_one((double)cnt[k], old_mu[k], old_phi[g], new_mu[k], new_phi[g]);
+    out[k] = match_one_fast((double)cnt[k], old_mu[k], old_phi[g], new_mu[k], new_phi[g]);
 }
 
 // a14: output pre-fill with the original counts as doubles (rows of filtered genes pass through; ComBat_seq.R:202)

@@ -13,6 +13,8 @@
 #include <cfloat>
 #include <cmath>
 
+#define CBS_HD __host__ __device__ __forceinline__
+
 namespace cbs {
 
 #define CBS_LN_SQRT_2PI 0.918938533204672741780329736406
@@ -20,26 +22,35 @@ namespace cbs {
 #define CBS_2PI         6.283185307179586476925286766559
 
 // stirlerr(k/2), k = 0..30:  log(n!) - log(sqrt(2 pi n) (n/e)^n), generated with mpmath at 40 digits
-__device__ __constant__ double c_sferr_halves[31] = {
-    0.0,
-    0.1534264097200273452913839, 0.08106146679532725821967026, 0.0548141210519176538961387,
-    0.04134069595540929409382208, 0.03316287351993628748511051, 0.02767792568499833914878929,
-    0.02374616365629749597133028, 0.02079067210376509311152277, 0.01848845053267318523077936,
-    0.01664469118982119216319487, 0.01513497322191737887351384, 0.01387612882307074799874573,
-    0.01281046524292022692425066, 0.01189670994589177009505572, 0.01110455975820691732663076,
-    0.01041126526197209649747857, 0.009799416126158803298390373, 0.009255462182712732917728637,
-    0.008768700134139385462955047, 0.008330563433362871256469319, 0.007934114564314020547249562,
-    0.007573675487951840794972024, 0.007244554301320383179546197, 0.006942840107209529865664153,
-    0.006665247032707682442356181, 0.006408994188004207068439631, 0.006171712263039457647534605,
-    0.005951370112758847735624416, 0.005746216513010115682026102, 0.00555473355196280137103869};
+#define CBS_SFERR_HALVES_INIT { \
+    0.0, \
+    0.1534264097200273452913839, 0.08106146679532725821967026, 0.0548141210519176538961387, \
+    0.04134069595540929409382208, 0.03316287351993628748511051, 0.02767792568499833914878929, \
+    0.02374616365629749597133028, 0.02079067210376509311152277, 0.01848845053267318523077936, \
+    0.01664469118982119216319487, 0.01513497322191737887351384, 0.01387612882307074799874573, \
+    0.01281046524292022692425066, 0.01189670994589177009505572, 0.01110455975820691732663076, \
+    0.01041126526197209649747857, 0.009799416126158803298390373, 0.009255462182712732917728637, \
+    0.008768700134139385462955047, 0.008330563433362871256469319, 0.007934114564314020547249562, \
+    0.007573675487951840794972024, 0.007244554301320383179546197, 0.006942840107209529865664153, \
+    0.006665247032707682442356181, 0.006408994188004207068439631, 0.006171712263039457647534605, \
+    0.005951370112758847735624416, 0.005746216513010115682026102, 0.00555473355196280137103869}
+__device__ __constant__ double c_sferr_halves[31] = CBS_SFERR_HALVES_INIT;
+static const double h_sferr_halves[31] = CBS_SFERR_HALVES_INIT;   // host copy (tests/hostmath compiles this header for the CPU)
+CBS_HD double sferr_half(int k) {
+#ifdef __CUDA_ARCH__
+    return c_sferr_halves[k];
+#else
+    return h_sferr_halves[k];
+#endif
+}
 
 // Stirling-series remainder of log(n!)
-__device__ __forceinline__ double stirlerr(double n) {
+CBS_HD double stirlerr(double n) {
     const double S0 = 0.083333333333333333333, S1 = 0.00277777777777777777778, S2 = 0.00079365079365079365079365,
                  S3 = 0.000595238095238095238095238, S4 = 0.0008417508417508417508417508;
     if (n <= 15.0) {
         const double nn = n + n;
-        if (nn == (double)(int)nn) return c_sferr_halves[(int)nn];
+        if (nn == (double)(int)nn) return sferr_half((int)nn);
         return lgamma(n + 1.0) - (n + 0.5) * log(n) + n - CBS_LN_SQRT_2PI;
     }
     const double nn = n * n;
@@ -50,8 +61,8 @@ __device__ __forceinline__ double stirlerr(double n) {
 }
 
 // bd0(x, np) = x log(x/np) + np - x, without cancellation when x ~ np
-__device__ __forceinline__ double bd0(double x, double np) {
-    if (!isfinite(x) || !isfinite(np) || np == 0.0) return nan("");
+CBS_HD double bd0(double x, double np) {
+    if (!isfinite(x) || !isfinite(np) || np == 0.0) return NAN;
     if (fabs(x - np) < 0.1 * (x + np)) {
         double v = (x - np) / (x + np);
         double s = (x - np) * v;
@@ -70,7 +81,7 @@ __device__ __forceinline__ double bd0(double x, double np) {
 
 // binomial pmf kernel of Loader's algorithm, linear (log_p = false) or log scale
 template <bool LOG>
-__device__ __forceinline__ double dbinom_raw(double x, double n, double p, double q) {
+CBS_HD double dbinom_raw(double x, double n, double p, double q) {
     if (p == 0) return (x == 0) ? (LOG ? 0.0 : 1.0) : (LOG ? -INFINITY : 0.0);
     if (q == 0) return (x == n) ? (LOG ? 0.0 : 1.0) : (LOG ? -INFINITY : 0.0);
     double lc;
@@ -91,9 +102,9 @@ __device__ __forceinline__ double dbinom_raw(double x, double n, double p, doubl
 
 // dnbinom(x; mu, size) for integer-valued x >= 0 (helper_seq.R:28), linear or log scale
 template <bool LOG>
-__device__ __forceinline__ double dnbinom_mu(double x, double size, double mu) {
+CBS_HD double dnbinom_mu(double x, double size, double mu) {
     if (isnan(x) || isnan(size) || isnan(mu)) return x + size + mu;
-    if (mu < 0 || size < 0) return nan("");
+    if (mu < 0 || size < 0) return NAN;
     if (x < 0 || !isfinite(x)) return LOG ? -INFINITY : 0.0;
     if (x == 0 && size == 0) return LOG ? 0.0 : 1.0;
     if (!isfinite(size)) {  // Poisson limit
@@ -117,7 +128,7 @@ __device__ __forceinline__ double dnbinom_mu(double x, double size, double mu) {
 }
 
 // x^a y^b / B(a,b) in saddle-point form (valid for all a, b > 0)
-__device__ __forceinline__ double brcomp(double a, double b, double x, double y) {
+CBS_HD double brcomp(double a, double b, double x, double y) {
     if (x == 0 || y == 0) return 0.0;
     const double n = a + b;
     const double lc = stirlerr(n) - stirlerr(a) - stirlerr(b) - bd0(a, n * x) - bd0(b, n * y);
@@ -125,7 +136,7 @@ __device__ __forceinline__ double brcomp(double a, double b, double x, double y)
 }
 
 // TOMS 708 continued fraction for I_x(a,b), lambda = (a+b)y - b >= 0
-__device__ __forceinline__ double bfrac(double a, double b, double x, double y, double lambda, double eps) {
+CBS_HD double bfrac(double a, double b, double x, double y, double lambda, double eps) {
     const double brc = brcomp(a, b, x, y);
     if (brc == 0.) return 0.;
     const double c = lambda + 1., c0 = b / a, c1 = 1. / a + 1., yp1 = y + 1.;
@@ -151,8 +162,8 @@ __device__ __forceinline__ double bfrac(double a, double b, double x, double y, 
 }
 
 // regularised incomplete beta I_x(a,b) (w) and its complement (w1); y = 1 - x is passed separately
-__device__ __forceinline__ void bratio(double a, double b, double x, double y, double* w, double* w1) {
-    if (isnan(a) || isnan(b) || isnan(x) || isnan(y) || a < 0 || b < 0 || x < 0 || x > 1) { *w = *w1 = nan(""); return; }
+CBS_HD void bratio(double a, double b, double x, double y, double* w, double* w1) {
+    if (isnan(a) || isnan(b) || isnan(x) || isnan(y) || a < 0 || b < 0 || x < 0 || x > 1) { *w = *w1 = NAN; return; }
     if (x == 0) { *w = 0; *w1 = 1; return; }
     if (y == 0) { *w = 1; *w1 = 0; return; }
     if (a == 0) { *w = 1; *w1 = 0; return; }
@@ -169,9 +180,9 @@ __device__ __forceinline__ void bratio(double a, double b, double x, double y, d
 }
 
 // pnbinom(q; mu, size), lower tail (helper_seq.R:53)
-__device__ __forceinline__ double pnbinom_mu(double x, double size, double mu) {
+CBS_HD double pnbinom_mu(double x, double size, double mu) {
     if (isnan(x) || isnan(size) || isnan(mu)) return x + size + mu;
-    if (!isfinite(mu) || size < 0 || mu < 0) return nan("");
+    if (!isfinite(mu) || size < 0 || mu < 0) return NAN;
     if (size == 0) return (x >= 0) ? 1.0 : 0.0;
     if (x < 0) return 0.0;
     if (!isfinite(x)) return 1.0;
@@ -182,9 +193,9 @@ __device__ __forceinline__ double pnbinom_mu(double x, double size, double mu) {
 }
 
 // pnbinom(q; size, prob), lower tail
-__device__ __forceinline__ double pnbinom_prob(double x, double size, double prob) {
+CBS_HD double pnbinom_prob(double x, double size, double prob) {
     if (isnan(x) || isnan(size) || isnan(prob)) return x + size + prob;
-    if (!isfinite(size) || !isfinite(prob) || size < 0 || prob <= 0 || prob > 1) return nan("");
+    if (!isfinite(size) || !isfinite(prob) || size < 0 || prob <= 0 || prob > 1) return NAN;
     if (size == 0) return (x >= 0) ? 1.0 : 0.0;
     if (x < 0) return 0.0;
     if (!isfinite(x)) return 1.0;
@@ -195,7 +206,7 @@ __device__ __forceinline__ double pnbinom_prob(double x, double size, double pro
 }
 
 // standard normal quantile, AS 241 (PPND16)
-__device__ __forceinline__ double qnorm01(double p) {
+CBS_HD double qnorm01(double p) {
     if (isnan(p)) return p;
     if (p <= 0) return (p == 0) ? -INFINITY : nan("");
     if (p >= 1) return (p == 1) ? INFINITY : nan("");
@@ -234,7 +245,7 @@ __device__ __forceinline__ double qnorm01(double p) {
 }
 
 // discrete search on the incr-grid: returns y with F(y) >= p and F(y - incr) < p (or y == 0); *z = F(y)
-__device__ __forceinline__ double qnb_search(double y, double* z, double p, double n, double pr, double incr) {
+CBS_HD double qnb_search(double y, double* z, double p, double n, double pr, double incr) {
     if (*z >= p) {
         for (;;) {
             double newz;
@@ -251,12 +262,12 @@ __device__ __forceinline__ double qnb_search(double y, double* z, double p, doub
 }
 
 // qnbinom(p; size, prob): smallest integer y >= 0 with pnbinom(y) >= p*(1-64*DBL_EPSILON)
-__device__ __forceinline__ double qnbinom_prob(double p, double size, double prob) {
+CBS_HD double qnbinom_prob(double p, double size, double prob) {
     if (isnan(p) || isnan(size) || isnan(prob)) return p + size + prob;
     if (prob == 0 && size == 0) return 0;
-    if (prob <= 0 || prob > 1 || size < 0) return nan("");
+    if (prob <= 0 || prob > 1 || size < 0) return NAN;
     if (prob == 1 || size == 0) return 0;
-    if (p < 0 || p > 1) return nan("");
+    if (p < 0 || p > 1) return NAN;
     if (p == 0) return 0;
     if (p == 1) return INFINITY;
     const double Q = 1.0 / prob, P = (1.0 - prob) * Q, mu = size * P, sigma = sqrt(size * P * Q);
@@ -278,9 +289,139 @@ __device__ __forceinline__ double qnbinom_prob(double p, double size, double pro
 }
 
 // qnbinom(p; mu, size) (helper_seq.R:58)
-__device__ __forceinline__ double qnbinom_mu(double p, double size, double mu) {
-    if (!isfinite(size)) return nan("");
+CBS_HD double qnbinom_mu(double p, double size, double mu) {
+    if (!isfinite(size)) return NAN;
     return qnbinom_prob(p, size, size / (size + mu));
+}
+
+// ---- fast path used by match_quantiles -----------------------------------------------------------------------
+// Same mathematics as pnbinom/qnbinom above (TOMS 708 continued fraction, Cornish-Fisher start, smallest y with
+// F(y) >= p(1 - 64 eps)), reorganised for the GPU: (i) the continued fraction uses three reciprocals per term
+// instead of seven divisions; (ii) the pmf comes for free from the fraction's prefactor,
+// x^a y^b / B(a, k+1) = pmf(k) * y * (a + k); (iii) qnbinom's unit-step search, which costs one continued fraction
+// per step and up to hundreds of steps for skewed distributions, becomes a walk along the pmf recurrence
+// F(y+1) = F(y) + pmf(y+1), pmf(y+1) = pmf(y) (y + size)/(y + 1) q.  The walk's rounding error is bounded; whenever
+// the decision F(y) >= p is closer than that bound the result is re-derived with continued fractions only, so the
+// answer is the one the unit-step search gives.
+struct NbCdf { double F, pmf; };
+
+CBS_HD double bfrac_fast(double a, double b, double x, double y, double lambda) {
+    const double eps = 2 * DBL_EPSILON;
+    const double c = lambda + 1., c0 = b / a, inva = 1. / a, c1 = inva + 1., yp1 = y + 1.;
+    double n = 0., p = 1., s = a + 1., an = 0., bn = 1., anp1 = 1., bnp1 = c / c1, r = c1 / c;
+    do {
+        n += 1.;
+        const double t = n * inva, w = n * (b - n) * x, rs = 1. / s;
+        double e = a * rs;
+        const double alpha = p * (p + c0) * e * e * (w * x);
+        e = (t + 1.) / (c1 + t + t);
+        const double beta = n + w * rs + e * (c + n * yp1);
+        p = t + 1.;
+        s += 2.;
+        const double ta = alpha * an + beta * anp1, tb = alpha * bn + beta * bnp1;
+        const double inv = 1. / tb, r0 = r;
+        r = ta * inv;
+        if (fabs(r - r0) <= eps * r) break;
+        an = anp1 * inv; bn = bnp1 * inv; anp1 = r; bnp1 = 1.;
+    } while (n < 10000);
+    return r;
+}
+
+// F = P(X <= k), pmf = P(X = k) for X ~ NB(size, prob), q = 1 - prob, k a non-negative integer, 0 < prob < 1
+CBS_HD NbCdf nb_cdf_pmf(double k, double size, double prob, double q) {
+    NbCdf o;
+    const double a = size, b = k + 1.;
+    const double brc = brcomp(a, b, prob, q);
+    o.pmf = brc / (q * (a + k));
+    const double lambda = (a > b) ? (a + b) * q - b : a - (a + b) * prob;
+    if (brc == 0.) { o.F = (lambda >= 0) ? 0.0 : 1.0; return o; }      // prefactor underflow: far tail
+    if (lambda >= 0) o.F = brc * bfrac_fast(a, b, prob, q, lambda);
+    else o.F = 0.5 - brc * bfrac_fast(b, a, q, prob, -lambda) + 0.5;
+    return o;
+}
+
+// unit-step search with continued fractions only (qnbinom's do_search with incr = 1), from y with z = F(y)
+CBS_HD double nb_search_exact(double y, double z, double p, double size, double prob, double q) {
+    if (z >= p) {
+        for (;;) {
+            if (y == 0) return y;
+            if (nb_cdf_pmf(y - 1, size, prob, q).F < p) return y;
+            y -= 1;
+        }
+    }
+    for (;;) {
+        y += 1;
+        if (nb_cdf_pmf(y, size, prob, q).F >= p) return y;
+    }
+}
+
+// qnbinom(p; size, prob) for 0 < p < 1, 0 < prob < 1, size > 0 (the callers handle the boundaries)
+CBS_HD double nb_quantile_fast(double p, double size, double prob) {
+    const double q = 0.5 - prob + 0.5;
+    const double Q = 1.0 / prob, P = (1.0 - prob) * Q, m = size * P, sigma = sqrt(size * P * Q);
+    const double gam = (Q + P) / sigma;
+    const double zn = qnorm01(p);
+    double y = nearbyint(m + sigma * (zn + gam * (zn * zn - 1) / 6));
+    if (!(y >= 0)) y = 0;
+    const double pp = p * (1 - 64 * DBL_EPSILON);
+    NbCdf c = nb_cdf_pmf(y, size, prob, q);
+    // up to two Newton refinements on the continuous extension when the start is far off (pmf ~ density)
+    for (int it = 0; it < 2; ++it) {
+        if (!(c.pmf > 0)) break;
+        double d = (pp - c.F) / c.pmf;
+        if (fabs(d) < 12.0) break;
+        d = fmin(fmax(d, -0.5 * y), fmax(y, 16.0));
+        const double y2 = fmax(0.0, nearbyint(y + d));
+        if (y2 == y) break;
+        y = y2;
+        c = nb_cdf_pmf(y, size, prob, q);
+    }
+    const double F0 = c.F;
+    double F = c.F, f = c.pmf, Fm, steps = 0;
+    bool bad = !(f > 0) || !isfinite(f);
+    if (!bad) {
+        if (F >= pp) {                                         // walk left to the smallest y with F(y) >= pp
+            for (;;) {
+                Fm = F - f;                                    // F(y - 1)
+                if (y == 0 || Fm < pp) break;
+                f = f * y / ((y - 1 + size) * q);
+                y -= 1; F = Fm; steps += 1;
+                if (!(f > 0)) { bad = true; break; }
+            }
+        } else {                                               // walk right until F(y) >= pp
+            for (;;) {
+                f = f * ((y + size) / (y + 1)) * q;
+                y += 1; F += f; steps += 1;
+                if (F >= pp) break;
+                if (!(f > 1e-300) || steps > 2e6) { bad = true; break; }
+            }
+            Fm = F - f;
+        }
+    }
+    if (!bad) {
+        const double tol = (steps + 16.0) * 4e-15 * fmax(F0, fmax(F, pp));
+        const bool tie = fabs(F - pp) <= tol || (y > 0 && fabs(Fm - pp) <= tol);
+        if (!tie) return y;
+    }
+    return nb_search_exact(y, nb_cdf_pmf(y, size, prob, q).F, pp, size, prob, q);
+}
+
+// match_quantiles for one element (helper_seq.R:46-64)
+CBS_HD double match_one_fast(double x, double old_mu, double old_phi, double new_mu, double new_phi) {
+    if (x <= 1) return x;                                      // helper_seq.R:50-51
+    const double so = 1.0 / old_phi, sn = 1.0 / new_phi;
+    if (!(old_mu > 0) || !(new_mu > 0) || !isfinite(old_mu) || !isfinite(new_mu) || !(so > 0) || !(sn > 0) ||
+        !isfinite(so) || !isfinite(sn)) {                      // degenerate parameters: the general routines
+        const double tmp_p = pnbinom_mu(x - 1, so, old_mu);
+        if (fabs(tmp_p - 1) < 1e-4) return x;
+        return 1 + qnbinom_mu(tmp_p, sn, new_mu);
+    }
+    const double tmp_p = nb_cdf_pmf(x - 1, so, so / (so + old_mu), old_mu / (so + old_mu)).F;     // helper_seq.R:53
+    if (fabs(tmp_p - 1) < 1e-4) return x;                      // helper_seq.R:54-56
+    if (!(tmp_p > 0)) return 1 + qnbinom_mu(tmp_p, sn, new_mu);
+    const double prob = sn / (sn + new_mu);
+    if (!(prob > 0) || !(prob < 1)) return 1 + qnbinom_mu(tmp_p, sn, new_mu);
+    return 1 + nb_quantile_fast(tmp_p, sn, prob);              // helper_seq.R:58
 }
 
 }  // namespace cbs

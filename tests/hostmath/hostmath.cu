@@ -1,0 +1,30 @@
+// TEST INFRASTRUCTURE: compiles the product's device math header (combat-seq_b200/csrc/nbmath.cuh) for the HOST so that
+// the not-gpu test tier can check the exact routines the kernels run (continued fraction, pmf walk, quantile search)
+// against the oracle and the golden vectors without a GPU.  Nothing in the product links this.
+#include "../../combat-seq_b200/csrc/nbmath.cuh"
+#include <cstdint>
+using namespace cbs;
+extern "C" {
+void hm_nb_logpmf(int64_t n, const double* x, const double* size, const double* mu, double* out) { for (int64_t i = 0; i < n; ++i) out[i] = dnbinom_mu<true>(x[i], size[i], mu[i]); }
+void hm_nb_cdf(int64_t n, const double* x, const double* size, const double* mu, double* out) { for (int64_t i = 0; i < n; ++i) out[i] = pnbinom_mu(x[i], size[i], mu[i]); }
+void hm_nb_cdf_fast(int64_t n, const double* x, const double* size, const double* mu, double* out) {
+    for (int64_t i = 0; i < n; ++i) out[i] = nb_cdf_pmf(x[i], size[i], size[i] / (size[i] + mu[i]), mu[i] / (size[i] + mu[i])).F;
+}
+void hm_nb_pmf_fast(int64_t n, const double* x, const double* size, const double* mu, double* out) {
+    for (int64_t i = 0; i < n; ++i) out[i] = nb_cdf_pmf(x[i], size[i], size[i] / (size[i] + mu[i]), mu[i] / (size[i] + mu[i])).pmf;
+}
+void hm_nb_quantile(int64_t n, const double* p, const double* size, const double* mu, double* out) { for (int64_t i = 0; i < n; ++i) out[i] = qnbinom_mu(p[i], size[i], mu[i]); }
+void hm_nb_quantile_fast(int64_t n, const double* p, const double* size, const double* mu, double* out) {
+    for (int64_t i = 0; i < n; ++i) out[i] = nb_quantile_fast(p[i], size[i], size[i] / (size[i] + mu[i]));
+}
+void hm_match_quantiles(int64_t n, const double* x, const double* omu, const double* ophi, const double* nmu, const double* nphi, double* out, int fast) {
+    for (int64_t i = 0; i < n; ++i) {
+        if (fast) out[i] = match_one_fast(x[i], omu[i], ophi[i], nmu[i], nphi[i]);
+        else {
+            if (x[i] <= 1) { out[i] = x[i]; continue; }
+            const double tp = pnbinom_mu(x[i] - 1, 1.0 / ophi[i], omu[i]);
+            out[i] = (fabs(tp - 1) < 1e-4) ? x[i] : 1 + qnbinom_mu(tp, 1.0 / nphi[i], nmu[i]);
+        }
+    }
+}
+}
