@@ -35,7 +35,7 @@ namespace cbs {
 
 constexpr int MCG_TILE = 128;        // CTA tile: 128 targets x 128 sources
 constexpr int MCG_KC = 8;            // k-chunk (doubles) per pipeline stage
-constexpr int MCG_STAGES = 4;
+constexpr int MCG_STAGES = 6;
 constexpr int MCG_MAX_KC = 64;       // max Chebyshev terms
 constexpr int MCG_SHIFT = 4;         // c: counts below c use the one-hot table
 constexpr int MCG_THREADS = 256;
@@ -210,11 +210,18 @@ __device__ __forceinline__ void dmma884(double& c0, double& c1, double a, double
                  : "+d"(c0), "+d"(c1) : "d"(a), "d"(b));
 }
 
-// weight accumulation with the cheap rejections first (the overwhelming majority of pairs has weight 0)
+// Pruning.  A source whose log-likelihood is more than MCG_PRUNE below the best one seen so far for that target
+// carries a weight below e^-40 = 4e-18 of the largest weight; all G of them together change the weighted means by
+// less than 3e-13 relative, so they are dropped before exp() is ever called (and they can never turn an all-zero
+// row, the helper_seq.R:30-31 fallback, into a non-zero one: what is dropped is smaller than a weight already seen).
+// In reference mode a.m is only this running maximum; the weights themselves stay exp(L), unshifted, so that they
+// underflow exactly where R's prod(dnbinom) does.
+constexpr double MCG_PRUNE = 40.0;
 template <int STABLE>
 __device__ __forceinline__ void mcg_add(McAcc& a, double L, double g, double p) {
     if (!STABLE) {
-        if (L > -746.0) {                              // exp(L) == 0 below -745.14 (denormal minimum / 2)
+        if (L > a.m) a.m = L;
+        if (L > -746.0 && L >= a.m - MCG_PRUNE) {      // exp(L) == 0 below -745.14 (denormal minimum / 2)
             const double w = exp(L);
             a.sw += w; a.sg += w * g; a.sp += w * p;
         }
@@ -222,30 +229,49 @@ __device__ __forceinline__ void mcg_add(McAcc& a, double L, double g, double p) 
         if (L > a.m && L > -1e29) {                    // -1e30 stands for log(0): an impossible source, weight 0
             const double sc = exp(a.m - L);            // exp(-inf) = 0 on the first hit
             a.sw = a.sw * sc + 1.0; a.sg = a.sg * sc + g; a.sp = a.sp * sc + p; a.m = L;
-        } else if (L > a.m - 100.0) {                  // below that the relative contribution is < 4e-44
+        } else if (L > a.m - MCG_PRUNE) {
             const double w = exp(L - a.m);
             a.sw += w; a.sg += w * g; a.sp += w * p;
         }
     }
 }
 
+__device__ __forceinline__ void mbar_arrive(uint64_t* bar) {
+    asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(smem_u32(bar)) : "memory");
+}
+
+// non-blocking probe of a phase
+__device__ __forceinline__ bool mbar_test(uint64_t* bar, uint32_t parity) {
+    uint32_t ok;
+    asm volatile("{\n\t.reg .pred p;\n\tmbarrier.test_wait.parity.shared::cta.b64 p, [%1], %2;\n\tselp.u32 %0, 1, 0, p;\n\t}"
+                 : "=r"(ok) : "r"(smem_u32(bar)), "r"(parity) : "memory");
+    return ok != 0;
+}
+
+constexpr int MCG_CONSUMER_WARPS = 8;
+constexpr int MCG_BLOCK = MCG_THREADS;
 constexpr size_t MCG_SMEM_STAGE = 2 * MCG_TILE * MCG_KC * sizeof(double);                         // P + Q chunk
 constexpr size_t MCG_SMEM_GP = 2 * MCG_TILE * 2 * sizeof(double);                                 // 2 buffers
-constexpr size_t MCG_SMEM_BYTES = MCG_STAGES * MCG_SMEM_STAGE + MCG_SMEM_GP + MCG_STAGES * sizeof(uint64_t) + 64;
+constexpr size_t MCG_SMEM_BYTES = MCG_STAGES * MCG_SMEM_STAGE + MCG_SMEM_GP + 2 * MCG_STAGES * sizeof(uint64_t) + 64;
 
-// One CTA = one 128-target tile x one split of the source tiles.  8 warps as 4 (targets) x 2 (sources); warp tile
-// 32 x 64 = 4 x 8 DMMA tiles.  part[(split*rows + i)] receives the partial sums of target row i.
+// One CTA = one 128-target tile x one split of the source tiles.  Eight warps, arranged 4 (targets) x 2 (sources),
+// warp tile 32 x 64 = 4 x 8 DMMA tiles.  Stages are handed over with a full/empty mbarrier pair each (no CTA-wide
+// barrier in the main loop); lane 0 of warp 0 doubles as the producer: at the top of every iteration it issues the
+// TMA bulk copies of every chunk whose stage the eight warps have already released (non-blocking probe), and only
+// blocks when the chunk it needs next has not been issued yet.  part[(split*rows + i)] receives the partial sums
+// of target row i.
 template <int STABLE>
-__global__ void __launch_bounds__(MCG_THREADS, 1)
+__global__ void __launch_bounds__(MCG_BLOCK, 1)
 k_mc_gemm(const double* __restrict__ P, const double* __restrict__ Q, const double2* __restrict__ gp, McgShape sh,
           long tile0, McAcc* __restrict__ part) {
     extern __shared__ __align__(128) unsigned char smem_raw[];
     double* stage_base = reinterpret_cast<double*>(smem_raw);
     double2* gp_s = reinterpret_cast<double2*>(smem_raw + MCG_STAGES * MCG_SMEM_STAGE);
-    uint64_t* bars = reinterpret_cast<uint64_t*>(smem_raw + MCG_STAGES * MCG_SMEM_STAGE + MCG_SMEM_GP);
+    uint64_t* full = reinterpret_cast<uint64_t*>(smem_raw + MCG_STAGES * MCG_SMEM_STAGE + MCG_SMEM_GP);
+    uint64_t* empty = full + MCG_STAGES;
 
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
-    const int wi = warp & 3, wj = warp >> 2;
+    const int wi = warp & 3, wj = (warp >> 2) & 1;
     const long itile = tile0 + blockIdx.x;
     const long NJ = sh.rows / MCG_TILE;
     const long jt0 = NJ * blockIdx.y / gridDim.y, jt1 = NJ * (blockIdx.y + 1) / gridDim.y;
@@ -253,91 +279,118 @@ k_mc_gemm(const double* __restrict__ P, const double* __restrict__ Q, const doub
     const long total = (jt1 - jt0) * NKC;
 
     if (tid == 0) {
-        for (int s = 0; s < MCG_STAGES; ++s) mbar_init(&bars[s], 1);
+        for (int s = 0; s < MCG_STAGES; ++s) { mbar_init(&full[s], 1); mbar_init(&empty[s], MCG_CONSUMER_WARPS); }
         asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
     }
     __syncthreads();
 
-    auto issue = [&](long it) {
-        const long jl = it / NKC;
-        const int kc = (int)(it - jl * NKC), st = (int)(it % MCG_STAGES);
-        double* ps = stage_base + (size_t)st * (2 * MCG_TILE * MCG_KC);
-        double* qs = ps + MCG_TILE * MCG_KC;
-        const uint32_t chunk_bytes = MCG_TILE * MCG_KC * sizeof(double);
-        mbar_expect_tx(&bars[st], 2 * chunk_bytes + (kc == 0 ? (uint32_t)(MCG_TILE * sizeof(double2)) : 0u));
-        bulk_g2s(ps, P + ((size_t)kc * sh.rows + itile * MCG_TILE) * MCG_KC, chunk_bytes, &bars[st]);
-        bulk_g2s(qs, Q + ((size_t)kc * sh.rows + (jt0 + jl) * MCG_TILE) * MCG_KC, chunk_bytes, &bars[st]);
-        if (kc == 0) bulk_g2s(gp_s + (jl & 1) * MCG_TILE, gp + (jt0 + jl) * MCG_TILE, MCG_TILE * sizeof(double2), &bars[st]);
-    };
-    if (tid == 0)
-        for (long it = 0; it < MCG_STAGES && it < total; ++it) issue(it);
-
-    double acc[4][8][2];
-#pragma unroll
-    for (int mt = 0; mt < 4; ++mt)
-#pragma unroll
-        for (int nt = 0; nt < 8; ++nt) acc[mt][nt][0] = acc[mt][nt][1] = 0.0;
     McAcc racc[4];
 #pragma unroll
-    for (int mt = 0; mt < 4; ++mt) { racc[mt].m = STABLE ? -INFINITY : 0.0; racc[mt].sw = racc[mt].sg = racc[mt].sp = 0.0; }
-
-    // fragment addressing: row = lane/4 within an 8-row MMA tile, column = lane%4 within a 4-wide k-step
+    for (int mt = 0; mt < 4; ++mt) { racc[mt].m = -INFINITY; racc[mt].sw = racc[mt].sg = racc[mt].sp = 0.0; }
     const int frow = lane >> 2, fcol = lane & 3;
-    const int swz = ((frow >> 1) & 1) << 2;                 // tile bases are multiples of 8, so bit 1 of the row is frow's
-    const int a_off = (wi * 32 + frow) * MCG_KC, b_off = (wj * 64 + frow) * MCG_KC;
 
-    for (long it = 0; it < total; ++it) {
-        const int st = (int)(it % MCG_STAGES);
-        const uint32_t parity = (uint32_t)((it / MCG_STAGES) & 1);
-        mbar_wait(&bars[st], parity);
-        const double* ps = stage_base + (size_t)st * (2 * MCG_TILE * MCG_KC);
-        const double* qs = ps + MCG_TILE * MCG_KC;
+    {
+        double acc[4][8][2];
 #pragma unroll
-        for (int ks = 0; ks < 2; ++ks) {
-            const int col = (ks * 4 + fcol) ^ swz;
-            double a[4], b[8];
+        for (int mt = 0; mt < 4; ++mt)
 #pragma unroll
-            for (int mt = 0; mt < 4; ++mt) a[mt] = ps[a_off + mt * 8 * MCG_KC + col];
+            for (int nt = 0; nt < 8; ++nt) acc[mt][nt][0] = acc[mt][nt][1] = 0.0;
+        // fragment addressing: row = lane/4 within an 8-row MMA tile, column = lane%4 within a 4-wide k-step
+        const int swz = ((frow >> 1) & 1) << 2;             // tile bases are multiples of 8, so bit 1 of the row is frow's
+        const int a_off = (wi * 32 + frow) * MCG_KC, b_off = (wj * 64 + frow) * MCG_KC;
+        long jl = 0; int kc = 0;
+        long next = 0, njl = 0; int nkc = 0;                 // producer state (warp 0, lane 0)
+        for (long it = 0; it < total; ++it) {
+            const int st = (int)(it % MCG_STAGES);
+            if (tid == 0) {
+                const uint32_t chunk_bytes = MCG_TILE * MCG_KC * sizeof(double);
+                while (next < total && next < it + MCG_STAGES) {
+                    const int ns = (int)(next % MCG_STAGES);
+                    if (next >= MCG_STAGES) {
+                        const uint32_t par = (uint32_t)(((next / MCG_STAGES) - 1) & 1);
+                        if (next > it) { if (!mbar_test(&empty[ns], par)) break; }   // prefetch only if the stage is free
+                        else mbar_wait(&empty[ns], par);                             // needed now
+                    }
+                    double* ps = stage_base + (size_t)ns * (2 * MCG_TILE * MCG_KC);
+                    double* qs = ps + MCG_TILE * MCG_KC;
+                    mbar_expect_tx(&full[ns], 2 * chunk_bytes + (nkc == 0 ? (uint32_t)(MCG_TILE * sizeof(double2)) : 0u));
+                    bulk_g2s(ps, P + ((size_t)nkc * sh.rows + itile * MCG_TILE) * MCG_KC, chunk_bytes, &full[ns]);
+                    bulk_g2s(qs, Q + ((size_t)nkc * sh.rows + (jt0 + njl) * MCG_TILE) * MCG_KC, chunk_bytes, &full[ns]);
+                    if (nkc == 0) bulk_g2s(gp_s + (njl & 1) * MCG_TILE, gp + (jt0 + njl) * MCG_TILE, MCG_TILE * sizeof(double2), &full[ns]);
+                    if (++nkc == NKC) { nkc = 0; ++njl; }
+                    ++next;
+                }
+            }
+            __syncwarp();
+            mbar_wait(&full[st], (uint32_t)((it / MCG_STAGES) & 1));
+            const double* ps = stage_base + (size_t)st * (2 * MCG_TILE * MCG_KC);
+            const double* qs = ps + MCG_TILE * MCG_KC;
 #pragma unroll
-            for (int nt = 0; nt < 8; ++nt) b[nt] = qs[b_off + nt * 8 * MCG_KC + col];
+            for (int ks = 0; ks < 2; ++ks) {
+                const int col = (ks * 4 + fcol) ^ swz;
+                double a[4], b[8];
 #pragma unroll
-            for (int mt = 0; mt < 4; ++mt)
+                for (int mt = 0; mt < 4; ++mt) a[mt] = ps[a_off + mt * 8 * MCG_KC + col];
 #pragma unroll
-                for (int nt = 0; nt < 8; ++nt) dmma884(acc[mt][nt][0], acc[mt][nt][1], a[mt], b[nt]);
-        }
-        __syncthreads();                                    // every warp is done with stage st
-        if (tid == 0 && it + MCG_STAGES < total) issue(it + MCG_STAGES);
+                for (int nt = 0; nt < 8; ++nt) b[nt] = qs[b_off + nt * 8 * MCG_KC + col];
+#pragma unroll
+                for (int mt = 0; mt < 4; ++mt)
+#pragma unroll
+                    for (int nt = 0; nt < 8; ++nt) dmma884(acc[mt][nt][0], acc[mt][nt][1], a[mt], b[nt]);
+            }
+            __syncwarp();
+            if (lane == 0) mbar_arrive(&empty[st]);          // this warp is done with stage st
 
-        const long jl = it / NKC;
-        if (it - jl * NKC == NKC - 1) {                     // last k-chunk of source tile jl: fold the weights in
-            const long jt = jt0 + jl;
-            const double2* g2 = gp_s + (jl & 1) * MCG_TILE;
-            const bool diag = (jt == itile);
-#pragma unroll
-            for (int nt = 0; nt < 8; ++nt) {
-#pragma unroll
-                for (int e = 0; e < 2; ++e) {
-                    const int jc = wj * 64 + nt * 8 + 2 * fcol + e;
-                    const double2 gpj = g2[jc];
+            if (++kc == NKC) {                               // last k-chunk of source tile jl: fold the weights in
+                const long jt = jt0 + jl;
+                const double2* g2 = gp_s + (jl & 1) * MCG_TILE;
+                const bool diag = (jt == itile);
+                if (!STABLE) {                               // share the running maxima of the 4 lanes of a row
 #pragma unroll
                     for (int mt = 0; mt < 4; ++mt) {
-                        const double L = acc[mt][nt][e];
-                        acc[mt][nt][e] = 0.0;
-                        if (diag && jc == wi * 32 + mt * 8 + frow) continue;      // mu[-i,]   helper_seq.R:11-14
-                        mcg_add<STABLE>(racc[mt], L, gpj.x, gpj.y);
+                        racc[mt].m = fmax(racc[mt].m, __shfl_xor_sync(0xffffffffu, racc[mt].m, 1));
+                        racc[mt].m = fmax(racc[mt].m, __shfl_xor_sync(0xffffffffu, racc[mt].m, 2));
                     }
                 }
+#pragma unroll
+                for (int nt = 0; nt < 8; ++nt) {
+                    // one warp vote per 8-column group skips exp() where every pair of the group is pruned
+                    bool need = false;
+#pragma unroll
+                    for (int mt = 0; mt < 4; ++mt)
+#pragma unroll
+                        for (int e = 0; e < 2; ++e)
+                            need |= STABLE ? (acc[mt][nt][e] > racc[mt].m - MCG_PRUNE)
+                                           : (acc[mt][nt][e] > fmax(racc[mt].m - MCG_PRUNE, -746.0));
+                    if (__any_sync(0xffffffffu, need)) {
+#pragma unroll
+                        for (int e = 0; e < 2; ++e) {
+                            const int jc = wj * 64 + nt * 8 + 2 * fcol + e;
+                            const double2 gpj = g2[jc];
+#pragma unroll
+                            for (int mt = 0; mt < 4; ++mt) {
+                                if (diag && jc == wi * 32 + mt * 8 + frow) continue;          // mu[-i,]   helper_seq.R:11-14
+                                mcg_add<STABLE>(racc[mt], acc[mt][nt][e], gpj.x, gpj.y);
+                            }
+                        }
+                    }
+#pragma unroll
+                    for (int mt = 0; mt < 4; ++mt) acc[mt][nt][0] = acc[mt][nt][1] = 0.0;
+                }
+                kc = 0; ++jl;
             }
         }
     }
     // reduce over the 4 lanes that share a row, then over the two source-side warps
     __syncthreads();
     McAcc* red = reinterpret_cast<McAcc*>(smem_raw);        // [2][128], aliases the (now idle) stage buffers
+    {
 #pragma unroll
-    for (int mt = 0; mt < 4; ++mt) {
-        McAcc a = racc[mt];
-        for (int o = 1; o <= 2; o <<= 1) { const McAcc b = mc_shfl_xor(a, o); mc_merge(a, b, STABLE); }
-        if (fcol == 0) red[wj * MCG_TILE + wi * 32 + mt * 8 + frow] = a;
+        for (int mt = 0; mt < 4; ++mt) {
+            McAcc a = racc[mt];
+            for (int o = 1; o <= 2; o <<= 1) { const McAcc b = mc_shfl_xor(a, o); mc_merge(a, b, STABLE); }
+            if (fcol == 0) red[wj * MCG_TILE + wi * 32 + mt * 8 + frow] = a;
+        }
     }
     __syncthreads();
     if (tid < MCG_TILE) {

@@ -225,9 +225,9 @@ static bool run_mc_batch_gemm(const int32_t* cnt, long G, int n, const int* d_co
         }
         const dim3 grid((unsigned)ntiles, (unsigned)nsplit);
         if (mc_mode == CBS_MC_STABLE)
-            CBS_LAUNCH(k_mc_gemm<1>, grid, MCG_THREADS, MCG_SMEM_BYTES, st, P, Q, gp, sh, tile0, part);
+            CBS_LAUNCH(k_mc_gemm<1>, grid, MCG_BLOCK, MCG_SMEM_BYTES, st, P, Q, gp, sh, tile0, part);
         else
-            CBS_LAUNCH(k_mc_gemm<0>, grid, MCG_THREADS, MCG_SMEM_BYTES, st, P, Q, gp, sh, tile0, part);
+            CBS_LAUNCH(k_mc_gemm<0>, grid, MCG_BLOCK, MCG_SMEM_BYTES, st, P, Q, gp, sh, tile0, part);
         CBS_LAUNCH(k_mcg_finalize, grid1(i1 - i0, 128), 128, 0, st, part, sh.rows, (int)nsplit, i0, i1,
                    mc_mode == CBS_MC_STABLE ? 1 : 0, d_gamma, d_phi, d_gamma_star, d_phi_star, d_nfb);
     }
