@@ -312,6 +312,21 @@ def roofline(L, prof, G, N, nb, world, steps, case):
     name = max(prof, key=lambda k: prof[k][0])
     ms, n = prof[name]
     avg_s = ms / n * 1e-3
+    if name.startswith("k_mc_gemm"):
+        # FP64 tensor-core contraction: log LH = P Q^T with inner length KT = n_b + Kc + 4 + 1;
+        # algorithmic flops of one launch (one batch, this rank's targets x all sources) = 2 * KT * G_targets * G.
+        n_b = float(N) / len(nb)
+        kc = L.get_diag("mc_terms")
+        kt = n_b + kc + 4 + 1
+        flops = 2.0 * kt * (float(G) / world) * G
+        peak = L.fp64_mma_peak_tflops()
+        ach = flops / avg_s / 1e12
+        return {"kernel": name, "bound": "tensor", "achieved": ach, "peak": peak, "unit": "TFLOP/s", "frac": ach / peak,
+                "traffic": None, "avg_launch_ms": ms / n, "launches": n,
+                "note": "FP64 tensor pipe (mma.sync m8n8k4 f64 = DMMA; tcgen05 has no FP64 path). peak = DMMA microbenchmark "
+                        "measured in this run (cbs_fp64_mma_peak; MEASURED_PEAKS.json has no FP64 figure); inner length "
+                        "KT = %d (n_b %d + %d Chebyshev terms + 5); %.3g gene pairs/s = %.3g NB terms/s"
+                        % (kt, n_b, kc, float(G) / world * G / avg_s, float(G) / world * G * n_b / avg_s)}
     if name.startswith("k_mc"):
         fp64 = L.fp64_peak_tflops()
         terms = float(G) * (G - 1.0) * N / world / len(nb)       # per launch: one batch, this rank's target shard

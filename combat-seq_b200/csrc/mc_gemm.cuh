@@ -214,52 +214,54 @@ __device__ __forceinline__ void dmma884(double& c0, double& c1, double a, double
 // carries a weight below e^-40 = 4e-18 of the largest weight; all G of them together change the weighted means by
 // less than 3e-13 relative, so they are dropped before exp() is ever called (and they can never turn an all-zero
 // row, the helper_seq.R:30-31 fallback, into a non-zero one: what is dropped is smaller than a weight already seen).
-// In reference mode a.m is only this running maximum; the weights themselves stay exp(L), unshifted, so that they
-// underflow exactly where R's prod(dnbinom) does.
+// In reference mode McAcc::m is only this running maximum; the weights themselves stay exp(L), unshifted, so that
+// they underflow exactly where R's prod(dnbinom) does.  In stable mode the sums are kept relative to exp(m)
+// (online log-sum-exp, rescaled once per source tile when the maximum moves).
 constexpr double MCG_PRUNE = 40.0;
-template <int STABLE>
-__device__ __forceinline__ void mcg_add(McAcc& a, double L, double g, double p) {
-    if (!STABLE) {
-        if (L > a.m) a.m = L;
-        if (L > -746.0 && L >= a.m - MCG_PRUNE) {      // exp(L) == 0 below -745.14 (denormal minimum / 2)
-            const double w = exp(L);
-            a.sw += w; a.sg += w * g; a.sp += w * p;
-        }
-    } else {
-        if (L > a.m && L > -1e29) {                    // -1e30 stands for log(0): an impossible source, weight 0
-            const double sc = exp(a.m - L);            // exp(-inf) = 0 on the first hit
-            a.sw = a.sw * sc + 1.0; a.sg = a.sg * sc + g; a.sp = a.sp * sc + p; a.m = L;
-        } else if (L > a.m - MCG_PRUNE) {
-            const double w = exp(L - a.m);
-            a.sw += w; a.sg += w * g; a.sp += w * p;
-        }
-    }
-}
 
 __device__ __forceinline__ void mbar_arrive(uint64_t* bar) {
     asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(smem_u32(bar)) : "memory");
 }
 
-// non-blocking probe of a phase
-__device__ __forceinline__ bool mbar_test(uint64_t* bar, uint32_t parity) {
-    uint32_t ok;
-    asm volatile("{\n\t.reg .pred p;\n\tmbarrier.test_wait.parity.shared::cta.b64 p, [%1], %2;\n\tselp.u32 %0, 1, 0, p;\n\t}"
-                 : "=r"(ok) : "r"(smem_u32(bar)), "r"(parity) : "memory");
-    return ok != 0;
+// exp(x) for x <= ~0.5 down to the underflow threshold (x < -745.14 gives 0; results in the denormal range are
+// rounded once, like the libm exp): x = k ln2 + r, |r| <= ln2/2, degree-12 Taylor polynomial evaluated with Estrin's
+// scheme (dependency depth 4 instead of 12, so that several independent calls overlap on the FP64 pipe), scaled by
+// 2^k in two normal-range factors.  Relative error < 4e-16.  Garbage (not a trap) for x = -inf / NaN: callers mask.
+__device__ __forceinline__ double mcg_exp(double x) {
+    const double kd = fma(x, 1.4426950408889634, 6755399441055744.0);           // 1.5 * 2^52: round to nearest integer
+    const int k = __double2loint(kd);
+    const double kf = kd - 6755399441055744.0;
+    double r = fma(kf, -6.93147180369123816490e-01, x);
+    r = fma(kf, -1.90821492927058770002e-10, r);
+    const double r2 = r * r, r4 = r2 * r2, r8 = r4 * r4;
+    const double a0 = 1.0 + r;
+    const double a1 = fma(r, 1.0 / 6, 0.5);
+    const double a2 = fma(r, 1.0 / 120, 1.0 / 24);
+    const double a3 = fma(r, 1.0 / 5040, 1.0 / 720);
+    const double a4 = fma(r, 1.0 / 362880, 1.0 / 40320);
+    const double a5 = fma(r, 1.0 / 39916800, 1.0 / 3628800);
+    const double b0 = fma(a1, r2, a0), b1 = fma(a3, r2, a2), b2 = fma(a5, r2, a4);
+    const double d0 = fma(b1, r4, b0), d1 = fma(1.0 / 479001600, r4, b2);
+    const double p = fma(d1, r8, d0);
+    const int k1 = k >> 1, k2 = k - k1;
+    const double s1 = __hiloint2double((k1 + 1023) << 20, 0), s2 = __hiloint2double((k2 + 1023) << 20, 0);
+    return (p * s1) * s2;
 }
 
 constexpr int MCG_CONSUMER_WARPS = 8;
-constexpr int MCG_BLOCK = MCG_THREADS;
+constexpr int MCG_BLOCK = MCG_CONSUMER_WARPS * 32;
 constexpr size_t MCG_SMEM_STAGE = 2 * MCG_TILE * MCG_KC * sizeof(double);                         // P + Q chunk
 constexpr size_t MCG_SMEM_GP = 2 * MCG_TILE * 2 * sizeof(double);                                 // 2 buffers
-constexpr size_t MCG_SMEM_BYTES = MCG_STAGES * MCG_SMEM_STAGE + MCG_SMEM_GP + 2 * MCG_STAGES * sizeof(uint64_t) + 64;
+constexpr size_t MCG_SMEM_BYTES = MCG_STAGES * MCG_SMEM_STAGE + MCG_SMEM_GP + 2 * MCG_STAGES * sizeof(uint64_t) + 64;   // full[] + done[]
+static_assert(MCG_THREADS == MCG_CONSUMER_WARPS * 32, "consumer thread count");
 
-// One CTA = one 128-target tile x one split of the source tiles.  Eight warps, arranged 4 (targets) x 2 (sources),
-// warp tile 32 x 64 = 4 x 8 DMMA tiles.  Stages are handed over with a full/empty mbarrier pair each (no CTA-wide
-// barrier in the main loop); lane 0 of warp 0 doubles as the producer: at the top of every iteration it issues the
-// TMA bulk copies of every chunk whose stage the eight warps have already released (non-blocking probe), and only
-// blocks when the chunk it needs next has not been issued yet.  part[(split*rows + i)] receives the partial sums
-// of target row i.
+// One CTA = one 128-target tile x one split of the source tiles.  Eight MMA warps, arranged 4 (targets) x 2
+// (sources), warp tile 32 x 64 = 4 x 8 DMMA tiles.  The k-chunks stream through a ring of MCG_STAGES stages filled
+// by TMA bulk copies that complete on a `full` mbarrier per stage.  There is no producer thread and no CTA-wide
+// barrier in the main loop: every warp counts itself out of a stage (shared-memory atomic), and the LAST warp to
+// leave a stage issues the copies that refill it.  A warp that is folding the weights of a finished source tile
+// (FP64 pipe) therefore never holds up the refills the other warps are waiting for, and the other warp of its
+// scheduler keeps the tensor pipe busy meanwhile.  part[(split*rows + i)] receives the partial sums of target row i.
 template <int STABLE>
 __global__ void __launch_bounds__(MCG_BLOCK, 1)
 k_mc_gemm(const double* __restrict__ P, const double* __restrict__ Q, const double2* __restrict__ gp, McgShape sh,
@@ -268,7 +270,7 @@ k_mc_gemm(const double* __restrict__ P, const double* __restrict__ Q, const doub
     double* stage_base = reinterpret_cast<double*>(smem_raw);
     double2* gp_s = reinterpret_cast<double2*>(smem_raw + MCG_STAGES * MCG_SMEM_STAGE);
     uint64_t* full = reinterpret_cast<uint64_t*>(smem_raw + MCG_STAGES * MCG_SMEM_STAGE + MCG_SMEM_GP);
-    uint64_t* empty = full + MCG_STAGES;
+    unsigned int* done = reinterpret_cast<unsigned int*>(full + MCG_STAGES);    // warps that have left each stage
 
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     const int wi = warp & 3, wj = (warp >> 2) & 1;
@@ -279,10 +281,27 @@ k_mc_gemm(const double* __restrict__ P, const double* __restrict__ Q, const doub
     const long total = (jt1 - jt0) * NKC;
 
     if (tid == 0) {
-        for (int s = 0; s < MCG_STAGES; ++s) { mbar_init(&full[s], 1); mbar_init(&empty[s], MCG_CONSUMER_WARPS); }
+        for (int s = 0; s < MCG_STAGES; ++s) { mbar_init(&full[s], 1); done[s] = 0; }
         asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
     }
     __syncthreads();
+
+    // copies of k-chunk `c` (P chunk, Q chunk and, with the first chunk of a source tile, its gamma/phi) into its stage
+    auto issue = [&](long c) {
+        const int ns = (int)(c % MCG_STAGES);
+        const long njl = c / NKC; const int nkc = (int)(c - njl * NKC);
+        const uint32_t chunk_bytes = MCG_TILE * MCG_KC * sizeof(double);
+        double* ps = stage_base + (size_t)ns * (2 * MCG_TILE * MCG_KC);
+        double* qs = ps + MCG_TILE * MCG_KC;
+        mbar_expect_tx(&full[ns], 2 * chunk_bytes + (nkc == 0 ? (uint32_t)(MCG_TILE * sizeof(double2)) : 0u));
+        bulk_g2s(ps, P + ((size_t)nkc * sh.rows + itile * MCG_TILE) * MCG_KC, chunk_bytes, &full[ns]);
+        bulk_g2s(qs, Q + ((size_t)nkc * sh.rows + (jt0 + njl) * MCG_TILE) * MCG_KC, chunk_bytes, &full[ns]);
+        // gamma/phi of source tile njl are double-buffered: buffer (njl & 1) was last read in the epilogue of tile
+        // njl - 2, which every warp has finished before it leaves chunk njl * NKC - MCG_STAGES (NKC > MCG_STAGES).
+        if (nkc == 0) bulk_g2s(gp_s + (njl & 1) * MCG_TILE, gp + (jt0 + njl) * MCG_TILE, MCG_TILE * sizeof(double2), &full[ns]);
+    };
+    if (tid == 0)
+        for (long c = 0; c < total && c < MCG_STAGES; ++c) issue(c);
 
     McAcc racc[4];
 #pragma unroll
@@ -290,6 +309,7 @@ k_mc_gemm(const double* __restrict__ P, const double* __restrict__ Q, const doub
     const int frow = lane >> 2, fcol = lane & 3;
 
     {
+        // ---- MMA warps ----
         double acc[4][8][2];
 #pragma unroll
         for (int mt = 0; mt < 4; ++mt)
@@ -299,29 +319,8 @@ k_mc_gemm(const double* __restrict__ P, const double* __restrict__ Q, const doub
         const int swz = ((frow >> 1) & 1) << 2;             // tile bases are multiples of 8, so bit 1 of the row is frow's
         const int a_off = (wi * 32 + frow) * MCG_KC, b_off = (wj * 64 + frow) * MCG_KC;
         long jl = 0; int kc = 0;
-        long next = 0, njl = 0; int nkc = 0;                 // producer state (warp 0, lane 0)
         for (long it = 0; it < total; ++it) {
             const int st = (int)(it % MCG_STAGES);
-            if (tid == 0) {
-                const uint32_t chunk_bytes = MCG_TILE * MCG_KC * sizeof(double);
-                while (next < total && next < it + MCG_STAGES) {
-                    const int ns = (int)(next % MCG_STAGES);
-                    if (next >= MCG_STAGES) {
-                        const uint32_t par = (uint32_t)(((next / MCG_STAGES) - 1) & 1);
-                        if (next > it) { if (!mbar_test(&empty[ns], par)) break; }   // prefetch only if the stage is free
-                        else mbar_wait(&empty[ns], par);                             // needed now
-                    }
-                    double* ps = stage_base + (size_t)ns * (2 * MCG_TILE * MCG_KC);
-                    double* qs = ps + MCG_TILE * MCG_KC;
-                    mbar_expect_tx(&full[ns], 2 * chunk_bytes + (nkc == 0 ? (uint32_t)(MCG_TILE * sizeof(double2)) : 0u));
-                    bulk_g2s(ps, P + ((size_t)nkc * sh.rows + itile * MCG_TILE) * MCG_KC, chunk_bytes, &full[ns]);
-                    bulk_g2s(qs, Q + ((size_t)nkc * sh.rows + (jt0 + njl) * MCG_TILE) * MCG_KC, chunk_bytes, &full[ns]);
-                    if (nkc == 0) bulk_g2s(gp_s + (njl & 1) * MCG_TILE, gp + (jt0 + njl) * MCG_TILE, MCG_TILE * sizeof(double2), &full[ns]);
-                    if (++nkc == NKC) { nkc = 0; ++njl; }
-                    ++next;
-                }
-            }
-            __syncwarp();
             mbar_wait(&full[st], (uint32_t)((it / MCG_STAGES) & 1));
             const double* ps = stage_base + (size_t)st * (2 * MCG_TILE * MCG_KC);
             const double* qs = ps + MCG_TILE * MCG_KC;
@@ -339,39 +338,71 @@ k_mc_gemm(const double* __restrict__ P, const double* __restrict__ Q, const doub
                     for (int nt = 0; nt < 8; ++nt) dmma884(acc[mt][nt][0], acc[mt][nt][1], a[mt], b[nt]);
             }
             __syncwarp();
-            if (lane == 0) mbar_arrive(&empty[st]);          // this warp is done with stage st
+            if (lane == 0) {                                 // this warp is done with stage st; the last one out refills it
+                __threadfence_block();
+                if (atomicAdd(&done[st], 1u) == MCG_CONSUMER_WARPS - 1) {
+                    done[st] = 0;
+                    __threadfence_block();
+                    if (it + MCG_STAGES < total) issue(it + MCG_STAGES);
+                }
+            }
 
             if (++kc == NKC) {                               // last k-chunk of source tile jl: fold the weights in
                 const long jt = jt0 + jl;
                 const double2* g2 = gp_s + (jl & 1) * MCG_TILE;
-                const bool diag = (jt == itile);
-                if (!STABLE) {                               // share the running maxima of the 4 lanes of a row
-#pragma unroll
-                    for (int mt = 0; mt < 4; ++mt) {
-                        racc[mt].m = fmax(racc[mt].m, __shfl_xor_sync(0xffffffffu, racc[mt].m, 1));
-                        racc[mt].m = fmax(racc[mt].m, __shfl_xor_sync(0xffffffffu, racc[mt].m, 2));
-                    }
-                }
-#pragma unroll
-                for (int nt = 0; nt < 8; ++nt) {
-                    // one warp vote per 8-column group skips exp() where every pair of the group is pruned
-                    bool need = false;
+                if (jt == itile) {                           // mu[-i,]: the gene itself is not a source  helper_seq.R:11-14
 #pragma unroll
                     for (int mt = 0; mt < 4; ++mt)
 #pragma unroll
-                        for (int e = 0; e < 2; ++e)
-                            need |= STABLE ? (acc[mt][nt][e] > racc[mt].m - MCG_PRUNE)
-                                           : (acc[mt][nt][e] > fmax(racc[mt].m - MCG_PRUNE, -746.0));
+                        for (int nt = 0; nt < 8; ++nt)
+#pragma unroll
+                            for (int e = 0; e < 2; ++e)
+                                if (wj * 64 + nt * 8 + 2 * fcol + e == wi * 32 + mt * 8 + frow) acc[mt][nt][e] = -INFINITY;
+                }
+                // running maximum of every target row (shared by the 4 lanes that hold the row) -> prune threshold
+                double thr[4];
+#pragma unroll
+                for (int mt = 0; mt < 4; ++mt) {
+                    double mx = fmax(acc[mt][0][0], acc[mt][0][1]);
+#pragma unroll
+                    for (int nt = 1; nt < 8; ++nt) mx = fmax(mx, fmax(acc[mt][nt][0], acc[mt][nt][1]));
+                    mx = fmax(mx, __shfl_xor_sync(0xffffffffu, mx, 1));
+                    mx = fmax(mx, __shfl_xor_sync(0xffffffffu, mx, 2));
+                    if (STABLE) {
+                        if (mx > racc[mt].m && mx > -1e29) {         // -1e30 stands for log(0): an impossible source
+                            const double sc = exp(racc[mt].m - mx);  // exp(-inf) = 0 on the first hit
+                            racc[mt].sw *= sc; racc[mt].sg *= sc; racc[mt].sp *= sc; racc[mt].m = mx;
+                        }
+                        thr[mt] = fmax(racc[mt].m - MCG_PRUNE, -1e29);
+                    } else {
+                        racc[mt].m = fmax(racc[mt].m, mx);
+                        thr[mt] = fmax(racc[mt].m - MCG_PRUNE, -746.0);   // exp(L) == 0 below -745.14
+                    }
+                }
+                // Fold the weights in.  A sizeable share of the pairs survives the pruning (about one in eight on
+                // RNA-seq-like data), so every lane group has work: the 8 elements of a column group are evaluated
+                // branch-free and independently (8 interleaved mcg_exp chains keep the FP64 pipe busy) and masked;
+                // one warp vote skips a column group whose 256 pairs are all pruned (far-apart genes).
+#pragma unroll
+                for (int nt = 0; nt < 8; ++nt) {
+                    bool need = false;
+#pragma unroll
+                    for (int mt = 0; mt < 4; ++mt) need |= (acc[mt][nt][0] > thr[mt]) | (acc[mt][nt][1] > thr[mt]);
                     if (__any_sync(0xffffffffu, need)) {
+                        const double2 gp0 = g2[wj * 64 + nt * 8 + 2 * fcol], gp1 = g2[wj * 64 + nt * 8 + 2 * fcol + 1];
+                        double w0[4], w1[4];
 #pragma unroll
-                        for (int e = 0; e < 2; ++e) {
-                            const int jc = wj * 64 + nt * 8 + 2 * fcol + e;
-                            const double2 gpj = g2[jc];
+                        for (int mt = 0; mt < 4; ++mt) {
+                            const double L0 = acc[mt][nt][0], L1 = acc[mt][nt][1];
+                            const double e0 = mcg_exp(STABLE ? L0 - racc[mt].m : L0), e1 = mcg_exp(STABLE ? L1 - racc[mt].m : L1);
+                            w0[mt] = (L0 > thr[mt]) ? e0 : 0.0;
+                            w1[mt] = (L1 > thr[mt]) ? e1 : 0.0;
+                        }
 #pragma unroll
-                            for (int mt = 0; mt < 4; ++mt) {
-                                if (diag && jc == wi * 32 + mt * 8 + frow) continue;          // mu[-i,]   helper_seq.R:11-14
-                                mcg_add<STABLE>(racc[mt], acc[mt][nt][e], gpj.x, gpj.y);
-                            }
+                        for (int mt = 0; mt < 4; ++mt) {
+                            racc[mt].sw += w0[mt] + w1[mt];
+                            racc[mt].sg = fma(w1[mt], gp1.x, fma(w0[mt], gp0.x, racc[mt].sg));
+                            racc[mt].sp = fma(w1[mt], gp1.y, fma(w0[mt], gp0.y, racc[mt].sp));
                         }
                     }
 #pragma unroll
