@@ -34,8 +34,10 @@
 namespace cbs {
 
 constexpr int MCG_TILE = 128;        // CTA tile: 128 targets x 128 sources
-constexpr int MCG_KC = 8;            // k-chunk (doubles) per pipeline stage
-constexpr int MCG_STAGES = 6;
+constexpr int MCG_KC = 8;            // k-chunk (doubles): the unit of the global layout and of one bulk copy
+constexpr int MCG_SUB = 2;           // k-chunks per pipeline stage (16 doubles of K per hand-over)
+constexpr int MCG_STAGES = 5;
+constexpr int MCG_GPBUF = 4;         // buffers of the per-source-tile (gamma, phi) pairs
 constexpr int MCG_MAX_KC = 64;       // max Chebyshev terms
 constexpr int MCG_SHIFT = 4;         // c: counts below c use the one-hot table
 constexpr int MCG_THREADS = 256;
@@ -44,7 +46,7 @@ struct McgShape {
     int n;          // samples in the batch
     int Kc;         // Chebyshev terms
     int KT;         // n + Kc + MCG_SHIFT + 1
-    int KTP;        // KT rounded up to a multiple of MCG_KC
+    int KTP;        // KT rounded up to a multiple of MCG_KC * MCG_SUB
     long rows;      // matrix rows, G rounded up to a multiple of MCG_TILE
     double ulo, uhi;   // range of u = log(r + c)
 };
@@ -250,8 +252,8 @@ __device__ __forceinline__ double mcg_exp(double x) {
 
 constexpr int MCG_CONSUMER_WARPS = 8;
 constexpr int MCG_BLOCK = MCG_CONSUMER_WARPS * 32;
-constexpr size_t MCG_SMEM_STAGE = 2 * MCG_TILE * MCG_KC * sizeof(double);                         // P + Q chunk
-constexpr size_t MCG_SMEM_GP = 2 * MCG_TILE * 2 * sizeof(double);                                 // 2 buffers
+constexpr size_t MCG_SMEM_STAGE = (size_t)MCG_SUB * 2 * MCG_TILE * MCG_KC * sizeof(double);       // SUB x (P + Q chunk)
+constexpr size_t MCG_SMEM_GP = (size_t)MCG_GPBUF * MCG_TILE * 2 * sizeof(double);
 constexpr size_t MCG_SMEM_BYTES = MCG_STAGES * MCG_SMEM_STAGE + MCG_SMEM_GP + 2 * MCG_STAGES * sizeof(uint64_t) + 64;   // full[] + done[]
 static_assert(MCG_THREADS == MCG_CONSUMER_WARPS * 32, "consumer thread count");
 
@@ -277,8 +279,8 @@ k_mc_gemm(const double* __restrict__ P, const double* __restrict__ Q, const doub
     const long itile = tile0 + blockIdx.x;
     const long NJ = sh.rows / MCG_TILE;
     const long jt0 = NJ * blockIdx.y / gridDim.y, jt1 = NJ * (blockIdx.y + 1) / gridDim.y;
-    const int NKC = sh.KTP / MCG_KC;
-    const long total = (jt1 - jt0) * NKC;
+    const int NKS = sh.KTP / (MCG_KC * MCG_SUB);                  // stages per source tile
+    const long total = (jt1 - jt0) * NKS;
 
     if (tid == 0) {
         for (int s = 0; s < MCG_STAGES; ++s) { mbar_init(&full[s], 1); done[s] = 0; }
@@ -286,19 +288,23 @@ k_mc_gemm(const double* __restrict__ P, const double* __restrict__ Q, const doub
     }
     __syncthreads();
 
-    // copies of k-chunk `c` (P chunk, Q chunk and, with the first chunk of a source tile, its gamma/phi) into its stage
+    // copies of hand-over `c` (MCG_SUB P chunks and Q chunks and, with the first one of a source tile, its gamma/phi)
     auto issue = [&](long c) {
         const int ns = (int)(c % MCG_STAGES);
-        const long njl = c / NKC; const int nkc = (int)(c - njl * NKC);
+        const long njl = c / NKS; const int nks = (int)(c - njl * NKS);
         const uint32_t chunk_bytes = MCG_TILE * MCG_KC * sizeof(double);
-        double* ps = stage_base + (size_t)ns * (2 * MCG_TILE * MCG_KC);
-        double* qs = ps + MCG_TILE * MCG_KC;
-        mbar_expect_tx(&full[ns], 2 * chunk_bytes + (nkc == 0 ? (uint32_t)(MCG_TILE * sizeof(double2)) : 0u));
-        bulk_g2s(ps, P + ((size_t)nkc * sh.rows + itile * MCG_TILE) * MCG_KC, chunk_bytes, &full[ns]);
-        bulk_g2s(qs, Q + ((size_t)nkc * sh.rows + (jt0 + njl) * MCG_TILE) * MCG_KC, chunk_bytes, &full[ns]);
-        // gamma/phi of source tile njl are double-buffered: buffer (njl & 1) was last read in the epilogue of tile
-        // njl - 2, which every warp has finished before it leaves chunk njl * NKC - MCG_STAGES (NKC > MCG_STAGES).
-        if (nkc == 0) bulk_g2s(gp_s + (njl & 1) * MCG_TILE, gp + (jt0 + njl) * MCG_TILE, MCG_TILE * sizeof(double2), &full[ns]);
+        double* sb = stage_base + (size_t)ns * (MCG_SUB * 2 * MCG_TILE * MCG_KC);
+        mbar_expect_tx(&full[ns], MCG_SUB * 2 * chunk_bytes + (nks == 0 ? (uint32_t)(MCG_TILE * sizeof(double2)) : 0u));
+#pragma unroll
+        for (int u = 0; u < MCG_SUB; ++u) {
+            const size_t kc = (size_t)nks * MCG_SUB + u;
+            bulk_g2s(sb + (2 * u) * MCG_TILE * MCG_KC, P + (kc * sh.rows + itile * MCG_TILE) * MCG_KC, chunk_bytes, &full[ns]);
+            bulk_g2s(sb + (2 * u + 1) * MCG_TILE * MCG_KC, Q + (kc * sh.rows + (jt0 + njl) * MCG_TILE) * MCG_KC, chunk_bytes, &full[ns]);
+        }
+        // gamma/phi of source tile njl go to buffer njl % MCG_GPBUF, last read in the epilogue of tile njl - MCG_GPBUF,
+        // which every warp has finished before it leaves hand-over njl * NKS - MCG_STAGES
+        // ((MCG_GPBUF - 1) * NKS >= MCG_STAGES + 1 is guaranteed by the host: KTP >= 2 stages).
+        if (nks == 0) bulk_g2s(gp_s + (njl % MCG_GPBUF) * MCG_TILE, gp + (jt0 + njl) * MCG_TILE, MCG_TILE * sizeof(double2), &full[ns]);
     };
     if (tid == 0)
         for (long c = 0; c < total && c < MCG_STAGES; ++c) issue(c);
@@ -319,10 +325,12 @@ k_mc_gemm(const double* __restrict__ P, const double* __restrict__ Q, const doub
         const int swz = ((frow >> 1) & 1) << 2;             // tile bases are multiples of 8, so bit 1 of the row is frow's
         const int a_off = (wi * 32 + frow) * MCG_KC, b_off = (wj * 64 + frow) * MCG_KC;
         long jl = 0; int kc = 0;
+        int st = 0; uint32_t phase = 0;
         for (long it = 0; it < total; ++it) {
-            const int st = (int)(it % MCG_STAGES);
-            mbar_wait(&full[st], (uint32_t)((it / MCG_STAGES) & 1));
-            const double* ps = stage_base + (size_t)st * (2 * MCG_TILE * MCG_KC);
+            mbar_wait(&full[st], phase);
+#pragma unroll
+            for (int u = 0; u < MCG_SUB; ++u) {
+            const double* ps = stage_base + (size_t)st * (MCG_SUB * 2 * MCG_TILE * MCG_KC) + (2 * u) * MCG_TILE * MCG_KC;
             const double* qs = ps + MCG_TILE * MCG_KC;
 #pragma unroll
             for (int ks = 0; ks < 2; ++ks) {
@@ -337,19 +345,21 @@ k_mc_gemm(const double* __restrict__ P, const double* __restrict__ Q, const doub
 #pragma unroll
                     for (int nt = 0; nt < 8; ++nt) dmma884(acc[mt][nt][0], acc[mt][nt][1], a[mt], b[nt]);
             }
+            }
             __syncwarp();
             if (lane == 0) {                                 // this warp is done with stage st; the last one out refills it
-                __threadfence_block();
-                if (atomicAdd(&done[st], 1u) == MCG_CONSUMER_WARPS - 1) {
+                uint32_t old;
+                asm volatile("atom.acq_rel.cta.shared::cta.add.u32 %0, [%1], 1;" : "=r"(old) : "r"(smem_u32(&done[st])) : "memory");
+                if (old == MCG_CONSUMER_WARPS - 1) {
                     done[st] = 0;
-                    __threadfence_block();
                     if (it + MCG_STAGES < total) issue(it + MCG_STAGES);
                 }
             }
+            if (++st == MCG_STAGES) { st = 0; phase ^= 1u; }
 
-            if (++kc == NKC) {                               // last k-chunk of source tile jl: fold the weights in
+            if (++kc == NKS) {                               // last k-chunk of source tile jl: fold the weights in
                 const long jt = jt0 + jl;
-                const double2* g2 = gp_s + (jl & 1) * MCG_TILE;
+                const double2* g2 = gp_s + (jl % MCG_GPBUF) * MCG_TILE;
                 if (jt == itile) {                           // mu[-i,]: the gene itself is not a source  helper_seq.R:11-14
 #pragma unroll
                     for (int mt = 0; mt < 4; ++mt)

@@ -193,7 +193,9 @@ static bool run_mc_batch_gemm(const int32_t* cnt, long G, int n, const int* d_co
     sh.Kc = mcg_terms(0.5 * (sh.uhi - sh.ulo));
     if (sh.Kc > MCG_MAX_KC) return false;
     sh.KT = n + sh.Kc + MCG_SHIFT + 1;
-    sh.KTP = std::max((sh.KT + MCG_KC - 1) / MCG_KC * MCG_KC, (MCG_STAGES + 1) * MCG_KC);
+    const int kstage = MCG_KC * MCG_SUB;                          // K per pipeline hand-over
+    sh.KTP = std::max((sh.KT + kstage - 1) / kstage * kstage, 2 * kstage);
+    static_assert((MCG_GPBUF - 1) * 2 >= MCG_STAGES + 1, "gamma/phi buffers must outlive the stage ring");
     sh.rows = (G + MCG_TILE - 1) / MCG_TILE * MCG_TILE;
     g_last_mc_kc = sh.Kc;
     std::vector<double> dct((size_t)sh.Kc * sh.Kc);
