@@ -23,7 +23,7 @@ STAGES = ("h2d", "prep", "common_disp", "tagwise_disp", "glm", "mc", "match_quan
 
 # every symbol include/combatseq.h declares (tests check that the library exports all of them)
 EXPORTS = ("cbs_version", "cbs_device_count", "cbs_last_error", "cbs_shutdown", "cbs_kernel_launches",
-           "cbs_comm_unique_id", "cbs_comm_create", "cbs_comm_destroy", "cbs_combat_seq", "cbs_nb_logpmf",
+           "cbs_comm_unique_id", "cbs_comm_create", "cbs_comm_destroy", "cbs_shard_range", "cbs_combat_seq", "cbs_nb_logpmf",
            "cbs_nb_cdf", "cbs_nb_quantile", "cbs_glm_fit", "cbs_apl", "cbs_common_disp", "cbs_tagwise_disp",
            "cbs_mc_int", "cbs_match_quantiles", "cbs_profile_enable", "cbs_profile_dump", "cbs_fp64_peak",
            "cbs_fp64_mma_peak", "cbs_set_tuning", "cbs_get_diag")
@@ -222,6 +222,13 @@ def comm_create(uid, rank, world, device):
     h = C.c_void_p()
     check(lib().cbs_comm_create(buf, rank, world, device, C.byref(h)))
     return h
+
+
+def shard_range(G, rank, world):
+    """Kept-gene rows [g0, g1) of `rank` (cbs_shard_range; host-only)."""
+    a, b = C.c_int64(0), C.c_int64(0)
+    check(lib().cbs_shard_range(C.c_int64(G), C.c_int32(rank), C.c_int32(world), C.byref(a), C.byref(b)))
+    return a.value, b.value
 
 
 def comm_destroy(h):

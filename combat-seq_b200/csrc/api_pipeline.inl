@@ -219,8 +219,16 @@ static void pipeline(const cbs_input* in, cbs_output* out, const T* h_or_d_count
 
 }  // namespace cbs
 
+extern "C" int cbs_shard_range(int64_t G, int32_t rank, int32_t world, int64_t* g0, int64_t* g1) {
+    if (G < 0 || world < 1 || rank < 0 || rank >= world || !g0 || !g1) return fail(CBS_EINVAL, "bad shard arguments");
+    long a, b;
+    shard_range((long)G, rank, world, &a, &b);
+    *g0 = a; *g1 = b;
+    return CBS_OK;
+}
+
 extern "C" int cbs_combat_seq(const cbs_input* in, cbs_output* out) {
-    CBS_NEED_GPU();
+    // argument validation comes first (it needs no device): the reference's stop() conditions keep their wording
     if (!in || !out) return fail(CBS_EINVAL, "null input/output struct");
     if (in->G0 <= 0 || in->N <= 0 || in->B <= 0 || in->p_mod < 1) return fail(CBS_EINVAL, "bad dimensions");
     if ((in->counts_f64 != nullptr) == (in->counts_i32 != nullptr)) return fail(CBS_EINVAL, "exactly one of counts_f64 / counts_i32 must be set");
@@ -253,6 +261,7 @@ extern "C" int cbs_combat_seq(const cbs_input* in, cbs_output* out) {
             }
         }
     }
+    CBS_NEED_GPU();
     CBS_ENTRY_BEGIN
     int dev = in->comm ? in->comm->device : in->device;
     if (dev >= 0) CBS_CUDA(cudaSetDevice(dev));

@@ -88,6 +88,10 @@ typedef struct cbs_comm cbs_comm;
 int cbs_comm_unique_id(void* id128);
 int cbs_comm_create(const void* id128, int rank, int world, int device, cbs_comm** out);
 int cbs_comm_destroy(cbs_comm* comm);
+/* Kept-gene rows [g0, g1) owned by `rank` of `world`: contiguous blocks rounded up to the 1024-gene reduction chunk, so
+ * that the chunk partial sums of the common-dispersion objective (and everything downstream) do not depend on the
+ * number of GPUs.  Host-only (needs no device). */
+int cbs_shard_range(int64_t G, int32_t rank, int32_t world, int64_t* g0, int64_t* g1);
 
 /* ---- the whole ComBat_seq() numeric body (ComBat_seq.R:33-203) -------------------------------------- */
 typedef struct {
