@@ -160,7 +160,7 @@ def run_reference(args):
     pkg = graft.load_package()
     case, d = make_case(pkg, args.workload, args.genes)
     G0, N = case.counts.shape
-    threads = min(cpu_threads(), graft.load_oracle().max_threads())
+    threads = cpu_threads()                       # explicit num_threads(): torchrun sets OMP_NUM_THREADS=1
     rows = args.cpu_genes or auto_cpu_rows(case)
     for _ in range(args.warmup):
         cpu_sample(case, d, max(50, rows // 4), threads)
@@ -286,7 +286,7 @@ def run_native(args):
                                "share": round(v[0] / total_k, 4)} for k, v in sorted(prof.items(), key=lambda kv: -kv[1][0])}
         line["roofline"] = roofline(L, prof, G, N, nb, world, args.steps, case)
         if world == 1 and not args.no_cpu:
-            threads = min(cpu_threads(), graft.load_oracle().max_threads())
+            threads = cpu_threads()                       # explicit num_threads(): torchrun sets OMP_NUM_THREADS=1
             r = cpu_sample(case, d, args.cpu_genes or auto_cpu_rows(case), threads)
             line["cpu_baseline"] = {"value": r["value"], "unit": UNIT, "cores": threads, "kind": "port",
                                     "sample": "CPU oracle (C++ restatement; R/edgeR not installed) on the first %d kept genes x %d "

@@ -64,25 +64,50 @@ struct Row {
 
 __device__ __forceinline__ int tri(int i, int j) { return i * (i + 1) / 2 + j; }   // i >= j
 
+// ---- lane groups --------------------------------------------------------------------------------------------------
+// The fitters are templates on LANES, the number of consecutive lanes of a warp that share one gene.  LANES = 1 is the
+// plain one-thread-per-gene form.  With LANES > 1 lane `ln` of the group takes the samples t = ln, ln + LANES, ... of
+// every sweep and the partial sums are combined with an XOR butterfly over the group's lanes (mask `gm`): a + b and
+// b + a are the same double, so every lane of the group ends up with bit-identical sums and the (data-dependent)
+// control flow of the iteration stays uniform inside the group.  Everything that is not a sweep over the samples
+// (Cholesky, lambda schedule, convergence tests) is done redundantly by all lanes of the group.
+template <int LANES>
+__device__ __forceinline__ double lane_sum(double v, unsigned gm) {
+#pragma unroll
+    for (int o = LANES / 2; o > 0; o >>= 1) v += __shfl_xor_sync(gm, v, o);
+    return v;
+}
+template <int LANES>
+__device__ __forceinline__ double lane_max(double v, unsigned gm) {
+#pragma unroll
+    for (int o = LANES / 2; o > 0; o >>= 1) v = fmax(v, __shfl_xor_sync(gm, v, o));
+    return v;
+}
+
 // edgeR glm_one_group on samples [t0,t1) of the design's sample list
-__device__ inline double fit_one_group(const DesignDev& d, const Row& r, int t0, int t1, int maxit, double tol) {
-    bool nonzero = false;
+template <int LANES = 1>
+__device__ inline double fit_one_group(const DesignDev& d, const Row& r, int t0, int t1, int maxit, double tol,
+                                       int ln = 0, unsigned gm = 0xffffffffu) {
+    double nz = 0;
     double cur = 0;
-    for (int t = t0; t < t1; ++t) {
+    for (int t = t0 + ln; t < t1; t += LANES) {
         const int c = d.col[t];
         const double y = r.y(c);
-        if (y > CBS_LOW_VALUE) { cur += y / exp(r.off(c)); nonzero = true; }
+        if (y > CBS_LOW_VALUE) { cur += y / exp(r.off(c)); nz = 1; }
     }
+    if (LANES > 1) { cur = lane_sum<LANES>(cur, gm); nz = lane_max<LANES>(nz, gm); }
+    const bool nonzero = nz > 0;
     cur = log(cur / (double)(t1 - t0));
     if (!nonzero) return -INFINITY;
     for (int i = 0; i < maxit; ++i) {
         double dl = 0, info = 0;
-        for (int t = t0; t < t1; ++t) {
+        for (int t = t0 + ln; t < t1; t += LANES) {
             const int c = d.col[t];
             const double mu = exp(cur + r.off(c)), den = 1 + mu * r.phi(c);
             dl += (r.y(c) - mu) / den;
             info += mu / den;
         }
+        if (LANES > 1) { dl = lane_sum<LANES>(dl, gm); info = lane_sum<LANES>(info, gm); }
         const double step = dl / info;
         cur += step;
         if (fabs(step) < tol) break;
@@ -110,12 +135,14 @@ __device__ __forceinline__ double lin_pred(const DesignDev& d, const Row& r, int
 }
 
 // One sweep over the samples at coefficients beta: deviance, X'WX (packed lower) and X'z.
-__device__ inline double lev_sweep(const DesignDev& d, const Row& r, const double* beta, double* xtwx, double* dl) {
+template <int LANES = 1>
+__device__ inline double lev_sweep(const DesignDev& d, const Row& r, const double* beta, double* xtwx, double* dl,
+                                   int ln = 0, unsigned gm = 0xffffffffu) {
     const int p = d.p;
     for (int i = 0; i < p * (p + 1) / 2; ++i) xtwx[i] = 0;
     for (int i = 0; i < p; ++i) dl[i] = 0;
     double dev = 0;
-    for (int t = 0; t < d.n; ++t) {
+    for (int t = ln; t < d.n; t += LANES) {
         const int c = d.col[t];
         const double mu = exp(lin_pred(d, r, t, beta)), y = r.y(c), phi = r.phi(c);
         dev += unit_nb_deviance(y, mu, phi);
@@ -126,6 +153,11 @@ __device__ inline double lev_sweep(const DesignDev& d, const Row& r, const doubl
             dl[ik] += vk * z;
             for (int k2 = d.rowptr[t]; k2 <= k; ++k2) xtwx[tri(ik, d.cidx[k2])] += vk * d.cval[k2] * W;
         }
+    }
+    if (LANES > 1) {
+        for (int i = 0; i < p * (p + 1) / 2; ++i) xtwx[i] = lane_sum<LANES>(xtwx[i], gm);
+        for (int i = 0; i < p; ++i) dl[i] = lane_sum<LANES>(dl[i], gm);
+        dev = lane_sum<LANES>(dev, gm);
     }
     return dev;
 }
@@ -152,11 +184,14 @@ __device__ inline void chol_solve_packed(const double* a, int p, double* b) {
 }
 
 // edgeR glm_levenberg::fit with the "null" start.  beta (out, p).  Returns false when y is all zero (beta = NaN, mu = 0).
-__device__ inline bool fit_levenberg(const DesignDev& d, const Row& r, double* beta, int maxit = 250, double tolerance = 1e-6) {
+template <int LANES = 1, int PM = PMAX>
+__device__ inline bool fit_levenberg(const DesignDev& d, const Row& r, double* beta, int ln = 0, unsigned gm = 0xffffffffu,
+                                     int maxit = 250, double tolerance = 1e-6) {
+    constexpr int PT = PM * (PM + 1) / 2;
     const int p = d.p, pt = p * (p + 1) / 2;
-    double xtwx[PTRI], xtwx_new[PTRI], work[PTRI], dl[PMAX], dl_new[PMAX], dbeta[PMAX], beta_new[PMAX];
+    double xtwx[PT], xtwx_new[PT], work[PT], dl[PM], dl_new[PM], dbeta[PM], beta_new[PM];
     double ymax = 0, sum_exprs = 0, sum_weight = 0;
-    for (int t = 0; t < d.n; ++t) {
+    for (int t = ln; t < d.n; t += LANES) {
         const int c = d.col[t];
         const double y = r.y(c);
         if (y > ymax) ymax = y;
@@ -164,10 +199,11 @@ __device__ inline bool fit_levenberg(const DesignDev& d, const Row& r, double* b
         sum_exprs += y * w / curN;
         sum_weight += w;
     }
+    if (LANES > 1) { ymax = lane_max<LANES>(ymax, gm); sum_exprs = lane_sum<LANES>(sum_exprs, gm); sum_weight = lane_sum<LANES>(sum_weight, gm); }
     if (ymax < CBS_LOW_VALUE) { for (int i = 0; i < p; ++i) beta[i] = nan(""); return false; }
     const double c0 = log(sum_exprs / sum_weight);
     for (int i = 0; i < p; ++i) beta[i] = d.start[i] * c0;
-    double dev = lev_sweep(d, r, beta, xtwx, dl);
+    double dev = lev_sweep<LANES>(d, r, beta, xtwx, dl, ln, gm);
     double max_info = -1, lambda = 0;
     int iter = 0;
     while ((++iter) <= maxit) {
@@ -185,7 +221,7 @@ __device__ inline bool fit_levenberg(const DesignDev& d, const Row& r, double* b
             } while (1);
             chol_solve_packed(work, p, dbeta);
             for (int i = 0; i < p; ++i) beta_new[i] = beta[i] + dbeta[i];
-            const double dev_new = lev_sweep(d, r, beta_new, xtwx_new, dl_new);
+            const double dev_new = lev_sweep<LANES>(d, r, beta_new, xtwx_new, dl_new, ln, gm);
             if (dev_new / ymax < CBS_SUPREMELY_LOW) low_dev = true;
             if (dev_new <= dev || low_dev) {
                 for (int i = 0; i < p; ++i) beta[i] = beta_new[i];
@@ -209,10 +245,12 @@ __device__ inline bool fit_levenberg(const DesignDev& d, const Row& r, double* b
 
 // glmFit.default's plain fit of one gene: coefficients beta[p]; cellbeta[p] additionally for one-way designs.
 // Returns the mode used so that the caller can form fitted values with fitted_at().
-__device__ inline void fit_gene(const DesignDev& d, const Row& r, double* beta, double* cellbeta) {
+template <int LANES = 1, int PM = PMAX>
+__device__ inline void fit_gene(const DesignDev& d, const Row& r, double* beta, double* cellbeta, int ln = 0,
+                                unsigned gm = 0xffffffffu) {
     if (d.oneway) {
         for (int l = 0; l < d.p; ++l) {
-            const double b = fit_one_group(d, r, d.cell_start[l], d.cell_start[l + 1], 50, 1e-10);
+            const double b = fit_one_group<LANES>(d, r, d.cell_start[l], d.cell_start[l + 1], 50, 1e-10, ln, gm);
             cellbeta[l] = fmax(b, -1e8);                        // mglmOneWay: pmax(beta, -1e8)
         }
         for (int k = 0; k < d.p; ++k) {
@@ -221,7 +259,7 @@ __device__ inline void fit_gene(const DesignDev& d, const Row& r, double* beta, 
             beta[k] = s;
         }
     } else {
-        fit_levenberg(d, r, beta);
+        fit_levenberg<LANES, PM>(d, r, beta, ln, gm);
     }
 }
 

@@ -162,6 +162,51 @@ k_glm_fit(const int32_t* __restrict__ cnt, long G, long g0, long g1, const doubl
     }
 }
 
+// Same contract as k_glm_fit with GLM_LANES consecutive lanes per gene (glm.cuh "lane groups"): the sweeps over the
+// samples are split over the lanes, so a 60k-gene x 1000-sample fit exposes 480k threads instead of 60k and the
+// per-thread dependent chain is 125 samples per sweep instead of 1000.  A warp holds 32 / GLM_LANES consecutive genes:
+// each load instruction touches GLM_LANES columns x (32 / GLM_LANES) consecutive rows of the column-major matrices.
+// Used for designs with p <= GLM_LANES_PMAX columns (packed X'WX of 136 doubles per thread in local memory).
+constexpr int GLM_LANES = 8;
+constexpr int GLM_LANES_PMAX = 16;
+__global__ void __launch_bounds__(128)
+k_glm_fit_lanes(const int32_t* __restrict__ cnt, long G, long g0, long g1, const double* __restrict__ logoff,
+                const double* __restrict__ yadd, double two_prior_over_meanlib, const double* __restrict__ phi,
+                const int* __restrict__ phi_col, const DesignDev* __restrict__ design, const double* __restrict__ goff_in,
+                int mode, double* __restrict__ coef, double* __restrict__ fitted, const double* __restrict__ alpha_w,
+                int n_alpha, double* __restrict__ alpha_out) {
+    const long slot = ((long)blockIdx.x * blockDim.x + threadIdx.x) / GLM_LANES;
+    const long g = g0 + slot;
+    const int ln = threadIdx.x % GLM_LANES;
+    if (g >= g1) return;                                    // whole groups leave together
+    const unsigned gm = ((1u << GLM_LANES) - 1u) << ((threadIdx.x & 31) - ln);
+    const DesignDev d = *design;
+    double goff = goff_in ? goff_in[g] : 0.0;
+    if (mode == 1) goff = log(exp(goff) + two_prior_over_meanlib);
+    RowSrc src{cnt, G, logoff, mode == 1 ? yadd : nullptr, phi, phi_col, 0.0};
+    Row r(src, g, goff);
+    double beta[GLM_LANES_PMAX], cellbeta[GLM_LANES_PMAX];
+    fit_gene<GLM_LANES, GLM_LANES_PMAX>(d, r, beta, cellbeta, ln, gm);
+    if (coef) for (int k = ln; k < d.p; k += GLM_LANES) coef[g + (long)k * G] = beta[k];
+    if (alpha_out && ln == 0) {
+        double a = 0;
+        for (int b = 0; b < n_alpha; ++b) a += beta[b] * alpha_w[b];
+        alpha_out[g] = a;
+    }
+    if (fitted) {
+        if (d.oneway) {
+            for (int l = 0; l < d.p; ++l)
+                for (int t = d.cell_start[l] + ln; t < d.cell_start[l + 1]; t += GLM_LANES) {
+                    const int c = d.col[t];
+                    fitted[g + (long)c * G] = exp(cellbeta[l] + r.off(c));
+                }
+        } else {
+            const bool dead = isnan(beta[0]);
+            for (int t = ln; t < d.n; t += GLM_LANES) fitted[g + (long)d.col[t] * G] = dead ? 0.0 : exp(lin_pred(d, r, t, beta));
+        }
+    }
+}
+
 // ---- a12/a13: batch-free parameters + match_quantiles (helper_seq.R:46-64), one thread per element -------
 __global__ void k_phi_star_mean(const double* __restrict__ phi_star_mat, long G, int B, double* __restrict__ phi_star) {
     const long g = (long)blockIdx.x * blockDim.x + threadIdx.x;

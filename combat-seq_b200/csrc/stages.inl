@@ -117,7 +117,7 @@ static void run_tagwise_disp(const int32_t* cnt, long G, long g0, long g1, const
 // = sum_b alpha_w[b] * coef[g,b].  d_lib is the per-sample library size on the device (N); h_lib the host copy.
 static void run_glm_fit(const int32_t* cnt, long G, long g0, long g1, int N, const double* d_logoff,
                         const std::vector<double>& h_lib, const double* d_phi, const int* d_phi_col,
-                        const DesignDev* d_design, const double* d_goff, double prior_count, double* d_coef,
+                        const DesignDev* d_design, int h_p, const double* d_goff, double prior_count, double* d_coef,
                         double* d_fitted, const double* d_alpha_w, int n_alpha, double* d_alpha, cudaStream_t st) {
     if (g1 <= g0) return;
     const dim3 grid = grid1(g1 - g0, 128);
@@ -132,13 +132,21 @@ static void run_glm_fit(const int32_t* cnt, long G, long g0, long g1, int N, con
         d_yadd = upload(g_dev, "glm_yadd", yadd.data(), (size_t)N, st);
         two_prior = 2 * prior_count / meanlib;
     }
+    // designs with few columns go to the lane-group kernel (GLM_LANES lanes per gene); wider ones stay one thread per gene
+    const bool lanes = h_p <= GLM_LANES_PMAX;
+    const dim3 lgrid = grid1((g1 - g0) * GLM_LANES, 128);
+    auto launch = [&](const double* yadd, double tp, int mode, double* coef, double* fitted, double* alpha) {
+        if (lanes)
+            CBS_LAUNCH(k_glm_fit_lanes, lgrid, 128, 0, st, cnt, G, g0, g1, d_logoff, yadd, tp, d_phi, d_phi_col, d_design,
+                       d_goff, mode, coef, fitted, d_alpha_w, n_alpha, alpha);
+        else
+            CBS_LAUNCH(k_glm_fit, grid, 128, 0, st, cnt, G, g0, g1, d_logoff, yadd, tp, d_phi, d_phi_col, d_design,
+                       d_goff, mode, coef, fitted, d_alpha_w, n_alpha, alpha);
+    };
     if (d_fitted || (prior_count <= 0 && (d_coef || d_alpha)))
-        CBS_LAUNCH(k_glm_fit, grid, 128, 0, st, cnt, G, g0, g1, d_logoff, (const double*)nullptr, 0.0, d_phi, d_phi_col,
-                   d_design, d_goff, 0, prior_count > 0 ? (double*)nullptr : d_coef, d_fitted, d_alpha_w, n_alpha,
-                   prior_count > 0 ? (double*)nullptr : d_alpha);
+        launch(nullptr, 0.0, 0, prior_count > 0 ? (double*)nullptr : d_coef, d_fitted, prior_count > 0 ? (double*)nullptr : d_alpha);
     if (prior_count > 0 && (d_coef || d_alpha))
-        CBS_LAUNCH(k_glm_fit, grid, 128, 0, st, cnt, G, g0, g1, d_logoff, d_yadd, two_prior, d_phi, d_phi_col, d_design,
-                   d_goff, 1, d_coef, (double*)nullptr, d_alpha_w, n_alpha, d_alpha);
+        launch(d_yadd, two_prior, 1, d_coef, (double*)nullptr, d_alpha);
 }
 
 // number of Chebyshev terms for the range h = (uhi - ulo)/2 of u = log(r + c): the series of lgamma(x + e^u - c)
