@@ -225,36 +225,55 @@ __device__ __forceinline__ void mbar_arrive(uint64_t* bar) {
     asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(smem_u32(bar)) : "memory");
 }
 
-// exp(x) for x <= ~0.5 down to the underflow threshold (x < -745.14 gives 0; results in the denormal range are
-// rounded once, like the libm exp): x = k ln2 + r, |r| <= ln2/2, degree-12 Taylor polynomial evaluated with Estrin's
-// scheme (dependency depth 4 instead of 12, so that several independent calls overlap on the FP64 pipe), scaled by
-// 2^k in two normal-range factors.  Relative error < 4e-16.  Garbage (not a trap) for x = -inf / NaN: callers mask.
-__device__ __forceinline__ double mcg_exp(double x) {
-    const double kd = fma(x, 1.4426950408889634, 6755399441055744.0);           // 1.5 * 2^52: round to nearest integer
-    const int k = __double2loint(kd);
-    const double kf = kd - 6755399441055744.0;
-    double r = fma(kf, -6.93147180369123816490e-01, x);
-    r = fma(kf, -1.90821492927058770002e-10, r);
-    const double r2 = r * r, r4 = r2 * r2, r8 = r4 * r4;
-    const double a0 = 1.0 + r;
-    const double a1 = fma(r, 1.0 / 6, 0.5);
-    const double a2 = fma(r, 1.0 / 120, 1.0 / 24);
-    const double a3 = fma(r, 1.0 / 5040, 1.0 / 720);
-    const double a4 = fma(r, 1.0 / 362880, 1.0 / 40320);
-    const double a5 = fma(r, 1.0 / 39916800, 1.0 / 3628800);
-    const double b0 = fma(a1, r2, a0), b1 = fma(a3, r2, a2), b2 = fma(a5, r2, a4);
-    const double d0 = fma(b1, r4, b0), d1 = fma(1.0 / 479001600, r4, b2);
-    const double p = fma(d1, r8, d0);
-    const int k1 = k >> 1, k2 = k - k1;
-    const double s1 = __hiloint2double((k1 + 1023) << 20, 0), s2 = __hiloint2double((k2 + 1023) << 20, 0);
-    return (p * s1) * s2;
+// 2^(j/64), j = 0..63, correctly rounded (mpmath); copied to shared memory by every CTA of k_mc_gemm
+__device__ __constant__ double c_exp2_64[64] = {
+    1, 1.0108892860517005, 1.0218971486541166, 1.0330248790212284,
+    1.0442737824274138, 1.0556451783605572, 1.0671404006768237, 1.0787607977571199,
+    1.0905077326652577, 1.1023825833078409, 1.1143867425958924, 1.1265216186082418,
+    1.1387886347566916, 1.1511892299529827, 1.1637248587775775, 1.1763969916502812,
+    1.189207115002721, 1.2021567314527031, 1.215247359980469, 1.22848053610687,
+    1.241857812073484, 1.2553807570246911, 1.2690509571917332, 1.2828700160787783,
+    1.2968395546510096, 1.3109612115247644, 1.3252366431597413, 1.3396675240533029,
+    1.3542555469368927, 1.3690024229745905, 1.383909881963832, 1.3989796725383112,
+    1.4142135623730951, 1.42961333839197, 1.4451808069770467, 1.460917794180647,
+    1.4768261459394993, 1.4929077282912648, 1.5091644275934228, 1.5255981507445384,
+    1.5422108254079407, 1.5590044002378369, 1.5759808451078865, 1.593142151342267,
+    1.6104903319492543, 1.6280274218573478, 1.6457554781539649, 1.6636765803267364,
+    1.681792830507429, 1.7001063537185235, 1.7186192981224779, 1.7373338352737062,
+    1.7562521603732995, 1.7753764925265212, 1.7947090750031072, 1.8142521755003989,
+    1.8340080864093424, 1.8539791250833855, 1.8741676341103, 1.8945759815869656,
+    1.9152065613971474, 1.9360617934922943, 1.9571441241754002, 1.9784560263879509
+};
+
+// exp(x) for x <= ~0.5 down to the underflow threshold (x < -745.14 gives 0; results in the denormal range are rounded
+// once, like the libm exp).  DMMA and DFMA share the FP64 units on B200 (tools/dmma_bench.cu, "mix"), so every FP64
+// instruction of the epilogue is taken from the contraction: x = (64 k + j) ln2/64 + r with |r| <= ln2/128, exp(x) =
+// 2^k * T[j] * (1 + p(r)) with a 64-entry table in shared memory and a degree-5 polynomial: 11 FP64 instructions,
+// the 2^k scaling is an integer add on the exponent field (plus one multiply that is 1.0 unless the result is
+// subnormal).  Relative error < 3e-16.  Garbage (not a trap, no out-of-range table index) for x = -inf / NaN: callers mask.
+__device__ __forceinline__ double mcg_exp(double x, const double* __restrict__ T) {
+    const double t = fma(x, 92.33248261689366, 6755399441055744.0);            // 64/ln2; 1.5 * 2^52 rounds to an integer
+    const int n = __double2loint(t);
+    const double nf = t - 6755399441055744.0;
+    double r = fma(nf, -0.010830424696249145, x);                              // ln2/64 = hi + lo
+    r = fma(nf, -3.623510646634843e-19, r);
+    double q = fma(r, 1.0 / 120, 1.0 / 24);
+    q = fma(q, r, 1.0 / 6);
+    q = fma(q, r, 0.5);
+    const double p = fma(q, r * r, r);
+    const double Tj = T[n & 63];
+    const double v = fma(Tj, p, Tj);
+    const int k = n >> 6, k1 = max(k, -1000);
+    const double vs = __hiloint2double(__double2hiint(v) + (k1 << 20), __double2loint(v));
+    return vs * __hiloint2double((k - k1 + 1023) << 20, 0);
 }
 
 constexpr int MCG_CONSUMER_WARPS = 8;
 constexpr int MCG_BLOCK = MCG_CONSUMER_WARPS * 32;
 constexpr size_t MCG_SMEM_STAGE = (size_t)MCG_SUB * 2 * MCG_TILE * MCG_KC * sizeof(double);       // SUB x (P + Q chunk)
 constexpr size_t MCG_SMEM_GP = (size_t)MCG_GPBUF * MCG_TILE * 2 * sizeof(double);
-constexpr size_t MCG_SMEM_BYTES = MCG_STAGES * MCG_SMEM_STAGE + MCG_SMEM_GP + 2 * MCG_STAGES * sizeof(uint64_t) + 64;   // full[] + done[]
+constexpr size_t MCG_SMEM_BYTES = MCG_STAGES * MCG_SMEM_STAGE + MCG_SMEM_GP + 2 * MCG_STAGES * sizeof(uint64_t) + 64   // full[] + done[]
+                                  + 64 * sizeof(double);                                                                 // exp2 table
 static_assert(MCG_THREADS == MCG_CONSUMER_WARPS * 32, "consumer thread count");
 
 // One CTA = one 128-target tile x one split of the source tiles.  Eight MMA warps, arranged 4 (targets) x 2
@@ -273,6 +292,8 @@ k_mc_gemm(const double* __restrict__ P, const double* __restrict__ Q, const doub
     double2* gp_s = reinterpret_cast<double2*>(smem_raw + MCG_STAGES * MCG_SMEM_STAGE);
     uint64_t* full = reinterpret_cast<uint64_t*>(smem_raw + MCG_STAGES * MCG_SMEM_STAGE + MCG_SMEM_GP);
     unsigned int* done = reinterpret_cast<unsigned int*>(full + MCG_STAGES);    // warps that have left each stage
+    double* exp_tab = reinterpret_cast<double*>(smem_raw + MCG_STAGES * MCG_SMEM_STAGE + MCG_SMEM_GP + 2 * MCG_STAGES * sizeof(uint64_t) + 64);
+    if (threadIdx.x < 64) exp_tab[threadIdx.x] = c_exp2_64[threadIdx.x];
 
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     const int wi = warp & 3, wj = (warp >> 2) & 1;
@@ -404,7 +425,7 @@ k_mc_gemm(const double* __restrict__ P, const double* __restrict__ Q, const doub
 #pragma unroll
                         for (int mt = 0; mt < 4; ++mt) {
                             const double L0 = acc[mt][nt][0], L1 = acc[mt][nt][1];
-                            const double e0 = mcg_exp(STABLE ? L0 - racc[mt].m : L0), e1 = mcg_exp(STABLE ? L1 - racc[mt].m : L1);
+                            const double e0 = mcg_exp(STABLE ? L0 - racc[mt].m : L0, exp_tab), e1 = mcg_exp(STABLE ? L1 - racc[mt].m : L1, exp_tab);
                             w0[mt] = (L0 > thr[mt]) ? e0 : 0.0;
                             w1[mt] = (L1 > thr[mt]) ? e1 : 0.0;
                         }

@@ -39,7 +39,7 @@ static void apl_sums(const double* d_apl, long G, long g0, long g1, const unsign
     double* d_part = g_dev.get<double>("apl_partial", nj * nchunk);
     CBS_CUDA(cudaMemsetAsync(d_part, 0, nj * nchunk * sizeof(double), st));
     const long c0 = g0 / APL_CHUNK, c1 = (g1 + APL_CHUNK - 1) / APL_CHUNK;
-    if (c1 > c0)
+    if (g1 > g0)                              // a rank without genes contributes exact zeros (its g0 == G need not be chunk-aligned)
         for (size_t e0 = 0; e0 < nj; e0 += APL_MAX_EVALS) {
             AplLaunch L;
             L.n_evals = (int)std::min<size_t>(APL_MAX_EVALS, nj - e0);
