@@ -40,7 +40,8 @@ constexpr int MCG_STAGES = 5;
 constexpr int MCG_GPBUF = 4;         // buffers of the per-source-tile (gamma, phi) pairs
 constexpr int MCG_MAX_KC = 64;       // max Chebyshev terms
 constexpr int MCG_SHIFT = 4;         // c: counts below c use the one-hot table
-constexpr int MCG_THREADS = 256;
+constexpr int MCG_MT = 2;            // 8-row DMMA tiles per warp along the targets (warp tile = 8*MCG_MT x 64)
+constexpr int MCG_THREADS = 32 * (MCG_TILE / (8 * MCG_MT)) * 2;   // warps: (128 / warp rows) x 2
 
 struct McgShape {
     int n;          // samples in the batch
@@ -268,7 +269,8 @@ __device__ __forceinline__ double mcg_exp(double x, const double* __restrict__ T
     return vs * __hiloint2double((k - k1 + 1023) << 20, 0);
 }
 
-constexpr int MCG_CONSUMER_WARPS = 8;
+constexpr int MCG_CONSUMER_WARPS = MCG_THREADS / 32;
+constexpr int MCG_WI = MCG_CONSUMER_WARPS / 2;      // warps along the targets
 constexpr int MCG_BLOCK = MCG_CONSUMER_WARPS * 32;
 constexpr size_t MCG_SMEM_STAGE = (size_t)MCG_SUB * 2 * MCG_TILE * MCG_KC * sizeof(double);       // SUB x (P + Q chunk)
 constexpr size_t MCG_SMEM_GP = (size_t)MCG_GPBUF * MCG_TILE * 2 * sizeof(double);
@@ -276,8 +278,8 @@ constexpr size_t MCG_SMEM_BYTES = MCG_STAGES * MCG_SMEM_STAGE + MCG_SMEM_GP + 2 
                                   + 64 * sizeof(double);                                                                 // exp2 table
 static_assert(MCG_THREADS == MCG_CONSUMER_WARPS * 32, "consumer thread count");
 
-// One CTA = one 128-target tile x one split of the source tiles.  Eight MMA warps, arranged 4 (targets) x 2
-// (sources), warp tile 32 x 64 = 4 x 8 DMMA tiles.  The k-chunks stream through a ring of MCG_STAGES stages filled
+// One CTA = one 128-target tile x one split of the source tiles.  Sixteen MMA warps, arranged 8 (targets) x 2
+// (sources), warp tile 16 x 64 = 2 x 8 DMMA tiles (64 accumulator registers, 128 registers per thread, 4 warps per scheduler).  The k-chunks stream through a ring of MCG_STAGES stages filled
 // by TMA bulk copies that complete on a `full` mbarrier per stage.  There is no producer thread and no CTA-wide
 // barrier in the main loop: every warp counts itself out of a stage (shared-memory atomic), and the LAST warp to
 // leave a stage issues the copies that refill it.  A warp that is folding the weights of a finished source tile
@@ -296,7 +298,7 @@ k_mc_gemm(const double* __restrict__ P, const double* __restrict__ Q, const doub
     if (threadIdx.x < 64) exp_tab[threadIdx.x] = c_exp2_64[threadIdx.x];
 
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
-    const int wi = warp & 3, wj = (warp >> 2) & 1;
+    const int wi = warp % MCG_WI, wj = warp / MCG_WI;
     const long itile = tile0 + blockIdx.x;
     const long NJ = sh.rows / MCG_TILE;
     const long jt0 = NJ * blockIdx.y / gridDim.y, jt1 = NJ * (blockIdx.y + 1) / gridDim.y;
@@ -330,21 +332,21 @@ k_mc_gemm(const double* __restrict__ P, const double* __restrict__ Q, const doub
     if (tid == 0)
         for (long c = 0; c < total && c < MCG_STAGES; ++c) issue(c);
 
-    McAcc racc[4];
+    McAcc racc[MCG_MT];
 #pragma unroll
-    for (int mt = 0; mt < 4; ++mt) { racc[mt].m = -INFINITY; racc[mt].sw = racc[mt].sg = racc[mt].sp = 0.0; }
+    for (int mt = 0; mt < MCG_MT; ++mt) { racc[mt].m = -INFINITY; racc[mt].sw = racc[mt].sg = racc[mt].sp = 0.0; }
     const int frow = lane >> 2, fcol = lane & 3;
 
     {
         // ---- MMA warps ----
-        double acc[4][8][2];
+        double acc[MCG_MT][8][2];
 #pragma unroll
-        for (int mt = 0; mt < 4; ++mt)
+        for (int mt = 0; mt < MCG_MT; ++mt)
 #pragma unroll
             for (int nt = 0; nt < 8; ++nt) acc[mt][nt][0] = acc[mt][nt][1] = 0.0;
         // fragment addressing: row = lane/4 within an 8-row MMA tile, column = lane%4 within a 4-wide k-step
         const int swz = ((frow >> 1) & 1) << 2;             // tile bases are multiples of 8, so bit 1 of the row is frow's
-        const int a_off = (wi * 32 + frow) * MCG_KC, b_off = (wj * 64 + frow) * MCG_KC;
+        const int a_off = (wi * (8 * MCG_MT) + frow) * MCG_KC, b_off = (wj * 64 + frow) * MCG_KC;
         long jl = 0; int kc = 0;
         int st = 0; uint32_t phase = 0;
         for (long it = 0; it < total; ++it) {
@@ -356,13 +358,13 @@ k_mc_gemm(const double* __restrict__ P, const double* __restrict__ Q, const doub
 #pragma unroll
             for (int ks = 0; ks < 2; ++ks) {
                 const int col = (ks * 4 + fcol) ^ swz;
-                double a[4], b[8];
+                double a[MCG_MT], b[8];
 #pragma unroll
-                for (int mt = 0; mt < 4; ++mt) a[mt] = ps[a_off + mt * 8 * MCG_KC + col];
+                for (int mt = 0; mt < MCG_MT; ++mt) a[mt] = ps[a_off + mt * 8 * MCG_KC + col];
 #pragma unroll
                 for (int nt = 0; nt < 8; ++nt) b[nt] = qs[b_off + nt * 8 * MCG_KC + col];
 #pragma unroll
-                for (int mt = 0; mt < 4; ++mt)
+                for (int mt = 0; mt < MCG_MT; ++mt)
 #pragma unroll
                     for (int nt = 0; nt < 8; ++nt) dmma884(acc[mt][nt][0], acc[mt][nt][1], a[mt], b[nt]);
             }
@@ -383,17 +385,17 @@ k_mc_gemm(const double* __restrict__ P, const double* __restrict__ Q, const doub
                 const double2* g2 = gp_s + (jl % MCG_GPBUF) * MCG_TILE;
                 if (jt == itile) {                           // mu[-i,]: the gene itself is not a source  helper_seq.R:11-14
 #pragma unroll
-                    for (int mt = 0; mt < 4; ++mt)
+                    for (int mt = 0; mt < MCG_MT; ++mt)
 #pragma unroll
                         for (int nt = 0; nt < 8; ++nt)
 #pragma unroll
                             for (int e = 0; e < 2; ++e)
-                                if (wj * 64 + nt * 8 + 2 * fcol + e == wi * 32 + mt * 8 + frow) acc[mt][nt][e] = -INFINITY;
+                                if (wj * 64 + nt * 8 + 2 * fcol + e == wi * (8 * MCG_MT) + mt * 8 + frow) acc[mt][nt][e] = -INFINITY;
                 }
                 // running maximum of every target row (shared by the 4 lanes that hold the row) -> prune threshold
-                double thr[4];
+                double thr[MCG_MT];
 #pragma unroll
-                for (int mt = 0; mt < 4; ++mt) {
+                for (int mt = 0; mt < MCG_MT; ++mt) {
                     double mx = fmax(acc[mt][0][0], acc[mt][0][1]);
 #pragma unroll
                     for (int nt = 1; nt < 8; ++nt) mx = fmax(mx, fmax(acc[mt][nt][0], acc[mt][nt][1]));
@@ -418,26 +420,26 @@ k_mc_gemm(const double* __restrict__ P, const double* __restrict__ Q, const doub
                 for (int nt = 0; nt < 8; ++nt) {
                     bool need = false;
 #pragma unroll
-                    for (int mt = 0; mt < 4; ++mt) need |= (acc[mt][nt][0] > thr[mt]) | (acc[mt][nt][1] > thr[mt]);
+                    for (int mt = 0; mt < MCG_MT; ++mt) need |= (acc[mt][nt][0] > thr[mt]) | (acc[mt][nt][1] > thr[mt]);
                     if (__any_sync(0xffffffffu, need)) {
                         const double2 gp0 = g2[wj * 64 + nt * 8 + 2 * fcol], gp1 = g2[wj * 64 + nt * 8 + 2 * fcol + 1];
-                        double w0[4], w1[4];
+                        double w0[MCG_MT], w1[MCG_MT];
 #pragma unroll
-                        for (int mt = 0; mt < 4; ++mt) {
+                        for (int mt = 0; mt < MCG_MT; ++mt) {
                             const double L0 = acc[mt][nt][0], L1 = acc[mt][nt][1];
                             const double e0 = mcg_exp(STABLE ? L0 - racc[mt].m : L0, exp_tab), e1 = mcg_exp(STABLE ? L1 - racc[mt].m : L1, exp_tab);
                             w0[mt] = (L0 > thr[mt]) ? e0 : 0.0;
                             w1[mt] = (L1 > thr[mt]) ? e1 : 0.0;
                         }
 #pragma unroll
-                        for (int mt = 0; mt < 4; ++mt) {
+                        for (int mt = 0; mt < MCG_MT; ++mt) {
                             racc[mt].sw += w0[mt] + w1[mt];
                             racc[mt].sg = fma(w1[mt], gp1.x, fma(w0[mt], gp0.x, racc[mt].sg));
                             racc[mt].sp = fma(w1[mt], gp1.y, fma(w0[mt], gp0.y, racc[mt].sp));
                         }
                     }
 #pragma unroll
-                    for (int mt = 0; mt < 4; ++mt) acc[mt][nt][0] = acc[mt][nt][1] = 0.0;
+                    for (int mt = 0; mt < MCG_MT; ++mt) acc[mt][nt][0] = acc[mt][nt][1] = 0.0;
                 }
                 kc = 0; ++jl;
             }
@@ -448,10 +450,10 @@ k_mc_gemm(const double* __restrict__ P, const double* __restrict__ Q, const doub
     McAcc* red = reinterpret_cast<McAcc*>(smem_raw);        // [2][128], aliases the (now idle) stage buffers
     {
 #pragma unroll
-        for (int mt = 0; mt < 4; ++mt) {
+        for (int mt = 0; mt < MCG_MT; ++mt) {
             McAcc a = racc[mt];
             for (int o = 1; o <= 2; o <<= 1) { const McAcc b = mc_shfl_xor(a, o); mc_merge(a, b, STABLE); }
-            if (fcol == 0) red[wj * MCG_TILE + wi * 32 + mt * 8 + frow] = a;
+            if (fcol == 0) red[wj * MCG_TILE + wi * (8 * MCG_MT) + mt * 8 + frow] = a;
         }
     }
     __syncthreads();
