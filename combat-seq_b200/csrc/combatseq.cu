@@ -23,6 +23,7 @@ static PinCache g_pin;
 
 // ---- tuning knobs (cbs_set_tuning) ----------------------------------------------------------------------------
 static int g_mc_algo = 0;            // 0 = auto (tensor-core contraction when gene.subset.n is NULL), 1 = direct, 2 = contraction
+static int g_apl_fast = 1;           // 1 = lgamma(y+1) table + hoisted log(r)/lgamma(r) in the APL kernel (same bits), 0 = per-sample calls
 static double g_mc_tail_tol = 1e-8;  // largest accepted Chebyshev tail estimate (log-likelihood units)
 static double g_last_mc_tail = 0;    // diagnostics: largest tail estimate of the last Monte-Carlo stage
 static int g_last_mc_kc = 0;         // diagnostics: Chebyshev terms used by the last contraction launch

@@ -317,10 +317,17 @@ __device__ inline void sytf2_packed(double* a, int n) {
 }
 
 // edgeR adjustedProfileLik for one gene at the dispersion carried by `r`: fit, NB log-likelihood, Cox-Reid term.
-__device__ inline double apl_gene(const DesignDev& d, const Row& r) {
+// lgfact (optional): table of lgamma(y + 1), y = 0..LGFACT_N-1, filled on the device by the same lgamma() (k_lgfact_init),
+// so a lookup returns the bits the call would.  With one dispersion per evaluation (the only form the pipeline uses)
+// log(r) and lgamma(r) are loop invariants and are evaluated once per gene instead of once per sample.
+constexpr int LGFACT_N = 2048;
+__device__ inline double apl_gene(const DesignDev& d, const Row& r, const double* __restrict__ lgfact = nullptr) {
     double beta[PMAX], cellbeta[PMAX], wm[PTRI];
     const int p = d.p;
     fit_gene(d, r, beta, cellbeta);
+    const bool scalar_phi = lgfact != nullptr && (r.s.phi == nullptr) && r.s.phi_scalar > 0;
+    double rr_c = 0, logrr_c = 0, lgrr_c = 0;
+    if (scalar_phi) { rr_c = 1 / r.s.phi_scalar; logrr_c = log(rr_c); lgrr_c = lgamma(rr_c); }
     for (int i = 0; i < p * (p + 1) / 2; ++i) wm[i] = 0;
     double sum_loglik = 0, sumw = 0;
     int l = 0;
@@ -332,11 +339,13 @@ __device__ inline double apl_gene(const DesignDev& d, const Row& r) {
         if (mu == 0) continue;
         const double y = r.y(c), phi = r.phi(c);
         double loglik;
+        const double lgy1 = (lgfact && y < (double)LGFACT_N && !r.s.yadd) ? lgfact[(int)y] : lgamma(y + 1);
         if (phi > 0) {
-            const double rr = 1 / phi, logmur = log(mu + rr);
-            loglik = y * log(mu) - y * logmur + rr * log(rr) - rr * logmur + lgamma(y + rr) - lgamma(y + 1) - lgamma(rr);
+            const double rr = scalar_phi ? rr_c : 1 / phi, logmur = log(mu + rr);
+            const double logrr = scalar_phi ? logrr_c : log(rr), lgrr = scalar_phi ? lgrr_c : lgamma(rr);
+            loglik = y * log(mu) - y * logmur + rr * logrr - rr * logmur + lgamma(y + rr) - lgy1 - lgrr;
         } else {
-            loglik = y * log(mu) - mu - lgamma(y + 1);
+            loglik = y * log(mu) - mu - lgy1;
         }
         const double W = mu / (1 + phi * mu);
         sum_loglik += loglik;

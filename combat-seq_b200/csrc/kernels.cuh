@@ -69,7 +69,7 @@ struct AplLaunch {
 __global__ void __launch_bounds__(128)
 k_apl(const int32_t* __restrict__ cnt, long G, long g0, long g1, const double* __restrict__ logoff,
       const DesignDev* __restrict__ designs, const unsigned char* __restrict__ sel, const double* __restrict__ phi_gene,
-      AplLaunch L, double* __restrict__ apl) {
+      AplLaunch L, double* __restrict__ apl, const double* __restrict__ lgfact) {
     const long g = g0 + (long)blockIdx.x * blockDim.x + threadIdx.x;
     const int e = blockIdx.y;
     if (g >= g1) return;
@@ -78,7 +78,13 @@ k_apl(const int32_t* __restrict__ cnt, long G, long g0, long g1, const double* _
     const DesignDev d = designs[di];
     RowSrc src{cnt, G, logoff, nullptr, nullptr, nullptr, phi_gene ? phi_gene[(long)e * G + g] : L.phi[e]};
     Row r(src, g, 0.0);
-    apl[(long)e * G + g] = apl_gene(d, r);
+    apl[(long)e * G + g] = apl_gene(d, r, lgfact);
+}
+
+// lgamma(y + 1) for y = 0..LGFACT_N-1 by the device lgamma() itself (see apl_gene)
+__global__ void k_lgfact_init(double* __restrict__ tab) {
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i < LGFACT_N) tab[i] = lgamma((double)i + 1.0);
 }
 
 // deterministic chunked sums: partial[e*nchunk + chunk] = sum of apl[e*G + g] over the selected genes of the chunk

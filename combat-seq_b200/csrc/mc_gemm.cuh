@@ -33,15 +33,16 @@
 
 namespace cbs {
 
-constexpr int MCG_TILE = 128;        // CTA tile: 128 targets x 128 sources
+constexpr int MCG_TILE = 128;        // source tile (and the row block of the P/Q layout): 128 genes
+constexpr int MCG_TI = 64;           // target rows per CTA: CTA tile = 64 targets x 128 sources, two CTAs per SM
 constexpr int MCG_KC = 8;            // k-chunk (doubles): the unit of the global layout and of one bulk copy
 constexpr int MCG_SUB = 2;           // k-chunks per pipeline stage (16 doubles of K per hand-over)
-constexpr int MCG_STAGES = 5;
+constexpr int MCG_STAGES = 4;
 constexpr int MCG_GPBUF = 4;         // buffers of the per-source-tile (gamma, phi) pairs
 constexpr int MCG_MAX_KC = 64;       // max Chebyshev terms
 constexpr int MCG_SHIFT = 4;         // c: counts below c use the one-hot table
 constexpr int MCG_MT = 2;            // 8-row DMMA tiles per warp along the targets (warp tile = 8*MCG_MT x 64)
-constexpr int MCG_THREADS = 32 * (MCG_TILE / (8 * MCG_MT)) * 2;   // warps: (128 / warp rows) x 2
+constexpr int MCG_THREADS = 32 * (MCG_TI / (8 * MCG_MT)) * 2;     // warps: (64 / warp rows) x 2 = 8
 
 struct McgShape {
     int n;          // samples in the batch
@@ -272,21 +273,23 @@ __device__ __forceinline__ double mcg_exp(double x, const double* __restrict__ T
 constexpr int MCG_CONSUMER_WARPS = MCG_THREADS / 32;
 constexpr int MCG_WI = MCG_CONSUMER_WARPS / 2;      // warps along the targets
 constexpr int MCG_BLOCK = MCG_CONSUMER_WARPS * 32;
-constexpr size_t MCG_SMEM_STAGE = (size_t)MCG_SUB * 2 * MCG_TILE * MCG_KC * sizeof(double);       // SUB x (P + Q chunk)
+constexpr int MCG_STAGE_DBL = MCG_SUB * (MCG_TI + MCG_TILE) * MCG_KC;                             // doubles per stage
+constexpr size_t MCG_SMEM_STAGE = (size_t)MCG_STAGE_DBL * sizeof(double);                         // SUB x (P chunk + Q chunk)
 constexpr size_t MCG_SMEM_GP = (size_t)MCG_GPBUF * MCG_TILE * 2 * sizeof(double);
 constexpr size_t MCG_SMEM_BYTES = MCG_STAGES * MCG_SMEM_STAGE + MCG_SMEM_GP + 2 * MCG_STAGES * sizeof(uint64_t) + 64   // full[] + done[]
                                   + 64 * sizeof(double);                                                                 // exp2 table
 static_assert(MCG_THREADS == MCG_CONSUMER_WARPS * 32, "consumer thread count");
 
-// One CTA = one 128-target tile x one split of the source tiles.  Sixteen MMA warps, arranged 8 (targets) x 2
-// (sources), warp tile 16 x 64 = 2 x 8 DMMA tiles (64 accumulator registers, 128 registers per thread, 4 warps per scheduler).  The k-chunks stream through a ring of MCG_STAGES stages filled
+// One CTA = one 64-target tile x one split of the source tiles.  Eight MMA warps, arranged 4 (targets) x 2 (sources),
+// warp tile 16 x 64 = 2 x 8 DMMA tiles (64 accumulator registers, 128 registers per thread); two CTAs share an SM, each
+// with its own stage ring, so a CTA that waits on its ring or folds weights leaves the FP64 units to the other one.  The k-chunks stream through a ring of MCG_STAGES stages filled
 // by TMA bulk copies that complete on a `full` mbarrier per stage.  There is no producer thread and no CTA-wide
 // barrier in the main loop: every warp counts itself out of a stage (shared-memory atomic), and the LAST warp to
 // leave a stage issues the copies that refill it.  A warp that is folding the weights of a finished source tile
 // (FP64 pipe) therefore never holds up the refills the other warps are waiting for, and the other warp of its
 // scheduler keeps the tensor pipe busy meanwhile.  part[(split*rows + i)] receives the partial sums of target row i.
 template <int STABLE>
-__global__ void __launch_bounds__(MCG_BLOCK, 1)
+__global__ void __launch_bounds__(MCG_BLOCK, 2)
 k_mc_gemm(const double* __restrict__ P, const double* __restrict__ Q, const double2* __restrict__ gp, McgShape sh,
           long tile0, McAcc* __restrict__ part) {
     extern __shared__ __align__(128) unsigned char smem_raw[];
@@ -315,14 +318,15 @@ k_mc_gemm(const double* __restrict__ P, const double* __restrict__ Q, const doub
     auto issue = [&](long c) {
         const int ns = (int)(c % MCG_STAGES);
         const long njl = c / NKS; const int nks = (int)(c - njl * NKS);
-        const uint32_t chunk_bytes = MCG_TILE * MCG_KC * sizeof(double);
-        double* sb = stage_base + (size_t)ns * (MCG_SUB * 2 * MCG_TILE * MCG_KC);
-        mbar_expect_tx(&full[ns], MCG_SUB * 2 * chunk_bytes + (nks == 0 ? (uint32_t)(MCG_TILE * sizeof(double2)) : 0u));
+        const uint32_t p_bytes = MCG_TI * MCG_KC * sizeof(double), q_bytes = MCG_TILE * MCG_KC * sizeof(double);
+        double* sb = stage_base + (size_t)ns * MCG_STAGE_DBL;
+        mbar_expect_tx(&full[ns], MCG_SUB * (p_bytes + q_bytes) + (nks == 0 ? (uint32_t)(MCG_TILE * sizeof(double2)) : 0u));
 #pragma unroll
         for (int u = 0; u < MCG_SUB; ++u) {
             const size_t kc = (size_t)nks * MCG_SUB + u;
-            bulk_g2s(sb + (2 * u) * MCG_TILE * MCG_KC, P + (kc * sh.rows + itile * MCG_TILE) * MCG_KC, chunk_bytes, &full[ns]);
-            bulk_g2s(sb + (2 * u + 1) * MCG_TILE * MCG_KC, Q + (kc * sh.rows + (jt0 + njl) * MCG_TILE) * MCG_KC, chunk_bytes, &full[ns]);
+            double* su = sb + u * (MCG_TI + MCG_TILE) * MCG_KC;
+            bulk_g2s(su, P + (kc * sh.rows + itile * MCG_TI) * MCG_KC, p_bytes, &full[ns]);
+            bulk_g2s(su + MCG_TI * MCG_KC, Q + (kc * sh.rows + (jt0 + njl) * MCG_TILE) * MCG_KC, q_bytes, &full[ns]);
         }
         // gamma/phi of source tile njl go to buffer njl % MCG_GPBUF, last read in the epilogue of tile njl - MCG_GPBUF,
         // which every warp has finished before it leaves hand-over njl * NKS - MCG_STAGES
@@ -353,8 +357,8 @@ k_mc_gemm(const double* __restrict__ P, const double* __restrict__ Q, const doub
             mbar_wait(&full[st], phase);
 #pragma unroll
             for (int u = 0; u < MCG_SUB; ++u) {
-            const double* ps = stage_base + (size_t)st * (MCG_SUB * 2 * MCG_TILE * MCG_KC) + (2 * u) * MCG_TILE * MCG_KC;
-            const double* qs = ps + MCG_TILE * MCG_KC;
+            const double* ps = stage_base + (size_t)st * MCG_STAGE_DBL + u * (MCG_TI + MCG_TILE) * MCG_KC;
+            const double* qs = ps + MCG_TI * MCG_KC;
 #pragma unroll
             for (int ks = 0; ks < 2; ++ks) {
                 const int col = (ks * 4 + fcol) ^ swz;
@@ -383,14 +387,15 @@ k_mc_gemm(const double* __restrict__ P, const double* __restrict__ Q, const doub
             if (++kc == NKS) {                               // last k-chunk of source tile jl: fold the weights in
                 const long jt = jt0 + jl;
                 const double2* g2 = gp_s + (jl % MCG_GPBUF) * MCG_TILE;
-                if (jt == itile) {                           // mu[-i,]: the gene itself is not a source  helper_seq.R:11-14
+                if (jt == (itile * MCG_TI) / MCG_TILE) {     // mu[-i,]: the gene itself is not a source  helper_seq.R:11-14
+                    const int ioff = (int)((itile * MCG_TI) % MCG_TILE);
 #pragma unroll
                     for (int mt = 0; mt < MCG_MT; ++mt)
 #pragma unroll
                         for (int nt = 0; nt < 8; ++nt)
 #pragma unroll
                             for (int e = 0; e < 2; ++e)
-                                if (wj * 64 + nt * 8 + 2 * fcol + e == wi * (8 * MCG_MT) + mt * 8 + frow) acc[mt][nt][e] = -INFINITY;
+                                if (wj * 64 + nt * 8 + 2 * fcol + e == ioff + wi * (8 * MCG_MT) + mt * 8 + frow) acc[mt][nt][e] = -INFINITY;
                 }
                 // running maximum of every target row (shared by the 4 lanes that hold the row) -> prune threshold
                 double thr[MCG_MT];
@@ -447,20 +452,20 @@ k_mc_gemm(const double* __restrict__ P, const double* __restrict__ Q, const doub
     }
     // reduce over the 4 lanes that share a row, then over the two source-side warps
     __syncthreads();
-    McAcc* red = reinterpret_cast<McAcc*>(smem_raw);        // [2][128], aliases the (now idle) stage buffers
+    McAcc* red = reinterpret_cast<McAcc*>(smem_raw);        // [2][MCG_TI], aliases the (now idle) stage buffers
     {
 #pragma unroll
         for (int mt = 0; mt < MCG_MT; ++mt) {
             McAcc a = racc[mt];
             for (int o = 1; o <= 2; o <<= 1) { const McAcc b = mc_shfl_xor(a, o); mc_merge(a, b, STABLE); }
-            if (fcol == 0) red[wj * MCG_TILE + wi * (8 * MCG_MT) + mt * 8 + frow] = a;
+            if (fcol == 0) red[wj * MCG_TI + wi * (8 * MCG_MT) + mt * 8 + frow] = a;
         }
     }
     __syncthreads();
-    if (tid < MCG_TILE) {
+    if (tid < MCG_TI) {
         McAcc a = red[tid];
-        mc_merge(a, red[MCG_TILE + tid], STABLE);
-        part[(size_t)blockIdx.y * sh.rows + itile * MCG_TILE + tid] = a;
+        mc_merge(a, red[MCG_TI + tid], STABLE);
+        part[(size_t)blockIdx.y * sh.rows + itile * MCG_TI + tid] = a;
     }
 }
 

@@ -19,13 +19,15 @@ static void launch_apl(const int32_t* cnt, long G, long g0, long g1, const doubl
                        const unsigned char* sel, const double* phi_gene, const std::vector<AplJob>& jobs, double* d_apl,
                        cudaStream_t st) {
     if (g1 <= g0) return;
+    double* lgfact = g_dev.get<double>("lgfact", (size_t)LGFACT_N);
+    CBS_LAUNCH(k_lgfact_init, grid1(LGFACT_N, 256), 256, 0, st, lgfact);
     for (size_t e0 = 0; e0 < jobs.size(); e0 += APL_MAX_EVALS) {
         AplLaunch L;
         L.n_evals = (int)std::min<size_t>(APL_MAX_EVALS, jobs.size() - e0);
         for (int e = 0; e < L.n_evals; ++e) { L.design[e] = jobs[e0 + e].design; L.phi[e] = jobs[e0 + e].phi; }
         dim3 grid((unsigned)((g1 - g0 + 127) / 128), (unsigned)L.n_evals);
         CBS_LAUNCH(k_apl, grid, 128, 0, st, cnt, G, g0, g1, logoff, designs, sel,
-                   phi_gene ? phi_gene + e0 * G : nullptr, L, d_apl + e0 * G);
+                   phi_gene ? phi_gene + e0 * G : nullptr, L, d_apl + e0 * G, g_apl_fast ? (const double*)lgfact : (const double*)nullptr);
     }
 }
 
@@ -221,16 +223,18 @@ static bool run_mc_batch_gemm(const int32_t* cnt, long G, int n, const int* d_co
     CBS_LAUNCH(k_mcg_prep_tgt, grid1(sh.rows, 128), 128, 0, st, cnt, G, d_cols, sh, Fn, d_dct, P, d_tail);
     CBS_LAUNCH(k_mcg_pack_gp, grid1(sh.rows, 256), 256, 0, st, d_gamma, d_phi, G, sh.rows, gp);
     if (i1 > i0) {
-        const long tile0 = i0 / MCG_TILE, ntiles = (i1 - i0 + MCG_TILE - 1) / MCG_TILE, NJ = sh.rows / MCG_TILE;
+        const long tile0 = i0 / MCG_TI, ntiles = (i1 - i0 + MCG_TI - 1) / MCG_TI, NJ = sh.rows / MCG_TILE;
         int sms = 148;
         { int dev = 0; cudaGetDevice(&dev); cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev); }
-        long nsplit = (8L * sms + ntiles - 1) / ntiles;
+        long nsplit = (16L * sms + ntiles - 1) / ntiles;          // two CTAs per SM: aim at >= 8 waves
         nsplit = std::max(1L, std::min(nsplit, std::min(32L, std::max(1L, NJ / 4))));
         McAcc* part = (McAcc*)g_dev.get<double>("mcg_part", (size_t)nsplit * sh.rows * (sizeof(McAcc) / sizeof(double)));
         static bool attr_set = false;
         if (!attr_set) {
             CBS_CUDA(cudaFuncSetAttribute(k_mc_gemm<0>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)MCG_SMEM_BYTES));
             CBS_CUDA(cudaFuncSetAttribute(k_mc_gemm<1>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)MCG_SMEM_BYTES));
+            CBS_CUDA(cudaFuncSetAttribute(k_mc_gemm<0>, cudaFuncAttributePreferredSharedMemoryCarveout, 100));   // two CTAs per SM
+            CBS_CUDA(cudaFuncSetAttribute(k_mc_gemm<1>, cudaFuncAttributePreferredSharedMemoryCarveout, 100));
             attr_set = true;
         }
         const dim3 grid((unsigned)ntiles, (unsigned)nsplit);
