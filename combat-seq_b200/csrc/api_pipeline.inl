@@ -182,9 +182,14 @@ static void pipeline(const cbs_input* in, cbs_output* out, const T* h_or_d_count
     out->row_begin = r0; out->row_end = r1;
     if (d_adj) {
         CBS_LAUNCH(k_counts_to_f64<T>, grid1(G0 * N, 256), 256, 0, st, d_in, G0 * N, d_adj);
-        if (g1 > g0)
-            CBS_LAUNCH(k_match_quantiles, dim3((unsigned)((g1 - g0 + 127) / 128), (unsigned)N), 128, 0, st, d_cnt, G, g0, g1,
-                       d_mu_hat, d_bidx, d_phi_hat, d_gamma_star, d_phi_star, d_keep_idx, G0, d_adj);
+        if (g1 > g0) {
+            std::vector<int> order;                                   // samples sorted by batch (stable)
+            order.reserve(N);
+            for (int b = 0; b < B; ++b) order.insert(order.end(), bcols[b].begin(), bcols[b].end());
+            int* d_order = upload(g_dev, "mq_order", order.data(), (size_t)N, st);
+            CBS_LAUNCH(k_match_quantiles_rows, dim3((unsigned)((g1 - g0 + 7) / 8), (unsigned)((N + 31) / 32)), 256, 0, st, d_cnt, G,
+                       g0, g1, d_mu_hat, d_bidx, d_order, N, d_phi_hat, d_gamma_star, d_phi_star, d_keep_idx, G0, d_adj);
+        }
     }
     lap(CBS_ST_MATCH_QUANTILES);
 

@@ -175,6 +175,7 @@ k_glm_fit(const int32_t* __restrict__ cnt, long G, long g0, long g1, const doubl
 // Used for designs with p <= GLM_LANES_PMAX columns (packed X'WX of 136 doubles per thread in local memory).
 constexpr int GLM_LANES = 8;
 constexpr int GLM_LANES_PMAX = 16;
+template <int PM>                                            // PM >= design columns: sizes the per-thread packed X'WX (local memory)
 __global__ void __launch_bounds__(128)
 k_glm_fit_lanes(const int32_t* __restrict__ cnt, long G, long g0, long g1, const double* __restrict__ logoff,
                 const double* __restrict__ yadd, double two_prior_over_meanlib, const double* __restrict__ phi,
@@ -191,8 +192,8 @@ k_glm_fit_lanes(const int32_t* __restrict__ cnt, long G, long g0, long g1, const
     if (mode == 1) goff = log(exp(goff) + two_prior_over_meanlib);
     RowSrc src{cnt, G, logoff, mode == 1 ? yadd : nullptr, phi, phi_col, 0.0};
     Row r(src, g, goff);
-    double beta[GLM_LANES_PMAX], cellbeta[GLM_LANES_PMAX];
-    fit_gene<GLM_LANES, GLM_LANES_PMAX>(d, r, beta, cellbeta, ln, gm);
+    double beta[PM], cellbeta[PM];
+    fit_gene<GLM_LANES, PM>(d, r, beta, cellbeta, ln, gm);
     if (coef) for (int k = ln; k < d.p; k += GLM_LANES) coef[g + (long)k * G] = beta[k];
     if (alpha_out && ln == 0) {
         double a = 0;
@@ -237,6 +238,42 @@ k_match_quantiles(const int32_t* __restrict__ cnt, long G, long g0, long g1, con
     const double new_mu = exp(log(old_mu) - gamma_star[g + (long)b * G]);     // ComBat_seq.R:176
     const double v = match_one_fast(x, old_mu, phi_hat[g + (long)b * G], new_mu, phi_star[g]);
     out[(keep_idx ? (long)keep_idx[g] : g) + (long)s * G0] = v;
+}
+
+// Same contract, different thread mapping: one warp = one gene x 32 samples of (mostly) one batch.  The nmath routines
+// branch on the magnitudes of x, mu and size (continued-fraction length, pmf-walk length, pass-throughs), and those are
+// similar along a gene's row and wildly different down a column: with one warp per 32 consecutive genes only 10 of 32
+// lanes were active per instruction (ncu, round 1).  A block owns an 8-gene x 32-sample tile: it is loaded with 8
+// consecutive genes per sample (whole 32-byte sectors), transposed through shared memory, computed with warp w = gene
+// w, lane l = sample l, and stored the way it was loaded.  order[] lists the samples sorted by batch.
+// grid: (ceil((g1-g0)/8), ceil(N/32)), block 256.
+__global__ void __launch_bounds__(256)
+k_match_quantiles_rows(const int32_t* __restrict__ cnt, long G, long g0, long g1, const double* __restrict__ mu_hat,
+                       const int* __restrict__ batch_idx, const int* __restrict__ order, int N,
+                       const double* __restrict__ phi_hat, const double* __restrict__ gamma_star,
+                       const double* __restrict__ phi_star, const int* __restrict__ keep_idx, long G0,
+                       double* __restrict__ out) {
+    __shared__ double s_mu[32][9], s_out[32][9];
+    __shared__ int s_x[32][9];
+    const int t = threadIdx.x, gi = t & 7, si = t >> 3, w = t >> 5, l = t & 31;
+    const long gl = g0 + (long)blockIdx.x * 8;
+    const int sbase = blockIdx.y * 32;
+    const bool io_ok = (gl + gi < g1) && (sbase + si < N);
+    const int s_io = io_ok ? order[sbase + si] : 0;
+    if (io_ok) {
+        s_x[si][gi] = cnt[gl + gi + (long)s_io * G];
+        s_mu[si][gi] = mu_hat[gl + gi + (long)s_io * G];
+    }
+    __syncthreads();
+    if (gl + w < g1 && sbase + l < N) {
+        const long g = gl + w;
+        const int b = batch_idx[order[sbase + l]];
+        const double old_mu = s_mu[l][w];
+        const double new_mu = exp(log(old_mu) - gamma_star[g + (long)b * G]);     // ComBat_seq.R:176
+        s_out[l][w] = match_one_fast((double)s_x[l][w], old_mu, phi_hat[g + (long)b * G], new_mu, phi_star[g]);
+    }
+    __syncthreads();
+    if (io_ok) out[(keep_idx ? (long)keep_idx[gl + gi] : gl + gi) + (long)s_io * G0] = s_out[si][gi];
 }
 
 // generic per-batch form used by cbs_match_quantiles (explicit new_mu)

@@ -138,13 +138,19 @@ k_mcg_prep_nodes(const int32_t* __restrict__ cnt, long G, const int* __restrict_
                  double* __restrict__ Fnode) {
     const long i = (long)blockIdx.x * blockDim.x + threadIdx.x;
     const int m = blockIdx.y;
-    if (i >= G) return;
     const double tn = cospi((m + 0.5) / sh.Kc);
     const double r = exp(0.5 * (sh.ulo + sh.uhi) + 0.5 * (sh.uhi - sh.ulo) * tn) - (double)MCG_SHIFT;
+    // r is the same for the whole block (one node): the small counts, which would each cost two lgamma() calls, come
+    // from an 11-entry table built with the very same expression
+    __shared__ double small[15 - MCG_SHIFT];
+    if (threadIdx.x < 15 - MCG_SHIFT) small[threadIdx.x] = lgamma_diff((double)(threadIdx.x + MCG_SHIFT), r);
+    __syncthreads();
+    if (i >= G) return;
     double f = 0;
     for (int t = 0; t < sh.n; ++t) {
         const int x = cnt[i + (long)cols[t] * G];
-        if (x >= MCG_SHIFT) f += lgamma_diff((double)x, r);
+        if (x >= 15) f += lgamma_diff((double)x, r);
+        else if (x >= MCG_SHIFT) f += small[x - MCG_SHIFT];
     }
     Fnode[(long)m * G + i] = f;
 }

@@ -138,10 +138,12 @@ static void run_glm_fit(const int32_t* cnt, long G, long g0, long g1, int N, con
     const bool lanes = h_p <= GLM_LANES_PMAX;
     const dim3 lgrid = grid1((g1 - g0) * GLM_LANES, 128);
     auto launch = [&](const double* yadd, double tp, int mode, double* coef, double* fitted, double* alpha) {
-        if (lanes)
-            CBS_LAUNCH(k_glm_fit_lanes, lgrid, 128, 0, st, cnt, G, g0, g1, d_logoff, yadd, tp, d_phi, d_phi_col, d_design,
-                       d_goff, mode, coef, fitted, d_alpha_w, n_alpha, alpha);
-        else
+#define CBS_GLM_LANES(PM_) CBS_LAUNCH(k_glm_fit_lanes<PM_>, lgrid, 128, 0, st, cnt, G, g0, g1, d_logoff, yadd, tp, d_phi, \
+                                      d_phi_col, d_design, d_goff, mode, coef, fitted, d_alpha_w, n_alpha, alpha)
+        if (lanes) {
+            if (h_p <= 4) CBS_GLM_LANES(4); else if (h_p <= 8) CBS_GLM_LANES(8); else if (h_p <= 12) CBS_GLM_LANES(12); else CBS_GLM_LANES(16);
+        } else
+#undef CBS_GLM_LANES
             CBS_LAUNCH(k_glm_fit, grid, 128, 0, st, cnt, G, g0, g1, d_logoff, yadd, tp, d_phi, d_phi_col, d_design,
                        d_goff, mode, coef, fitted, d_alpha_w, n_alpha, alpha);
     };
