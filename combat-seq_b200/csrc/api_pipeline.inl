@@ -85,7 +85,9 @@ static void pipeline(const cbs_input* in, cbs_output* out, const T* h_or_d_count
     std::vector<double> lib(N), logoff(N);
     for (int s = 0; s < N; ++s) { lib[s] = (double)cs[s]; logoff[s] = std::log(lib[s]); }
     if (out->lib_size) memcpy(out->lib_size, lib.data(), (size_t)N * sizeof(double));
-    double* d_logoff = upload(g_dev, "logoff", logoff.data(), (size_t)N, st);
+    std::vector<double> offpairs((size_t)2 * N);                  // (log(lib), lib) pairs: see glm.cuh RowSrc::logoff
+    for (int s = 0; s < N; ++s) { offpairs[2 * s] = logoff[s]; offpairs[2 * s + 1] = lib[s]; }
+    double* d_logoff = upload(g_dev, "logoff", offpairs.data(), (size_t)2 * N, st);
 
     long g0, g1;
     shard_range(G, rank, world, &g0, &g1);

@@ -55,9 +55,9 @@ int cbs_glm_fit(int64_t G, int32_t n, const int32_t* counts, const double* desig
     std::vector<int> pc(n, 0);
     if (disp_cols) for (int s = 0; s < n; ++s) pc[s] = disp_cols[s];
     int* d_pc = upload(g_dev, "phi_col", pc.data(), (size_t)n);
-    std::vector<double> hlib(lib, lib + n), logoff(n);
-    for (int s = 0; s < n; ++s) logoff[s] = std::log(hlib[s]);
-    double* d_logoff = upload(g_dev, "logoff", logoff.data(), (size_t)n);
+    std::vector<double> hlib(lib, lib + n), logoff((size_t)2 * n);
+    for (int s = 0; s < n; ++s) { logoff[2 * s] = std::log(hlib[s]); logoff[2 * s + 1] = hlib[s]; }
+    double* d_logoff = upload(g_dev, "logoff", logoff.data(), (size_t)2 * n);
     double* d_goff = gene_offset ? upload(g_dev, "goff", gene_offset, (size_t)G) : nullptr;
     double* d_coef = coef ? g_dev.get<double>("coef", (size_t)G * p) : nullptr;
     double* d_fit = fitted ? g_dev.get<double>("mu_hat", (size_t)G * n) : nullptr;
@@ -80,9 +80,9 @@ int cbs_apl(int64_t G, int32_t n, const int32_t* counts, const double* design, i
     ds.add(subproblem_design(design, n, p));
     ds.finish();
     int32_t* d_cnt = upload(g_dev, "cnt", counts, (size_t)G * n);
-    std::vector<double> logoff(n);
-    for (int s = 0; s < n; ++s) logoff[s] = std::log(lib[s]);
-    double* d_logoff = upload(g_dev, "logoff", logoff.data(), (size_t)n);
+    std::vector<double> logoff((size_t)2 * n);
+    for (int s = 0; s < n; ++s) { logoff[2 * s] = std::log(lib[s]); logoff[2 * s + 1] = lib[s]; }
+    double* d_logoff = upload(g_dev, "logoff", logoff.data(), (size_t)2 * n);
     std::vector<AplJob> jobs(D);
     for (int d = 0; d < D; ++d) jobs[d] = {0, disp_per_gene ? 0.0 : disp[d]};
     double* d_pg = disp_per_gene ? upload(g_dev, "apl_phi_gene", disp, (size_t)G * D) : nullptr;
@@ -114,9 +114,9 @@ struct OneBatch {
                    d_ident, (long)G, d_tmp, d_cs);
         std::vector<unsigned long long> cs(n);
         CBS_CUDA(cudaMemcpy(cs.data(), d_cs, (size_t)n * sizeof(unsigned long long), cudaMemcpyDeviceToHost));
-        std::vector<double> logoff(n);
-        for (int s = 0; s < n; ++s) logoff[s] = std::log((double)cs[s]);
-        d_logoff = upload(g_dev, "logoff", logoff.data(), (size_t)n);
+        std::vector<double> logoff((size_t)2 * n);
+        for (int s = 0; s < n; ++s) { logoff[2 * s] = std::log((double)cs[s]); logoff[2 * s + 1] = (double)cs[s]; }
+        d_logoff = upload(g_dev, "logoff", logoff.data(), (size_t)2 * n);
         std::vector<int> bidx(n, 0);
         d_bidx = upload(g_dev, "batch_idx", bidx.data(), (size_t)n);
         d_sel = g_dev.get<unsigned char>("sel", (size_t)G);
