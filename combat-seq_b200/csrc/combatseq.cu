@@ -94,7 +94,7 @@ struct DesignSet {
             return p;
         };
         DesignDev d;
-        d.n = h.n; d.p = h.p; d.oneway = h.oneway;
+        d.n = h.n; d.p = h.p; d.oneway = h.oneway; d.ncls = h.ncls;
         d.col = (const int*)up(h.col.data(), h.col.size() * sizeof(int));
         d.cell_start = (const int*)up(h.cell_start.data(), h.cell_start.size() * sizeof(int));
         d.minv = (const double*)up(h.minv.data(), h.minv.size() * sizeof(double));

@@ -29,6 +29,7 @@ constexpr int PTRI = PMAX * (PMAX + 1) / 2;  // packed lower triangle
 // A (sub)problem design: n samples, p columns.  Arrays live in global memory (read-only, tiny, L1-resident).
 struct DesignDev {
     int n, p, oneway;
+    int ncls;              // > 0 (Levenberg designs only): samples grouped by distinct design row, cell_start[ncls+1]
     const int* col;        // [n] column of each sample in the G x N matrices; grouped by cell when oneway
     const int* cell_start; // [p+1] sample ranges of the cells (oneway)
     const double* minv;    // [p*p] column-major inverse of the distinct design rows: coef = minv * cellbeta
@@ -147,6 +148,33 @@ __device__ inline double lev_sweep(const DesignDev& d, const Row& r, const doubl
     for (int i = 0; i < p * (p + 1) / 2; ++i) xtwx[i] = 0;
     for (int i = 0; i < p; ++i) dl[i] = 0;
     double dev = 0;
+    if (d.ncls > 0) {
+        // Samples grouped by distinct design row: mu_s = exp(gene offset + x_c'beta) * lib.size_s needs one exp per class,
+        // and X'WX, X'z only need the class sums of W and z (the packed matrix is touched once per class, not per sample).
+        for (int c = 0; c < d.ncls; ++c) {
+            const int t0 = d.cell_start[c], t1 = d.cell_start[c + 1], k0 = d.rowptr[t0], k1 = d.rowptr[t0 + 1];
+            double eta = r.goff;
+            for (int k = k0; k < k1; ++k) eta += d.cval[k] * beta[d.cidx[k]];
+            const double E = exp(eta);
+            double sw = 0, sz = 0;
+            for (int t = t0 + ln; t < t1; t += LANES) {
+                const int col = d.col[t];
+                const double mu = E * r.lib(col), y = r.y(col), phi = r.phi(col);
+                dev += unit_nb_deviance(y, mu, phi);
+                const double inv = 1.0 / (1 + mu * phi);
+                sw += mu * inv; sz += (y - mu) * inv;
+            }
+            if (LANES > 1) { sw = lane_sum<LANES>(sw, gm); sz = lane_sum<LANES>(sz, gm); }
+            for (int k = k0; k < k1; ++k) {
+                const int ik = d.cidx[k];
+                const double vk = d.cval[k];
+                dl[ik] += vk * sz;
+                for (int k2 = k0; k2 <= k; ++k2) xtwx[tri(ik, d.cidx[k2])] += vk * d.cval[k2] * sw;
+            }
+        }
+        if (LANES > 1) dev = lane_sum<LANES>(dev, gm);
+        return dev;
+    }
     for (int t = ln; t < d.n; t += LANES) {
         const int c = d.col[t];
         const double mu = exp(lin_pred(d, r, t, beta)), y = r.y(c), phi = r.phi(c);
@@ -196,11 +224,12 @@ __device__ inline bool fit_levenberg(const DesignDev& d, const Row& r, double* b
     const int p = d.p, pt = p * (p + 1) / 2;
     double xtwx[PT], xtwx_new[PT], work[PT], dl[PM], dl_new[PM], dbeta[PM], beta_new[PM];
     double ymax = 0, sum_exprs = 0, sum_weight = 0;
+    const double eg0 = exp(r.goff);
     for (int t = ln; t < d.n; t += LANES) {
         const int c = d.col[t];
         const double y = r.y(c);
         if (y > ymax) ymax = y;
-        const double curN = exp(r.off(c)), w = curN / (1 + r.phi(c) * curN);
+        const double curN = r.lib(c) * eg0, w = curN / (1 + r.phi(c) * curN);
         sum_exprs += y * w / curN;
         sum_weight += w;
     }

@@ -57,6 +57,7 @@ inline int qr_rank(const double* Xin, int n, int p, double tol = 1e-7) {
 
 struct HostDesign {
     int n = 0, p = 0, oneway = 0;
+    int ncls = 0;                  // > 0: Levenberg design whose samples are grouped by distinct design row (cell_start has ncls+1 entries)
     std::vector<int> col;          // global column of each sample slot (cell-grouped when oneway)
     std::vector<int> cell_start;   // p+1
     std::vector<double> minv;      // p x p
@@ -155,6 +156,17 @@ inline HostDesign make_design(const double* X, int n, int p, const int* cols) {
         for (int s = 0; s < n; ++s) order[s] = s;
         std::vector<double> ones(n, 1.0);
         lstsq(X, n, p, ones.data(), d.start.data());
+        // few distinct design rows (categorical covariates): group the samples by row so that the device sweeps can share
+        // exp(x'beta) and the X'WX update inside a class (glm.cuh lev_sweep)
+        if (nlev <= 32 && nlev < n) {
+            std::vector<int> grp(n);
+            for (int s = 0; s < n; ++s) grp[s] = (int)(std::lower_bound(lev.begin(), lev.end(), h[s]) - lev.begin());
+            std::stable_sort(order.begin(), order.end(), [&](int a, int b) { return grp[a] < grp[b]; });
+            d.ncls = nlev;
+            d.cell_start.assign(nlev + 1, 0);
+            for (int s = 0; s < n; ++s) d.cell_start[grp[s] + 1]++;
+            for (int l = 0; l < nlev; ++l) d.cell_start[l + 1] += d.cell_start[l];
+        }
     }
     d.col.resize(n);
     d.rowptr.assign(n + 1, 0);
