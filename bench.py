@@ -324,7 +324,8 @@ def roofline(L, prof, G, N, nb, world, steps, case):
         return {"kernel": name, "bound": "tensor", "achieved": ach, "peak": peak, "unit": "TFLOP/s", "frac": ach / peak,
                 "traffic": None, "avg_launch_ms": ms / n, "launches": n,
                 "note": "FP64 tensor pipe (mma.sync m8n8k4 f64 = DMMA; tcgen05 has no FP64 path). peak = DMMA microbenchmark "
-                        "measured in this run (cbs_fp64_mma_peak; MEASURED_PEAKS.json has no FP64 figure); inner length "
+                        "measured in this run (cbs_fp64_mma_peak; MEASURED_PEAKS.json has no FP64 figure; DMMA and DFMA share "
+                        "the FP64 units on B200, so the epilogue's exp() work comes out of the same budget); inner length "
                         "KT = %d (n_b %d + %d Chebyshev terms + 5); %.3g gene pairs/s = %.3g NB terms/s"
                         % (kt, n_b, kc, float(G) / world * G / avg_s, float(G) / world * G * n_b / avg_s)}
     if name.startswith("k_mc"):

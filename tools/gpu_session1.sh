@@ -7,6 +7,8 @@ nvidia-smi --query-gpu=name,clocks.sm,clocks.max.sm,power.draw --format=csv > $O
 timeout 900 python -m pytest tests -m gpu -x -q > $O/pytest_gpu.txt 2>&1; echo "pytest rc=$?" >> $O/pytest_gpu.txt
 timeout 900 python bench.py --steps 3 --warmup 3 > $O/bench_c5.json 2> $O/bench_c5.err; echo "bench rc=$?" >> $O/bench_c5.err
 timeout 300 python tools/mc_time.py 20000 100 2 > $O/mc_time.txt 2>&1
+timeout 300 python __graft_entry__.py smoke > $O/smoke.txt 2>&1; echo "smoke rc=$?" >> $O/smoke.txt
+timeout 300 python bench.py --impl reference --steps 1 --warmup 1 > $O/bench_ref.json 2> $O/bench_ref.err
 timeout 300 python bench.py --workload C4 --steps 3 --warmup 3 --no-cpu > $O/bench_c4.json 2> $O/bench_c4.err
 timeout 300 python bench.py --workload C2 --steps 3 --warmup 3 --no-cpu > $O/bench_c2.json 2> $O/bench_c2.err
 CMD="python bench.py --steps 1 --warmup 1 --no-cpu"
