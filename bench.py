@@ -300,8 +300,30 @@ def run_native(args):
         dist.destroy_process_group()
 
 
+def ncu_traffic(name, G, N, world):
+    """dram__bytes_read.sum + dram__bytes_write.sum per launch of this kernel, from the committed `ncu --set full` capture
+    (profiles/ncu_traffic.json, written from the capture's raw page).  The capture is of the 1-GPU C5 workload, so the
+    figure is only reported for that shape; otherwise null."""
+    if world != 1 or (G, N) != (60000, 1000):
+        return None
+    try:
+        tab = json.load(open(os.path.join(ROOT, "profiles", "ncu_traffic.json")))
+    except (OSError, ValueError):
+        return None
+    for k, v in tab.items():
+        if name.startswith(k):
+            return v["dram_bytes_per_launch"]
+    return None
+
+
 def roofline(L, prof, G, N, nb, world, steps, case):
     """Roofline of the dominant kernel (largest share of device time in the timed region)."""
+    r = _roofline(L, prof, G, N, nb, world, steps, case)
+    r["traffic"] = ncu_traffic(r["kernel"], int(case.counts.shape[0]), N, world)
+    return r
+
+
+def _roofline(L, prof, G, N, nb, world, steps, case):
     peaks = {}
     try:
         peaks = json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json")))

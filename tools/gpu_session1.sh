@@ -20,6 +20,10 @@ for k in k_mc_gemm k_match_quantiles k_glm_fit k_apl; do
   ncu -i /tmp/prof_$k.ncu-rep --page details --csv > $O/prof_${k}_details.csv 2>/dev/null
   ncu -i /tmp/prof_$k.ncu-rep --page source --csv > $O/prof_${k}_source.csv 2>/dev/null
 done
-cp /tmp/prof_k_mc_gemm.ncu-rep $O/ 2>/dev/null
+# gpurun_out/ is capped at 64 MiB: keep text summaries, gzip the big per-instruction pages, leave the .ncu-rep files on the box
+for k in k_mc_gemm k_match_quantiles k_glm_fit k_apl; do
+  { python tools/ncu_raw_summary.py $O/prof_${k}_raw.csv; echo; python tools/ncu_src_summary.py $O/prof_${k}_source.csv 18; } > $O/summary_$k.txt 2>&1
+  gzip -f $O/prof_${k}_source.csv
+done
 du -sh $O
 ls -la $O
