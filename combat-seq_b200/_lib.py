@@ -9,7 +9,7 @@ import os
 import numpy as np
 
 HERE = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(HERE, "libcombatseq.so")
+LIB_PATH = os.environ.get("COMBATSEQ_LIB") or os.path.join(HERE, "libcombatseq.so")   # (override: development builds)
 
 f64p = C.POINTER(C.c_double)
 i32p = C.POINTER(C.c_int32)

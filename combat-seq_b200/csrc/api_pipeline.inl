@@ -163,7 +163,7 @@ static void pipeline(const cbs_input* in, cbs_output* out, const T* h_or_d_count
             int* d_cols = upload(g_dev, "mc_cols", bcols[b].data(), bcols[b].size(), st);
             run_mc_batch(d_cnt, G, (int)bcols[b].size(), d_cols, g0, g1, d_mu_hat, d_gamma_hat + (size_t)b * G,
                          d_phi_hat + (size_t)b * G, in->mc_mode, in->gene_subset_n > 0 ? in->gene_subset_n : 0,
-                         in->seed + (uint64_t)b, d_gamma_star + (size_t)b * G, d_ps + (size_t)b * G, d_nfb + b, st);
+                         in->seed + (uint64_t)b, d_gamma_star + (size_t)b * G, d_ps + (size_t)b * G, d_nfb + b, st, comm);
             CBS_CUDA(cudaStreamSynchronize(st));      // mc_cols / mc_* scratch is reused by the next batch
         }
         CBS_CUDA(cudaMemcpy(nfb.data(), d_nfb, (size_t)B * sizeof(unsigned long long), cudaMemcpyDeviceToHost));
@@ -189,8 +189,18 @@ static void pipeline(const cbs_input* in, cbs_output* out, const T* h_or_d_count
             order.reserve(N);
             for (int b = 0; b < B; ++b) order.insert(order.end(), bcols[b].begin(), bcols[b].end());
             int* d_order = upload(g_dev, "mq_order", order.data(), (size_t)N, st);
-            CBS_LAUNCH(k_match_quantiles_rows, dim3((unsigned)((g1 - g0 + 7) / 8), (unsigned)((N + 31) / 32)), 256, 0, st, d_cnt, G,
-                       g0, g1, d_mu_hat, d_bidx, d_order, N, d_phi_hat, d_gamma_star, d_phi_star, d_keep_idx, G0, d_adj);
+            if (g_mq_rows == 3)
+                CBS_LAUNCH(k_match_quantiles_warp<true>, dim3((unsigned)((g1 - g0 + 3) / 4), (unsigned)((N + 31) / 32)), 128, 0, st, d_cnt, G,
+                           g0, g1, d_mu_hat, d_bidx, d_order, N, d_phi_hat, d_gamma_star, d_phi_star, d_keep_idx, G0, d_adj);
+            else if (g_mq_rows == 2)
+                CBS_LAUNCH(k_match_quantiles_warp<false>, dim3((unsigned)((g1 - g0 + 3) / 4), (unsigned)((N + 31) / 32)), 128, 0, st, d_cnt, G,
+                           g0, g1, d_mu_hat, d_bidx, d_order, N, d_phi_hat, d_gamma_star, d_phi_star, d_keep_idx, G0, d_adj);
+            else if (g_mq_rows == 4)
+                CBS_LAUNCH(k_match_quantiles_rows<true>, dim3((unsigned)((g1 - g0 + 7) / 8), (unsigned)((N + 31) / 32)), 256, 0, st, d_cnt, G,
+                           g0, g1, d_mu_hat, d_bidx, d_order, N, d_phi_hat, d_gamma_star, d_phi_star, d_keep_idx, G0, d_adj);
+            else
+                CBS_LAUNCH(k_match_quantiles_rows<false>, dim3((unsigned)((g1 - g0 + 7) / 8), (unsigned)((N + 31) / 32)), 256, 0, st, d_cnt, G,
+                           g0, g1, d_mu_hat, d_bidx, d_order, N, d_phi_hat, d_gamma_star, d_phi_star, d_keep_idx, G0, d_adj);
         }
     }
     lap(CBS_ST_MATCH_QUANTILES);

@@ -23,6 +23,9 @@ static PinCache g_pin;
 
 // ---- tuning knobs (cbs_set_tuning) ----------------------------------------------------------------------------
 static int g_mc_algo = 0;            // 0 = auto (tensor-core contraction when gene.subset.n is NULL), 1 = direct, 2 = contraction
+static int g_glm_scr = 1;            // 1 = Levenberg work arrays of the lane-group GLM kernel in shared memory (one copy per gene)
+static int g_mq_rows = 3;            // match_quantiles: 3 = warp per gene, out-of-line continued fraction (fastest, same bits); 2 = same, inlined;
+                                     // 1 = 8x32 tiles via shared memory, inlined; 4 = tiles, out-of-line
 static int g_apl_fast = 1;           // 1 = lgamma(y+1) table + hoisted log(r)/lgamma(r) in the APL kernel (same bits), 0 = per-sample calls
 static double g_mc_tail_tol = 1e-8;  // largest accepted Chebyshev tail estimate (log-likelihood units)
 static double g_last_mc_tail = 0;    // diagnostics: largest tail estimate of the last Monte-Carlo stage
@@ -69,7 +72,7 @@ NcclApi* nccl_api() {
             throw CbsError{CBS_ENCCL};                                                              \
         }                                                                                           \
     } while (0)
-constexpr int NCCL_INT8 = 0, NCCL_FLOAT64 = 8, NCCL_SUM = 0;   // ncclDataType_t / ncclRedOp_t values (nccl.h)
+constexpr int NCCL_INT8 = 0, NCCL_UINT64 = 5, NCCL_FLOAT64 = 8, NCCL_SUM = 0, NCCL_MAX = 2;   // ncclDataType_t / ncclRedOp_t values (nccl.h)
 
 static bool have_gpu() {
     int n = 0;

@@ -171,6 +171,7 @@ __device__ inline double lev_sweep(const DesignDev& d, const Row& r, const doubl
                 dl[ik] += vk * sz;
                 for (int k2 = k0; k2 <= k; ++k2) xtwx[tri(ik, d.cidx[k2])] += vk * d.cval[k2] * sw;
             }
+            if (LANES > 1) __syncwarp(gm);                    // (shared scratch) the group updates X'WX as one
         }
         if (LANES > 1) dev = lane_sum<LANES>(dev, gm);
         return dev;
@@ -217,12 +218,31 @@ __device__ inline void chol_solve_packed(const double* a, int p, double* b) {
 }
 
 // edgeR glm_levenberg::fit with the "null" start.  beta (out, p).  Returns false when y is all zero (beta = NaN, mu = 0).
-template <int LANES = 1, int PM = PMAX>
+// Work arrays of one Levenberg fit: 3 packed p x p triangles and 4 p-vectors.  One thread per gene keeps them in local
+// memory.  A lane group can share ONE copy in shared memory (SCR = true, `scr` = lev_scratch_doubles<PM>() doubles owned
+// by the group): outside the sample sweeps every lane of the group executes the same instructions on bit-identical
+// values, so the group's lanes read and write the same words in lock-step.  That needs the class form of the sweep
+// (d.ncls > 0), where the lanes' partial sums are combined BEFORE X'WX is touched; the per-sample form accumulates a
+// private X'WX per lane and keeps the local arrays.
+template <int PM>
+__host__ __device__ constexpr int lev_scratch_doubles() {
+    // 3 PT + 4 PM, padded so that the 4 groups of a warp fall on disjoint shared-memory banks (stride = 4 mod 8)
+    return (3 * (PM * (PM + 1) / 2) + 4 * PM + 3) / 8 * 8 + 4;
+}
+template <int LANES = 1, int PM = PMAX, bool SCR = false>
 __device__ inline bool fit_levenberg(const DesignDev& d, const Row& r, double* beta, int ln = 0, unsigned gm = 0xffffffffu,
-                                     int maxit = 250, double tolerance = 1e-6) {
+                                     int maxit = 250, double tolerance = 1e-6, double* scr = nullptr) {
     constexpr int PT = PM * (PM + 1) / 2;
+    constexpr int LT = SCR ? 1 : PT, LV = SCR ? 1 : PM;
     const int p = d.p, pt = p * (p + 1) / 2;
-    double xtwx[PT], xtwx_new[PT], work[PT], dl[PM], dl_new[PM], dbeta[PM], beta_new[PM];
+    double l_xtwx[LT], l_xtwx_new[LT], l_work[LT], l_dl[LV], l_dl_new[LV], l_dbeta[LV], l_beta_new[LV];
+    double* const xtwx = SCR ? scr : l_xtwx;
+    double* const xtwx_new = SCR ? scr + PT : l_xtwx_new;
+    double* const work = SCR ? scr + 2 * PT : l_work;
+    double* const dl = SCR ? scr + 3 * PT : l_dl;
+    double* const dl_new = SCR ? scr + 3 * PT + PM : l_dl_new;
+    double* const dbeta = SCR ? scr + 3 * PT + 2 * PM : l_dbeta;
+    double* const beta_new = SCR ? scr + 3 * PT + 3 * PM : l_beta_new;
     double ymax = 0, sum_exprs = 0, sum_weight = 0;
     const double eg0 = exp(r.goff);
     for (int t = ln; t < d.n; t += LANES) {
@@ -281,7 +301,7 @@ __device__ inline bool fit_levenberg(const DesignDev& d, const Row& r, double* b
 // Returns the mode used so that the caller can form fitted values with fitted_at().
 template <int LANES = 1, int PM = PMAX>
 __device__ inline void fit_gene(const DesignDev& d, const Row& r, double* beta, double* cellbeta, int ln = 0,
-                                unsigned gm = 0xffffffffu) {
+                                unsigned gm = 0xffffffffu, double* scr = nullptr) {
     if (d.oneway) {
         for (int l = 0; l < d.p; ++l) {
             const double b = fit_one_group<LANES>(d, r, d.cell_start[l], d.cell_start[l + 1], 50, 1e-10, ln, gm);
@@ -293,7 +313,8 @@ __device__ inline void fit_gene(const DesignDev& d, const Row& r, double* beta, 
             beta[k] = s;
         }
     } else {
-        fit_levenberg<LANES, PM>(d, r, beta, ln, gm);
+        if (LANES > 1 && scr != nullptr && d.ncls > 0) fit_levenberg<LANES, PM, true>(d, r, beta, ln, gm, 250, 1e-6, scr);
+        else fit_levenberg<LANES, PM, false>(d, r, beta, ln, gm);
     }
 }
 
@@ -359,17 +380,34 @@ __device__ inline double apl_gene(const DesignDev& d, const Row& r, const double
     double beta[PMAX], cellbeta[PMAX], wm[PTRI];
     const int p = d.p;
     fit_gene(d, r, beta, cellbeta);
-    const bool scalar_phi = lgfact != nullptr && (r.s.phi == nullptr) && r.s.phi_scalar > 0;
+    const bool fast = lgfact != nullptr;                    // the "apl_fast" knob: table + hoisting + product form
+    const bool scalar_phi = fast && (r.s.phi == nullptr) && r.s.phi_scalar > 0;
     double rr_c = 0, logrr_c = 0, lgrr_c = 0;
     if (scalar_phi) { rr_c = 1 / r.s.phi_scalar; logrr_c = log(rr_c); lgrr_c = lgamma(rr_c); }
     for (int i = 0; i < p * (p + 1) / 2; ++i) wm[i] = 0;
     double sum_loglik = 0, sumw = 0;
-    int l = 0;
+    int l = -1;
+    double ecell = 0;
     for (int t = 0; t < d.n; ++t) {
         const int c = d.col[t];
-        double mu;
-        if (d.oneway) { while (t >= d.cell_start[l + 1]) ++l; mu = exp(cellbeta[l] + r.off(c)); }
-        else mu = isnan(beta[0]) ? 0.0 : exp(lin_pred(d, r, t, beta));
+        double mu, logmu;
+        if (d.oneway) {
+            // mu = exp(cell coefficient + gene offset) * lib.size and log(mu) = the linear predictor itself: one exp per
+            // cell instead of an exp and a log per sample (last-place differences against exp/log of the sum)
+            if (fast) {
+                if (l < 0 || t >= d.cell_start[l + 1]) { if (l < 0) l = 0; while (t >= d.cell_start[l + 1]) ++l; ecell = exp(cellbeta[l] + r.goff); }
+                mu = ecell * r.lib(c);
+                logmu = cellbeta[l] + r.off(c);
+            } else {
+                if (l < 0) l = 0;
+                while (t >= d.cell_start[l + 1]) ++l;
+                mu = exp(cellbeta[l] + r.off(c));
+                logmu = log(mu);
+            }
+        } else {
+            mu = isnan(beta[0]) ? 0.0 : exp(lin_pred(d, r, t, beta));
+            logmu = log(mu);
+        }
         if (mu == 0) continue;
         const double y = r.y(c), phi = r.phi(c);
         double loglik;
@@ -377,9 +415,9 @@ __device__ inline double apl_gene(const DesignDev& d, const Row& r, const double
         if (phi > 0) {
             const double rr = scalar_phi ? rr_c : 1 / phi, logmur = log(mu + rr);
             const double logrr = scalar_phi ? logrr_c : log(rr), lgrr = scalar_phi ? lgrr_c : lgamma(rr);
-            loglik = y * log(mu) - y * logmur + rr * logrr - rr * logmur + lgamma(y + rr) - lgy1 - lgrr;
+            loglik = y * logmu - y * logmur + rr * logrr - rr * logmur + lgamma(y + rr) - lgy1 - lgrr;
         } else {
-            loglik = y * log(mu) - mu - lgy1;
+            loglik = y * logmu - mu - lgy1;
         }
         const double W = mu / (1 + phi * mu);
         sum_loglik += loglik;

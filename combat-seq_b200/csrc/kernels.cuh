@@ -172,16 +172,18 @@ k_glm_fit(const int32_t* __restrict__ cnt, long G, long g0, long g1, const doubl
 // samples are split over the lanes, so a 60k-gene x 1000-sample fit exposes 480k threads instead of 60k and the
 // per-thread dependent chain is 125 samples per sweep instead of 1000.  A warp holds 32 / GLM_LANES consecutive genes:
 // each load instruction touches GLM_LANES columns x (32 / GLM_LANES) consecutive rows of the column-major matrices.
-// Used for designs with p <= GLM_LANES_PMAX columns (packed X'WX of 136 doubles per thread in local memory).
+// Used for designs with p <= GLM_LANES_PMAX columns.  use_scr: the Levenberg work arrays (3 packed X'WX + 4 vectors) are
+// one shared-memory copy per gene instead of a local-memory copy per lane (ncu, round 1: the local copies made 10.9 GB of
+// DRAM traffic per launch, 15x the algorithmic bytes); dynamic shared memory = (128 / GLM_LANES) * lev_scratch_doubles<PM>().
 constexpr int GLM_LANES = 8;
 constexpr int GLM_LANES_PMAX = 16;
 template <int PM>                                            // PM >= design columns: sizes the per-thread packed X'WX (local memory)
-__global__ void __launch_bounds__(128)
+__global__ void __launch_bounds__(128, 5)
 k_glm_fit_lanes(const int32_t* __restrict__ cnt, long G, long g0, long g1, const double* __restrict__ logoff,
                 const double* __restrict__ yadd, double two_prior_over_meanlib, const double* __restrict__ phi,
                 const int* __restrict__ phi_col, const DesignDev* __restrict__ design, const double* __restrict__ goff_in,
                 int mode, double* __restrict__ coef, double* __restrict__ fitted, const double* __restrict__ alpha_w,
-                int n_alpha, double* __restrict__ alpha_out) {
+                int n_alpha, double* __restrict__ alpha_out, int use_scr) {
     const long slot = ((long)blockIdx.x * blockDim.x + threadIdx.x) / GLM_LANES;
     const long g = g0 + slot;
     const int ln = threadIdx.x % GLM_LANES;
@@ -193,7 +195,9 @@ k_glm_fit_lanes(const int32_t* __restrict__ cnt, long G, long g0, long g1, const
     RowSrc src{cnt, G, logoff, mode == 1 ? yadd : nullptr, phi, phi_col, 0.0};
     Row r(src, g, goff);
     double beta[PM], cellbeta[PM];
-    fit_gene<GLM_LANES, PM>(d, r, beta, cellbeta, ln, gm);
+    extern __shared__ __align__(16) double glm_scr[];       // lev_scratch_doubles<PM>() per lane group, or nothing
+    double* scr = use_scr ? glm_scr + (threadIdx.x / GLM_LANES) * lev_scratch_doubles<PM>() : nullptr;
+    fit_gene<GLM_LANES, PM>(d, r, beta, cellbeta, ln, gm, scr);
     if (coef) for (int k = ln; k < d.p; k += GLM_LANES) coef[g + (long)k * G] = beta[k];
     if (alpha_out && ln == 0) {
         double a = 0;
@@ -247,6 +251,7 @@ k_match_quantiles(const int32_t* __restrict__ cnt, long G, long g0, long g1, con
 // consecutive genes per sample (whole 32-byte sectors), transposed through shared memory, computed with warp w = gene
 // w, lane l = sample l, and stored the way it was loaded.  order[] lists the samples sorted by batch.
 // grid: (ceil((g1-g0)/8), ceil(N/32)), block 256.
+template <bool NI>                                           // NI: out-of-line continued fraction (nbmath.cuh)
 __global__ void __launch_bounds__(256)
 k_match_quantiles_rows(const int32_t* __restrict__ cnt, long G, long g0, long g1, const double* __restrict__ mu_hat,
                        const int* __restrict__ batch_idx, const int* __restrict__ order, int N,
@@ -270,10 +275,32 @@ k_match_quantiles_rows(const int32_t* __restrict__ cnt, long G, long g0, long g1
         const int b = batch_idx[order[sbase + l]];
         const double old_mu = s_mu[l][w];
         const double new_mu = exp(log(old_mu) - gamma_star[g + (long)b * G]);     // ComBat_seq.R:176
-        s_out[l][w] = match_one_fast((double)s_x[l][w], old_mu, phi_hat[g + (long)b * G], new_mu, phi_star[g]);
+        s_out[l][w] = match_one_fast<NI>((double)s_x[l][w], old_mu, phi_hat[g + (long)b * G], new_mu, phi_star[g]);
     }
     __syncthreads();
     if (io_ok) out[(keep_idx ? (long)keep_idx[gl + gi] : gl + gi) + (long)s_io * G0] = s_out[si][gi];
+}
+
+// Warp = gene, lane = sample like k_match_quantiles_rows, but without the shared-memory tile: the kernel is bound by
+// FP64 arithmetic and divergence (ncu, round 1: 34 % FP64 pipe, 14 of 32 lanes active, DRAM traffic 0.3 % of peak), so
+// the strided loads and stores (one 32-byte sector per element, mostly L2 hits because the 4 warps of a block and the
+// neighbouring blocks share the sectors) cost nothing, while the two block barriers of the tiled form kept finished
+// warps waiting for the slowest gene of the tile (23 % of the stall samples).  grid: (ceil((g1-g0)/4), ceil(N/32)), block 128.
+template <bool NI>                                           // NI: out-of-line continued fraction (nbmath.cuh)
+__global__ void __launch_bounds__(128, 5)
+k_match_quantiles_warp(const int32_t* __restrict__ cnt, long G, long g0, long g1, const double* __restrict__ mu_hat,
+                       const int* __restrict__ batch_idx, const int* __restrict__ order, int N,
+                       const double* __restrict__ phi_hat, const double* __restrict__ gamma_star,
+                       const double* __restrict__ phi_star, const int* __restrict__ keep_idx, long G0,
+                       double* __restrict__ out) {
+    const long g = g0 + (long)blockIdx.x * 4 + (threadIdx.x >> 5);
+    const int si = blockIdx.y * 32 + (threadIdx.x & 31);
+    if (g >= g1 || si >= N) return;
+    const int s = order[si], b = batch_idx[s];
+    const double x = (double)cnt[g + (long)s * G];
+    const double old_mu = mu_hat[g + (long)s * G];
+    const double new_mu = exp(log(old_mu) - gamma_star[g + (long)b * G]);     // ComBat_seq.R:176
+    out[(keep_idx ? (long)keep_idx[g] : g) + (long)s * G0] = match_one_fast<NI>(x, old_mu, phi_hat[g + (long)b * G], new_mu, phi_star[g]);
 }
 
 // generic per-batch form used by cbs_match_quantiles (explicit new_mu)

@@ -36,9 +36,18 @@ namespace cbs {
 constexpr int MCG_TILE = 128;        // source tile (and the row block of the P/Q layout): 128 genes
 constexpr int MCG_TI = 64;           // target rows per CTA: CTA tile = 64 targets x 128 sources, two CTAs per SM
 constexpr int MCG_KC = 8;            // k-chunk (doubles): the unit of the global layout and of one bulk copy
-constexpr int MCG_SUB = 2;           // k-chunks per pipeline stage (16 doubles of K per hand-over)
-constexpr int MCG_STAGES = 4;
-constexpr int MCG_GPBUF = 4;         // buffers of the per-source-tile (gamma, phi) pairs
+#ifndef MCG_SUB_N                    // (development builds override the ring geometry: tools/build_variants.sh)
+#define MCG_SUB_N 2
+#endif
+#ifndef MCG_STAGES_N
+#define MCG_STAGES_N 4
+#endif
+constexpr int MCG_SUB = MCG_SUB_N;   // k-chunks per pipeline stage (16 doubles of K per hand-over)
+constexpr int MCG_STAGES = MCG_STAGES_N;
+#ifndef MCG_GPBUF_N
+#define MCG_GPBUF_N 4
+#endif
+constexpr int MCG_GPBUF = MCG_GPBUF_N;       // buffers of the per-source-tile (gamma, phi) pairs
 constexpr int MCG_MAX_KC = 64;       // max Chebyshev terms
 constexpr int MCG_SHIFT = 4;         // c: counts below c use the one-hot table
 constexpr int MCG_MT = 2;            // 8-row DMMA tiles per warp along the targets (warp tile = 8*MCG_MT x 64)
@@ -48,7 +57,7 @@ struct McgShape {
     int n;          // samples in the batch
     int Kc;         // Chebyshev terms
     int KT;         // n + Kc + MCG_SHIFT + 1
-    int KTP;        // KT rounded up to a multiple of MCG_KC * MCG_SUB
+    int KTP;        // KT rounded up to a multiple of MCG_KC (the last hand-over of a source tile may hold one k-chunk)
     long rows;      // matrix rows, G rounded up to a multiple of MCG_TILE
     double ulo, uhi;   // range of u = log(r + c)
 };
@@ -134,9 +143,9 @@ k_mcg_prep_src(const double* __restrict__ mu_hat, long G, const int* __restrict_
 
 // ---- target side, step 1: F_i at the Chebyshev nodes.  grid (ceil(G/128), Kc); Fnode is [m*G + i] ----------
 __global__ void __launch_bounds__(128)
-k_mcg_prep_nodes(const int32_t* __restrict__ cnt, long G, const int* __restrict__ cols, McgShape sh,
+k_mcg_prep_nodes(const int32_t* __restrict__ cnt, long G, const int* __restrict__ cols, McgShape sh, long ip0, long ip1,
                  double* __restrict__ Fnode) {
-    const long i = (long)blockIdx.x * blockDim.x + threadIdx.x;
+    const long i = ip0 + (long)blockIdx.x * blockDim.x + threadIdx.x;     // targets [ip0, ip1): this rank's rows of P
     const int m = blockIdx.y;
     const double tn = cospi((m + 0.5) / sh.Kc);
     const double r = exp(0.5 * (sh.ulo + sh.uhi) + 0.5 * (sh.uhi - sh.ulo) * tn) - (double)MCG_SHIFT;
@@ -145,7 +154,7 @@ k_mcg_prep_nodes(const int32_t* __restrict__ cnt, long G, const int* __restrict_
     __shared__ double small[15 - MCG_SHIFT];
     if (threadIdx.x < 15 - MCG_SHIFT) small[threadIdx.x] = lgamma_diff((double)(threadIdx.x + MCG_SHIFT), r);
     __syncthreads();
-    if (i >= G) return;
+    if (i >= G || i >= ip1) return;
     double f = 0;
     for (int t = 0; t < sh.n; ++t) {
         const int x = cnt[i + (long)cols[t] * G];
@@ -160,10 +169,10 @@ k_mcg_prep_nodes(const int32_t* __restrict__ cnt, long G, const int* __restrict_
 // bit pattern of |C_{Kc-1}| + |C_{Kc-2}| (non-negative doubles order like their bit patterns).
 __global__ void __launch_bounds__(128)
 k_mcg_prep_tgt(const int32_t* __restrict__ cnt, long G, const int* __restrict__ cols, McgShape sh,
-               const double* __restrict__ Fnode, const double* __restrict__ dct, double* __restrict__ P,
+               long ip0, long ip1, const double* __restrict__ Fnode, const double* __restrict__ dct, double* __restrict__ P,
                unsigned long long* __restrict__ tail_bits) {
-    const long i = (long)blockIdx.x * blockDim.x + threadIdx.x;
-    if (i >= sh.rows) return;
+    const long i = ip0 + (long)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= ip1) return;
     const int n = sh.n, Kc = sh.Kc;
     if (i >= G) {
         for (int k = 0; k < sh.KTP; ++k) P[mcg_index(sh.rows, i, k)] = 0.0;
@@ -311,7 +320,9 @@ k_mc_gemm(const double* __restrict__ P, const double* __restrict__ Q, const doub
     const long itile = tile0 + blockIdx.x;
     const long NJ = sh.rows / MCG_TILE;
     const long jt0 = NJ * blockIdx.y / gridDim.y, jt1 = NJ * (blockIdx.y + 1) / gridDim.y;
-    const int NKS = sh.KTP / (MCG_KC * MCG_SUB);                  // stages per source tile
+    const int NCH = sh.KTP / MCG_KC;                              // k-chunks per source tile
+    const int NKS = (NCH + MCG_SUB - 1) / MCG_SUB;                // hand-overs (stages) per source tile
+    const int last_sub = NCH - (NKS - 1) * MCG_SUB;               // k-chunks in a tile's last hand-over (1..MCG_SUB)
     const long total = (jt1 - jt0) * NKS;
 
     if (tid == 0) {
@@ -326,9 +337,11 @@ k_mc_gemm(const double* __restrict__ P, const double* __restrict__ Q, const doub
         const long njl = c / NKS; const int nks = (int)(c - njl * NKS);
         const uint32_t p_bytes = MCG_TI * MCG_KC * sizeof(double), q_bytes = MCG_TILE * MCG_KC * sizeof(double);
         double* sb = stage_base + (size_t)ns * MCG_STAGE_DBL;
-        mbar_expect_tx(&full[ns], MCG_SUB * (p_bytes + q_bytes) + (nks == 0 ? (uint32_t)(MCG_TILE * sizeof(double2)) : 0u));
+        const int nsub = (nks == NKS - 1) ? last_sub : MCG_SUB;
+        mbar_expect_tx(&full[ns], nsub * (p_bytes + q_bytes) + (nks == 0 ? (uint32_t)(MCG_TILE * sizeof(double2)) : 0u));
 #pragma unroll
         for (int u = 0; u < MCG_SUB; ++u) {
+            if (u >= nsub) break;
             const size_t kc = (size_t)nks * MCG_SUB + u;
             double* su = sb + u * (MCG_TI + MCG_TILE) * MCG_KC;
             bulk_g2s(su, P + (kc * sh.rows + itile * MCG_TI) * MCG_KC, p_bytes, &full[ns]);
@@ -361,8 +374,10 @@ k_mc_gemm(const double* __restrict__ P, const double* __restrict__ Q, const doub
         int st = 0; uint32_t phase = 0;
         for (long it = 0; it < total; ++it) {
             mbar_wait(&full[st], phase);
+            const int nsub = (kc == NKS - 1) ? last_sub : MCG_SUB;
 #pragma unroll
             for (int u = 0; u < MCG_SUB; ++u) {
+            if (u >= nsub) break;                            // warp-uniform: a tile's last hand-over may be short
             const double* ps = stage_base + (size_t)st * MCG_STAGE_DBL + u * (MCG_TI + MCG_TILE) * MCG_KC;
             const double* qs = ps + MCG_TI * MCG_KC;
 #pragma unroll
@@ -427,6 +442,13 @@ k_mc_gemm(const double* __restrict__ P, const double* __restrict__ Q, const doub
                 // RNA-seq-like data), so every lane group has work: the 8 elements of a column group are evaluated
                 // branch-free and independently (8 interleaved mcg_exp chains keep the FP64 pipe busy) and masked;
                 // one warp vote skips a column group whose 256 pairs are all pruned (far-apart genes).
+#ifdef MCG_DIAG_NO_EPILOGUE                                  // diagnostic build: what the contraction costs without the fold
+#pragma unroll
+                for (int nt = 0; nt < 8; ++nt)
+#pragma unroll
+                    for (int mt = 0; mt < MCG_MT; ++mt) { racc[mt].sw += acc[mt][nt][0] + acc[mt][nt][1]; acc[mt][nt][0] = acc[mt][nt][1] = 0.0; }
+                if (false)
+#endif
 #pragma unroll
                 for (int nt = 0; nt < 8; ++nt) {
                     bool need = false;

@@ -80,6 +80,8 @@ int cbs_set_tuning(const char* key, double value) {
     if (!strcmp(key, "mc_algo")) { if (value < 0 || value > 2) return fail(CBS_EINVAL, "mc_algo must be 0, 1 or 2"); g_mc_algo = (int)value; return CBS_OK; }
     if (!strcmp(key, "mc_tail_tol")) { g_mc_tail_tol = value; return CBS_OK; }
     if (!strcmp(key, "apl_fast")) { g_apl_fast = value != 0; return CBS_OK; }
+    if (!strcmp(key, "glm_scr")) { g_glm_scr = value != 0; return CBS_OK; }
+    if (!strcmp(key, "mq_rows")) { g_mq_rows = (int)value; return CBS_OK; }
     return fail(CBS_EINVAL, "unknown tuning key '%s'", key);
 }
 int cbs_get_diag(const char* key, double* value) {

@@ -138,8 +138,14 @@ static void run_glm_fit(const int32_t* cnt, long G, long g0, long g1, int N, con
     const bool lanes = h_p <= GLM_LANES_PMAX;
     const dim3 lgrid = grid1((g1 - g0) * GLM_LANES, 128);
     auto launch = [&](const double* yadd, double tp, int mode, double* coef, double* fitted, double* alpha) {
-#define CBS_GLM_LANES(PM_) CBS_LAUNCH(k_glm_fit_lanes<PM_>, lgrid, 128, 0, st, cnt, G, g0, g1, d_logoff, yadd, tp, d_phi, \
-                                      d_phi_col, d_design, d_goff, mode, coef, fitted, d_alpha_w, n_alpha, alpha)
+        // one shared-memory copy of the Levenberg work arrays per gene (16 genes per block)
+#define CBS_GLM_LANES(PM_) do { \
+            const size_t smem = g_glm_scr ? (size_t)(128 / GLM_LANES) * lev_scratch_doubles<PM_>() * sizeof(double) : 0; \
+            static bool attr_set = false; \
+            if (!attr_set) { CBS_CUDA(cudaFuncSetAttribute(k_glm_fit_lanes<PM_>, cudaFuncAttributeMaxDynamicSharedMemorySize, \
+                                                           (int)((128 / GLM_LANES) * lev_scratch_doubles<PM_>() * sizeof(double)))); attr_set = true; } \
+            CBS_LAUNCH(k_glm_fit_lanes<PM_>, lgrid, 128, smem, st, cnt, G, g0, g1, d_logoff, yadd, tp, d_phi, \
+                       d_phi_col, d_design, d_goff, mode, coef, fitted, d_alpha_w, n_alpha, alpha, g_glm_scr ? 1 : 0); } while (0)
         if (lanes) {
             if (h_p <= 4) CBS_GLM_LANES(4); else if (h_p <= 8) CBS_GLM_LANES(8); else if (h_p <= 12) CBS_GLM_LANES(12); else CBS_GLM_LANES(16);
         } else
@@ -190,7 +196,8 @@ static void run_mc_batch_direct(const int32_t* cnt, long G, int n, const int* d_
 // *tail_out receives the series' tail estimate (synchronises the stream).
 static bool run_mc_batch_gemm(const int32_t* cnt, long G, int n, const int* d_cols, long i0, long i1, const double* d_mu_hat,
                               const double* d_gamma, const double* d_phi, int mc_mode, double* d_gamma_star,
-                              double* d_phi_star, unsigned long long* d_nfb, cudaStream_t st, double* tail_out) {
+                              double* d_phi_star, unsigned long long* d_nfb, cudaStream_t st, double* tail_out,
+                              cbs_comm* comm = nullptr) {
     double* d_rng = g_dev.get<double>("mcg_range", 2);
     CBS_LAUNCH(k_mcg_phi_range, dim3(1), 256, 0, st, d_phi, G, d_rng);
     double rng[2];
@@ -205,8 +212,8 @@ static bool run_mc_batch_gemm(const int32_t* cnt, long G, int n, const int* d_co
     sh.Kc = mcg_terms(0.5 * (sh.uhi - sh.ulo));
     if (sh.Kc > MCG_MAX_KC) return false;
     sh.KT = n + sh.Kc + MCG_SHIFT + 1;
-    const int kstage = MCG_KC * MCG_SUB;                          // K per pipeline hand-over
-    sh.KTP = std::max((sh.KT + kstage - 1) / kstage * kstage, 2 * kstage);
+    // K is padded to whole 8-wide k-chunks only; at least two full hand-overs per source tile (gamma/phi buffering)
+    sh.KTP = std::max((sh.KT + MCG_KC - 1) / MCG_KC * MCG_KC, 2 * MCG_KC * MCG_SUB);
     static_assert((MCG_GPBUF - 1) * 2 >= MCG_STAGES + 1, "gamma/phi buffers must outlive the stage ring");
     sh.rows = (G + MCG_TILE - 1) / MCG_TILE * MCG_TILE;
     g_last_mc_kc = sh.Kc;
@@ -221,8 +228,12 @@ static bool run_mc_batch_gemm(const int32_t* cnt, long G, int n, const int* d_co
     unsigned long long* d_tail = g_dev.get<unsigned long long>("mcg_tail", 1);
     CBS_CUDA(cudaMemsetAsync(d_tail, 0, sizeof(unsigned long long), st));
     CBS_LAUNCH(k_mcg_prep_src, grid1(sh.rows, 128), 128, 0, st, d_mu_hat, G, d_cols, d_phi, sh, Q);
-    CBS_LAUNCH(k_mcg_prep_nodes, dim3((unsigned)((G + 127) / 128), (unsigned)sh.Kc), 128, 0, st, cnt, G, d_cols, sh, Fn);
-    CBS_LAUNCH(k_mcg_prep_tgt, grid1(sh.rows, 128), 128, 0, st, cnt, G, d_cols, sh, Fn, d_dct, P, d_tail);
+    // P is only needed for this rank's target tiles (Q for all sources)
+    const long ip0 = i1 > i0 ? i0 / MCG_TI * MCG_TI : 0, ip1 = i1 > i0 ? std::min(sh.rows, (i1 + MCG_TI - 1) / MCG_TI * MCG_TI) : 0;
+    if (ip1 > ip0) {
+        CBS_LAUNCH(k_mcg_prep_nodes, dim3((unsigned)((ip1 - ip0 + 127) / 128), (unsigned)sh.Kc), 128, 0, st, cnt, G, d_cols, sh, ip0, ip1, Fn);
+        CBS_LAUNCH(k_mcg_prep_tgt, grid1(ip1 - ip0, 128), 128, 0, st, cnt, G, d_cols, sh, ip0, ip1, Fn, d_dct, P, d_tail);
+    }
     CBS_LAUNCH(k_mcg_pack_gp, grid1(sh.rows, 256), 256, 0, st, d_gamma, d_phi, G, sh.rows, gp);
     if (i1 > i0) {
         const long tile0 = i0 / MCG_TI, ntiles = (i1 - i0 + MCG_TI - 1) / MCG_TI, NJ = sh.rows / MCG_TILE;
@@ -256,6 +267,8 @@ static bool run_mc_batch_gemm(const int32_t* cnt, long G, int n, const int* d_co
         CBS_LAUNCH(k_mcg_finalize, grid1(i1 - i0, 128), 128, 0, st, part, sh.rows, (int)nsplit, i0, i1,
                    mc_mode == CBS_MC_STABLE ? 1 : 0, d_gamma, d_phi, d_gamma_star, d_phi_star, d_nfb);
     }
+    // the series' tail is judged over ALL targets, so that every rank takes the same decision a single GPU would
+    if (comm && comm->world > 1) CBS_NCCL(nccl_api()->AllReduce(d_tail, d_tail, 1, NCCL_UINT64, NCCL_MAX, comm->nccl, st));
     unsigned long long tb = 0;
     CBS_CUDA(cudaMemcpyAsync(&tb, d_tail, sizeof tb, cudaMemcpyDeviceToHost, st));
     CBS_CUDA(cudaStreamSynchronize(st));
@@ -268,12 +281,13 @@ static bool run_mc_batch_gemm(const int32_t* cnt, long G, int n, const int* d_co
 // d_nfb must be zero on entry.
 static void run_mc_batch(const int32_t* cnt, long G, int n, const int* d_cols, long i0, long i1, const double* d_mu_hat,
                          const double* d_gamma, const double* d_phi, int mc_mode, int subset_n, uint64_t seed,
-                         double* d_gamma_star, double* d_phi_star, unsigned long long* d_nfb, cudaStream_t st) {
+                         double* d_gamma_star, double* d_phi_star, unsigned long long* d_nfb, cudaStream_t st,
+                         cbs_comm* comm = nullptr) {
     if (subset_n >= G - 1) subset_n = 0;
     const bool want_gemm = subset_n <= 0 && g_mc_algo != 1 && G >= 2;
     if (want_gemm) {
         double tail = 0;
-        if (run_mc_batch_gemm(cnt, G, n, d_cols, i0, i1, d_mu_hat, d_gamma, d_phi, mc_mode, d_gamma_star, d_phi_star, d_nfb, st, &tail)) {
+        if (run_mc_batch_gemm(cnt, G, n, d_cols, i0, i1, d_mu_hat, d_gamma, d_phi, mc_mode, d_gamma_star, d_phi_star, d_nfb, st, &tail, comm)) {
             g_last_mc_tail = std::max(g_last_mc_tail, tail);
             if (tail <= g_mc_tail_tol || g_mc_algo == 2) return;
             CBS_CUDA(cudaMemsetAsync(d_nfb, 0, sizeof(unsigned long long), st));     // series not converged: redo exactly
