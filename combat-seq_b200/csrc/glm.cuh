@@ -376,7 +376,8 @@ __device__ inline void sytf2_packed(double* a, int n) {
 // so a lookup returns the bits the call would.  With one dispersion per evaluation (the only form the pipeline uses)
 // log(r) and lgamma(r) are loop invariants and are evaluated once per gene instead of once per sample.
 constexpr int LGFACT_N = 2048;
-__device__ inline double apl_gene(const DesignDev& d, const Row& r, const double* __restrict__ lgfact = nullptr) {
+__device__ inline double apl_gene(const DesignDev& d, const Row& r, const double* __restrict__ lgfact = nullptr,
+                                  const double* __restrict__ lgr = nullptr) {      // lgr[y] = lgamma(y + 1/phi), y < LGFACT_N (scalar phi)
     double beta[PMAX], cellbeta[PMAX], wm[PTRI];
     const int p = d.p;
     fit_gene(d, r, beta, cellbeta);
@@ -415,7 +416,8 @@ __device__ inline double apl_gene(const DesignDev& d, const Row& r, const double
         if (phi > 0) {
             const double rr = scalar_phi ? rr_c : 1 / phi, logmur = log(mu + rr);
             const double logrr = scalar_phi ? logrr_c : log(rr), lgrr = scalar_phi ? lgrr_c : lgamma(rr);
-            loglik = y * logmu - y * logmur + rr * logrr - rr * logmur + lgamma(y + rr) - lgy1 - lgrr;
+            const double lgyr = (scalar_phi && lgr && y < (double)LGFACT_N && !r.s.yadd) ? lgr[(int)y] : lgamma(y + rr);
+            loglik = y * logmu - y * logmur + rr * logrr - rr * logmur + lgyr - lgy1 - lgrr;
         } else {
             loglik = y * logmu - mu - lgy1;
         }

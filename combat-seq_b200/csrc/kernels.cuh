@@ -69,7 +69,7 @@ struct AplLaunch {
 __global__ void __launch_bounds__(128)
 k_apl(const int32_t* __restrict__ cnt, long G, long g0, long g1, const double* __restrict__ logoff,
       const DesignDev* __restrict__ designs, const unsigned char* __restrict__ sel, const double* __restrict__ phi_gene,
-      AplLaunch L, double* __restrict__ apl, const double* __restrict__ lgfact) {
+      AplLaunch L, double* __restrict__ apl, const double* __restrict__ lgfact, const double* __restrict__ lgr) {
     const long g = g0 + (long)blockIdx.x * blockDim.x + threadIdx.x;
     const int e = blockIdx.y;
     if (g >= g1) return;
@@ -78,13 +78,21 @@ k_apl(const int32_t* __restrict__ cnt, long G, long g0, long g1, const double* _
     const DesignDev d = designs[di];
     RowSrc src{cnt, G, logoff, nullptr, nullptr, nullptr, phi_gene ? phi_gene[(long)e * G + g] : L.phi[e]};
     Row r(src, g, 0.0);
-    apl[(long)e * G + g] = apl_gene(d, r, lgfact);
+    apl[(long)e * G + g] = apl_gene(d, r, lgfact, (lgr && !phi_gene) ? lgr + (long)e * LGFACT_N : nullptr);
 }
 
 // lgamma(y + 1) for y = 0..LGFACT_N-1 by the device lgamma() itself (see apl_gene)
 __global__ void k_lgfact_init(double* __restrict__ tab) {
     const int i = blockIdx.x * blockDim.x + threadIdx.x;
     if (i < LGFACT_N) tab[i] = lgamma((double)i + 1.0);
+}
+
+// lgamma(y + 1/phi_e) for y = 0..LGFACT_N-1 and every evaluation e of a launch: with one dispersion per evaluation the
+// term depends on the count only, so 2048 calls per evaluation replace one call per gene and sample (same bits).
+__global__ void k_lgr_init(AplLaunch L, double* __restrict__ tab) {      // grid (LGFACT_N / 256, n_evals)
+    const int y = blockIdx.x * blockDim.x + threadIdx.x, e = blockIdx.y;
+    const double rr = 1 / L.phi[e];
+    if (y < LGFACT_N) tab[(long)e * LGFACT_N + y] = lgamma((double)y + rr);
 }
 
 // deterministic chunked sums: partial[e*nchunk + chunk] = sum of apl[e*G + g] over the selected genes of the chunk

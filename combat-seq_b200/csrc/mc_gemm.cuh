@@ -50,7 +50,13 @@ constexpr int MCG_STAGES = MCG_STAGES_N;
 constexpr int MCG_GPBUF = MCG_GPBUF_N;       // buffers of the per-source-tile (gamma, phi) pairs
 constexpr int MCG_MAX_KC = 64;       // max Chebyshev terms
 constexpr int MCG_SHIFT = 4;         // c: counts below c use the one-hot table
-constexpr int MCG_MT = 2;            // 8-row DMMA tiles per warp along the targets (warp tile = 8*MCG_MT x 64)
+constexpr int MCG_MT = 2;            // 8-row DMMA tiles per warp along the targets (warp tile = 8*MCG_MT x 8*MCG_NT)
+#ifndef MCG_NT_N                     // (development builds: 4 = 64 x 64 CTA tiles, 16 x 32 warp tiles, three CTAs per SM)
+#define MCG_NT_N 8
+#endif
+constexpr int MCG_NT = MCG_NT_N;     // 8-column DMMA tiles per warp along the sources
+constexpr int MCG_TJ = 2 * 8 * MCG_NT;   // source columns per CTA tile (two warps side by side): 128
+constexpr int MCG_CTAS = MCG_NT == 8 ? 2 : 3;   // CTAs per SM the kernel is sized for
 constexpr int MCG_THREADS = 32 * (MCG_TI / (8 * MCG_MT)) * 2;     // warps: (64 / warp rows) x 2 = 8
 
 struct McgShape {
@@ -142,24 +148,32 @@ k_mcg_prep_src(const double* __restrict__ mu_hat, long G, const int* __restrict_
 }
 
 // ---- target side, step 1: F_i at the Chebyshev nodes.  grid (ceil(G/128), Kc); Fnode is [m*G + i] ----------
-__global__ void __launch_bounds__(128)
-k_mcg_prep_nodes(const int32_t* __restrict__ cnt, long G, const int* __restrict__ cols, McgShape sh, long ip0, long ip1,
-                 double* __restrict__ Fnode) {
-    const long i = ip0 + (long)blockIdx.x * blockDim.x + threadIdx.x;     // targets [ip0, ip1): this rank's rows of P
-    const int m = blockIdx.y;
+// The summand depends on the count and the node only, so it is tabulated once per batch for counts below MCG_LGTAB
+// (k_mcg_node_table: Kc x MCG_LGTAB evaluations instead of Kc x G x n_b; the table holds the bits the direct call
+// returns) and the sweep over the samples becomes a lookup.  Larger counts take the direct call.
+constexpr int MCG_LGTAB = 8192;
+__global__ void __launch_bounds__(256)
+k_mcg_node_table(McgShape sh, double* __restrict__ tab) {          // grid (MCG_LGTAB / 256, Kc)
+    const int x = blockIdx.x * blockDim.x + threadIdx.x, m = blockIdx.y;
     const double tn = cospi((m + 0.5) / sh.Kc);
     const double r = exp(0.5 * (sh.ulo + sh.uhi) + 0.5 * (sh.uhi - sh.ulo) * tn) - (double)MCG_SHIFT;
-    // r is the same for the whole block (one node): the small counts, which would each cost two lgamma() calls, come
-    // from an 11-entry table built with the very same expression
-    __shared__ double small[15 - MCG_SHIFT];
-    if (threadIdx.x < 15 - MCG_SHIFT) small[threadIdx.x] = lgamma_diff((double)(threadIdx.x + MCG_SHIFT), r);
-    __syncthreads();
+    tab[(long)m * MCG_LGTAB + x] = x >= MCG_SHIFT ? lgamma_diff((double)x, r) : 0.0;
+}
+
+__global__ void __launch_bounds__(128)
+k_mcg_prep_nodes(const int32_t* __restrict__ cnt, long G, const int* __restrict__ cols, McgShape sh, long ip0, long ip1,
+                 const double* __restrict__ tab, double* __restrict__ Fnode) {
+    const long i = ip0 + (long)blockIdx.x * blockDim.x + threadIdx.x;     // targets [ip0, ip1): this rank's rows of P
+    const int m = blockIdx.y;
     if (i >= G || i >= ip1) return;
+    const double tn = cospi((m + 0.5) / sh.Kc);
+    const double r = exp(0.5 * (sh.ulo + sh.uhi) + 0.5 * (sh.uhi - sh.ulo) * tn) - (double)MCG_SHIFT;
+    const double* __restrict__ t_m = tab + (long)m * MCG_LGTAB;
     double f = 0;
     for (int t = 0; t < sh.n; ++t) {
         const int x = cnt[i + (long)cols[t] * G];
-        if (x >= 15) f += lgamma_diff((double)x, r);
-        else if (x >= MCG_SHIFT) f += small[x - MCG_SHIFT];
+        if (x >= MCG_LGTAB) f += lgamma_diff((double)x, r);
+        else if (x >= MCG_SHIFT) f += __ldg(t_m + x);
     }
     Fnode[(long)m * G + i] = f;
 }
@@ -211,14 +225,20 @@ __device__ __forceinline__ void mbar_init(uint64_t* bar, int count) {
 __device__ __forceinline__ void mbar_expect_tx(uint64_t* bar, uint32_t bytes) {
     asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(smem_u32(bar)), "r"(bytes) : "memory");
 }
+// A warp that finds its stage not landed yet backs off for ~200 ns instead of re-polling at once: the polls of the warps
+// that run ahead of the ring (every warp but the slowest, in steady state) otherwise take issue slots from the warps that
+// feed the FP64 units (measured on C5-sized batches: 34.1 -> 33.5 ms per launch; a try_wait suspend hint gave 33.9).
+#ifndef MCG_WAIT_SLEEP
+#define MCG_WAIT_SLEEP 200
+#endif
 __device__ __forceinline__ void mbar_wait(uint64_t* bar, uint32_t parity) {
-    asm volatile(
-        "{\n\t.reg .pred p;\n\t"
-        "WAIT_%=:\n\t"
-        "mbarrier.try_wait.parity.shared::cta.b64 p, [%0], %1;\n\t"
-        "@p bra DONE_%=;\n\t"
-        "bra WAIT_%=;\n\t"
-        "DONE_%=:\n\t}" ::"r"(smem_u32(bar)), "r"(parity) : "memory");
+    for (;;) {
+        uint32_t ok;
+        asm volatile("{\n\t.reg .pred p;\n\tmbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n\tselp.u32 %0, 1, 0, p;\n\t}"
+                     : "=r"(ok) : "r"(smem_u32(bar)), "r"(parity) : "memory");
+        if (ok) return;
+        __nanosleep(MCG_WAIT_SLEEP);
+    }
 }
 __device__ __forceinline__ void bulk_g2s(void* dst, const void* src, uint32_t bytes, uint64_t* bar) {
     asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];"
@@ -288,9 +308,9 @@ __device__ __forceinline__ double mcg_exp(double x, const double* __restrict__ T
 constexpr int MCG_CONSUMER_WARPS = MCG_THREADS / 32;
 constexpr int MCG_WI = MCG_CONSUMER_WARPS / 2;      // warps along the targets
 constexpr int MCG_BLOCK = MCG_CONSUMER_WARPS * 32;
-constexpr int MCG_STAGE_DBL = MCG_SUB * (MCG_TI + MCG_TILE) * MCG_KC;                             // doubles per stage
+constexpr int MCG_STAGE_DBL = MCG_SUB * (MCG_TI + MCG_TJ) * MCG_KC;                             // doubles per stage
 constexpr size_t MCG_SMEM_STAGE = (size_t)MCG_STAGE_DBL * sizeof(double);                         // SUB x (P chunk + Q chunk)
-constexpr size_t MCG_SMEM_GP = (size_t)MCG_GPBUF * MCG_TILE * 2 * sizeof(double);
+constexpr size_t MCG_SMEM_GP = (size_t)MCG_GPBUF * MCG_TJ * 2 * sizeof(double);
 constexpr size_t MCG_SMEM_BYTES = MCG_STAGES * MCG_SMEM_STAGE + MCG_SMEM_GP + 2 * MCG_STAGES * sizeof(uint64_t) + 64   // full[] + done[]
                                   + 64 * sizeof(double);                                                                 // exp2 table
 static_assert(MCG_THREADS == MCG_CONSUMER_WARPS * 32, "consumer thread count");
@@ -304,7 +324,7 @@ static_assert(MCG_THREADS == MCG_CONSUMER_WARPS * 32, "consumer thread count");
 // (FP64 pipe) therefore never holds up the refills the other warps are waiting for, and the other warp of its
 // scheduler keeps the tensor pipe busy meanwhile.  part[(split*rows + i)] receives the partial sums of target row i.
 template <int STABLE>
-__global__ void __launch_bounds__(MCG_BLOCK, 2)
+__global__ void __launch_bounds__(MCG_BLOCK, MCG_CTAS)
 k_mc_gemm(const double* __restrict__ P, const double* __restrict__ Q, const double2* __restrict__ gp, McgShape sh,
           long tile0, McAcc* __restrict__ part) {
     extern __shared__ __align__(128) unsigned char smem_raw[];
@@ -318,7 +338,7 @@ k_mc_gemm(const double* __restrict__ P, const double* __restrict__ Q, const doub
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     const int wi = warp % MCG_WI, wj = warp / MCG_WI;
     const long itile = tile0 + blockIdx.x;
-    const long NJ = sh.rows / MCG_TILE;
+    const long NJ = sh.rows / MCG_TJ;
     const long jt0 = NJ * blockIdx.y / gridDim.y, jt1 = NJ * (blockIdx.y + 1) / gridDim.y;
     const int NCH = sh.KTP / MCG_KC;                              // k-chunks per source tile
     const int NKS = (NCH + MCG_SUB - 1) / MCG_SUB;                // hand-overs (stages) per source tile
@@ -335,22 +355,22 @@ k_mc_gemm(const double* __restrict__ P, const double* __restrict__ Q, const doub
     auto issue = [&](long c) {
         const int ns = (int)(c % MCG_STAGES);
         const long njl = c / NKS; const int nks = (int)(c - njl * NKS);
-        const uint32_t p_bytes = MCG_TI * MCG_KC * sizeof(double), q_bytes = MCG_TILE * MCG_KC * sizeof(double);
+        const uint32_t p_bytes = MCG_TI * MCG_KC * sizeof(double), q_bytes = MCG_TJ * MCG_KC * sizeof(double);
         double* sb = stage_base + (size_t)ns * MCG_STAGE_DBL;
         const int nsub = (nks == NKS - 1) ? last_sub : MCG_SUB;
-        mbar_expect_tx(&full[ns], nsub * (p_bytes + q_bytes) + (nks == 0 ? (uint32_t)(MCG_TILE * sizeof(double2)) : 0u));
+        mbar_expect_tx(&full[ns], nsub * (p_bytes + q_bytes) + (nks == 0 ? (uint32_t)(MCG_TJ * sizeof(double2)) : 0u));
 #pragma unroll
         for (int u = 0; u < MCG_SUB; ++u) {
             if (u >= nsub) break;
             const size_t kc = (size_t)nks * MCG_SUB + u;
-            double* su = sb + u * (MCG_TI + MCG_TILE) * MCG_KC;
+            double* su = sb + u * (MCG_TI + MCG_TJ) * MCG_KC;
             bulk_g2s(su, P + (kc * sh.rows + itile * MCG_TI) * MCG_KC, p_bytes, &full[ns]);
-            bulk_g2s(su + MCG_TI * MCG_KC, Q + (kc * sh.rows + (jt0 + njl) * MCG_TILE) * MCG_KC, q_bytes, &full[ns]);
+            bulk_g2s(su + MCG_TI * MCG_KC, Q + (kc * sh.rows + (jt0 + njl) * MCG_TJ) * MCG_KC, q_bytes, &full[ns]);
         }
         // gamma/phi of source tile njl go to buffer njl % MCG_GPBUF, last read in the epilogue of tile njl - MCG_GPBUF,
         // which every warp has finished before it leaves hand-over njl * NKS - MCG_STAGES
         // ((MCG_GPBUF - 1) * NKS >= MCG_STAGES + 1 is guaranteed by the host: KTP >= 2 stages).
-        if (nks == 0) bulk_g2s(gp_s + (njl % MCG_GPBUF) * MCG_TILE, gp + (jt0 + njl) * MCG_TILE, MCG_TILE * sizeof(double2), &full[ns]);
+        if (nks == 0) bulk_g2s(gp_s + (njl % MCG_GPBUF) * MCG_TJ, gp + (jt0 + njl) * MCG_TJ, MCG_TJ * sizeof(double2), &full[ns]);
     };
     if (tid == 0)
         for (long c = 0; c < total && c < MCG_STAGES; ++c) issue(c);
@@ -362,14 +382,14 @@ k_mc_gemm(const double* __restrict__ P, const double* __restrict__ Q, const doub
 
     {
         // ---- MMA warps ----
-        double acc[MCG_MT][8][2];
+        double acc[MCG_MT][MCG_NT][2];
 #pragma unroll
         for (int mt = 0; mt < MCG_MT; ++mt)
 #pragma unroll
-            for (int nt = 0; nt < 8; ++nt) acc[mt][nt][0] = acc[mt][nt][1] = 0.0;
+            for (int nt = 0; nt < MCG_NT; ++nt) acc[mt][nt][0] = acc[mt][nt][1] = 0.0;
         // fragment addressing: row = lane/4 within an 8-row MMA tile, column = lane%4 within a 4-wide k-step
         const int swz = ((frow >> 1) & 1) << 2;             // tile bases are multiples of 8, so bit 1 of the row is frow's
-        const int a_off = (wi * (8 * MCG_MT) + frow) * MCG_KC, b_off = (wj * 64 + frow) * MCG_KC;
+        const int a_off = (wi * (8 * MCG_MT) + frow) * MCG_KC, b_off = (wj * (8 * MCG_NT) + frow) * MCG_KC;
         long jl = 0; int kc = 0;
         int st = 0; uint32_t phase = 0;
         for (long it = 0; it < total; ++it) {
@@ -378,20 +398,20 @@ k_mc_gemm(const double* __restrict__ P, const double* __restrict__ Q, const doub
 #pragma unroll
             for (int u = 0; u < MCG_SUB; ++u) {
             if (u >= nsub) break;                            // warp-uniform: a tile's last hand-over may be short
-            const double* ps = stage_base + (size_t)st * MCG_STAGE_DBL + u * (MCG_TI + MCG_TILE) * MCG_KC;
+            const double* ps = stage_base + (size_t)st * MCG_STAGE_DBL + u * (MCG_TI + MCG_TJ) * MCG_KC;
             const double* qs = ps + MCG_TI * MCG_KC;
 #pragma unroll
             for (int ks = 0; ks < 2; ++ks) {
                 const int col = (ks * 4 + fcol) ^ swz;
-                double a[MCG_MT], b[8];
+                double a[MCG_MT], b[MCG_NT];
 #pragma unroll
                 for (int mt = 0; mt < MCG_MT; ++mt) a[mt] = ps[a_off + mt * 8 * MCG_KC + col];
 #pragma unroll
-                for (int nt = 0; nt < 8; ++nt) b[nt] = qs[b_off + nt * 8 * MCG_KC + col];
+                for (int nt = 0; nt < MCG_NT; ++nt) b[nt] = qs[b_off + nt * 8 * MCG_KC + col];
 #pragma unroll
                 for (int mt = 0; mt < MCG_MT; ++mt)
 #pragma unroll
-                    for (int nt = 0; nt < 8; ++nt) dmma884(acc[mt][nt][0], acc[mt][nt][1], a[mt], b[nt]);
+                    for (int nt = 0; nt < MCG_NT; ++nt) dmma884(acc[mt][nt][0], acc[mt][nt][1], a[mt], b[nt]);
             }
             }
             __syncwarp();
@@ -407,16 +427,16 @@ k_mc_gemm(const double* __restrict__ P, const double* __restrict__ Q, const doub
 
             if (++kc == NKS) {                               // last k-chunk of source tile jl: fold the weights in
                 const long jt = jt0 + jl;
-                const double2* g2 = gp_s + (jl % MCG_GPBUF) * MCG_TILE;
-                if (jt == (itile * MCG_TI) / MCG_TILE) {     // mu[-i,]: the gene itself is not a source  helper_seq.R:11-14
-                    const int ioff = (int)((itile * MCG_TI) % MCG_TILE);
+                const double2* g2 = gp_s + (jl % MCG_GPBUF) * MCG_TJ;
+                if (jt == (itile * MCG_TI) / MCG_TJ) {     // mu[-i,]: the gene itself is not a source  helper_seq.R:11-14
+                    const int ioff = (int)((itile * MCG_TI) % MCG_TJ);
 #pragma unroll
                     for (int mt = 0; mt < MCG_MT; ++mt)
 #pragma unroll
-                        for (int nt = 0; nt < 8; ++nt)
+                        for (int nt = 0; nt < MCG_NT; ++nt)
 #pragma unroll
                             for (int e = 0; e < 2; ++e)
-                                if (wj * 64 + nt * 8 + 2 * fcol + e == ioff + wi * (8 * MCG_MT) + mt * 8 + frow) acc[mt][nt][e] = -INFINITY;
+                                if (wj * (8 * MCG_NT) + nt * 8 + 2 * fcol + e == ioff + wi * (8 * MCG_MT) + mt * 8 + frow) acc[mt][nt][e] = -INFINITY;
                 }
                 // running maximum of every target row (shared by the 4 lanes that hold the row) -> prune threshold
                 double thr[MCG_MT];
@@ -424,7 +444,7 @@ k_mc_gemm(const double* __restrict__ P, const double* __restrict__ Q, const doub
                 for (int mt = 0; mt < MCG_MT; ++mt) {
                     double mx = fmax(acc[mt][0][0], acc[mt][0][1]);
 #pragma unroll
-                    for (int nt = 1; nt < 8; ++nt) mx = fmax(mx, fmax(acc[mt][nt][0], acc[mt][nt][1]));
+                    for (int nt = 1; nt < MCG_NT; ++nt) mx = fmax(mx, fmax(acc[mt][nt][0], acc[mt][nt][1]));
                     mx = fmax(mx, __shfl_xor_sync(0xffffffffu, mx, 1));
                     mx = fmax(mx, __shfl_xor_sync(0xffffffffu, mx, 2));
                     if (STABLE) {
@@ -444,18 +464,18 @@ k_mc_gemm(const double* __restrict__ P, const double* __restrict__ Q, const doub
                 // one warp vote skips a column group whose 256 pairs are all pruned (far-apart genes).
 #ifdef MCG_DIAG_NO_EPILOGUE                                  // diagnostic build: what the contraction costs without the fold
 #pragma unroll
-                for (int nt = 0; nt < 8; ++nt)
+                for (int nt = 0; nt < MCG_NT; ++nt)
 #pragma unroll
                     for (int mt = 0; mt < MCG_MT; ++mt) { racc[mt].sw += acc[mt][nt][0] + acc[mt][nt][1]; acc[mt][nt][0] = acc[mt][nt][1] = 0.0; }
                 if (false)
 #endif
 #pragma unroll
-                for (int nt = 0; nt < 8; ++nt) {
+                for (int nt = 0; nt < MCG_NT; ++nt) {
                     bool need = false;
 #pragma unroll
                     for (int mt = 0; mt < MCG_MT; ++mt) need |= (acc[mt][nt][0] > thr[mt]) | (acc[mt][nt][1] > thr[mt]);
                     if (__any_sync(0xffffffffu, need)) {
-                        const double2 gp0 = g2[wj * 64 + nt * 8 + 2 * fcol], gp1 = g2[wj * 64 + nt * 8 + 2 * fcol + 1];
+                        const double2 gp0 = g2[wj * (8 * MCG_NT) + nt * 8 + 2 * fcol], gp1 = g2[wj * (8 * MCG_NT) + nt * 8 + 2 * fcol + 1];
                         double w0[MCG_MT], w1[MCG_MT];
 #pragma unroll
                         for (int mt = 0; mt < MCG_MT; ++mt) {

@@ -26,8 +26,14 @@ static void launch_apl(const int32_t* cnt, long G, long g0, long g1, const doubl
         L.n_evals = (int)std::min<size_t>(APL_MAX_EVALS, jobs.size() - e0);
         for (int e = 0; e < L.n_evals; ++e) { L.design[e] = jobs[e0 + e].design; L.phi[e] = jobs[e0 + e].phi; }
         dim3 grid((unsigned)((g1 - g0 + 127) / 128), (unsigned)L.n_evals);
+        const double* lgr = nullptr;
+        if (g_apl_fast && !phi_gene) {
+            double* t = g_dev.get<double>("lgr", (size_t)APL_MAX_EVALS * LGFACT_N);
+            CBS_LAUNCH(k_lgr_init, dim3(LGFACT_N / 256, (unsigned)L.n_evals), 256, 0, st, L, t);
+            lgr = t;
+        }
         CBS_LAUNCH(k_apl, grid, 128, 0, st, cnt, G, g0, g1, logoff, designs, sel,
-                   phi_gene ? phi_gene + e0 * G : nullptr, L, d_apl + e0 * G, g_apl_fast ? (const double*)lgfact : (const double*)nullptr);
+                   phi_gene ? phi_gene + e0 * G : nullptr, L, d_apl + e0 * G, g_apl_fast ? (const double*)lgfact : (const double*)nullptr, lgr);
     }
 }
 
@@ -231,17 +237,19 @@ static bool run_mc_batch_gemm(const int32_t* cnt, long G, int n, const int* d_co
     // P is only needed for this rank's target tiles (Q for all sources)
     const long ip0 = i1 > i0 ? i0 / MCG_TI * MCG_TI : 0, ip1 = i1 > i0 ? std::min(sh.rows, (i1 + MCG_TI - 1) / MCG_TI * MCG_TI) : 0;
     if (ip1 > ip0) {
-        CBS_LAUNCH(k_mcg_prep_nodes, dim3((unsigned)((ip1 - ip0 + 127) / 128), (unsigned)sh.Kc), 128, 0, st, cnt, G, d_cols, sh, ip0, ip1, Fn);
+        double* d_lgtab = g_dev.get<double>("mcg_lgtab", (size_t)sh.Kc * MCG_LGTAB);
+        CBS_LAUNCH(k_mcg_node_table, dim3(MCG_LGTAB / 256, (unsigned)sh.Kc), 256, 0, st, sh, d_lgtab);
+        CBS_LAUNCH(k_mcg_prep_nodes, dim3((unsigned)((ip1 - ip0 + 127) / 128), (unsigned)sh.Kc), 128, 0, st, cnt, G, d_cols, sh, ip0, ip1, d_lgtab, Fn);
         CBS_LAUNCH(k_mcg_prep_tgt, grid1(ip1 - ip0, 128), 128, 0, st, cnt, G, d_cols, sh, ip0, ip1, Fn, d_dct, P, d_tail);
     }
     CBS_LAUNCH(k_mcg_pack_gp, grid1(sh.rows, 256), 256, 0, st, d_gamma, d_phi, G, sh.rows, gp);
     if (i1 > i0) {
-        const long tile0 = i0 / MCG_TI, ntiles = (i1 - i0 + MCG_TI - 1) / MCG_TI, NJ = sh.rows / MCG_TILE;
+        const long tile0 = i0 / MCG_TI, ntiles = (i1 - i0 + MCG_TI - 1) / MCG_TI, NJ = sh.rows / MCG_TJ;
         int sms = 148;
         { int dev = 0; cudaGetDevice(&dev); cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev); }
         // source-tile splits: at least ~8 waves of CTAs (two CTAs per SM), and among the candidates the split count whose
         // last wave is fullest (2811 CTAs on 296 slots waste half a wave; 4690 waste 1 %)
-        const long slots = 2L * sms;
+        const long slots = (long)MCG_CTAS * sms;
         const long lo = std::max(1L, (8 * slots + ntiles - 1) / ntiles), hi = std::min(32L, std::max(1L, NJ / 4));
         long nsplit = std::min(lo, hi);
         double best = 0;

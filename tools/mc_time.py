@@ -19,4 +19,4 @@ for algo in algos:
         prof = L.profile_dump(); L.profile_enable(False)
         tot = sum(v[0] for v in prof.values())
         print("algo %d mode %d G=%d n=%d: kernels %.2f ms, terms/s %.3g, fallback %d, Kc %d" % (algo, mode, G, n, tot, G * (G - 1.0) * n / tot * 1e3, r[2], L.get_diag("mc_terms")),
-              {k: round(v[0], 3) for k, v in prof.items()})
+              {k: round(v[0], 3) for k, v in prof.items()}, "checksum %.12e %.12e" % (float(np.nansum(r[0])), float(np.nansum(r[1]))))
