@@ -462,6 +462,40 @@ k_mc_gemm(const double* __restrict__ P, const double* __restrict__ Q, const doub
                 // RNA-seq-like data), so every lane group has work: the 8 elements of a column group are evaluated
                 // branch-free and independently (8 interleaved mcg_exp chains keep the FP64 pipe busy) and masked;
                 // one warp vote skips a column group whose 256 pairs are all pruned (far-apart genes).
+#ifdef MCG_EPI_COMPACT
+                // Compacted fold (development build): about one pair in eight survives the pruning, so instead of 32
+                // masked exp() per thread every lane walks the list of its own survivors; the warp loops until the
+                // lane with the most survivors is done.  The accumulators are parked in local memory for the walk
+                // (registers cannot be indexed by a run-time value).
+#pragma unroll
+                for (int mt = 0; mt < MCG_MT; ++mt) {
+                    double la[MCG_NT * 2];
+                    unsigned mask = 0;
+#pragma unroll
+                    for (int nt = 0; nt < MCG_NT; ++nt)
+#pragma unroll
+                        for (int e = 0; e < 2; ++e) {
+                            const double L = acc[mt][nt][e];
+                            la[nt * 2 + e] = L;
+                            mask |= (L > thr[mt]) ? (1u << (nt * 2 + e)) : 0u;
+                            acc[mt][nt][e] = 0.0;
+                        }
+                    const double mref = STABLE ? racc[mt].m : 0.0;
+                    double sw = racc[mt].sw, sg = racc[mt].sg, sp = racc[mt].sp;
+                    while (__any_sync(0xffffffffu, mask != 0u)) {
+                        if (mask != 0u) {
+                            const int q = __ffs(mask) - 1;
+                            mask &= mask - 1u;
+                            const double L = la[q];
+                            const double2 gq = g2[wj * (8 * MCG_NT) + (q >> 1) * 8 + 2 * fcol + (q & 1)];
+                            const double w = mcg_exp(L - mref, exp_tab);
+                            sw += w; sg = fma(w, gq.x, sg); sp = fma(w, gq.y, sp);
+                        }
+                    }
+                    racc[mt].sw = sw; racc[mt].sg = sg; racc[mt].sp = sp;
+                }
+                if (false)
+#endif
 #ifdef MCG_DIAG_NO_EPILOGUE                                  // diagnostic build: what the contraction costs without the fold
 #pragma unroll
                 for (int nt = 0; nt < MCG_NT; ++nt)
