@@ -344,7 +344,19 @@ CBS_HD NbCdf nb_cdf_pmf(double k, double size, double prob, double q) {
 // (1.6 MB: seven copies of the continued fraction, two of the general nmath routines), far beyond the instruction
 // cache, and its warps diverge onto different copies (ncu, round 1: "no instruction" = 24 % of the stall cycles).
 // Same arithmetic, same results; only the call structure differs.
-static __host__ __device__ __noinline__ NbCdf nb_cdf_pmf_ni(double k, double size, double prob, double q) { return nb_cdf_pmf(k, size, prob, q); }
+static __host__ __device__ __noinline__ double bfrac_fast_ni(double a, double b, double x, double y, double lambda) { return bfrac_fast(a, b, x, y, lambda); }
+static __host__ __device__ __noinline__ NbCdf nb_cdf_pmf_ni(double k, double size, double prob, double q) {
+    NbCdf o;                                                  // nb_cdf_pmf with ONE copy of the continued fraction
+    const double a = size, b = k + 1.;
+    const double brc = brcomp(a, b, prob, q);
+    o.pmf = brc / (q * (a + k));
+    const double lambda = (a > b) ? (a + b) * q - b : a - (a + b) * prob;
+    if (brc == 0.) { o.F = (lambda >= 0) ? 0.0 : 1.0; return o; }
+    const bool fwd = lambda >= 0;
+    const double cf = bfrac_fast_ni(fwd ? a : b, fwd ? b : a, fwd ? prob : q, fwd ? q : prob, fwd ? lambda : -lambda);
+    o.F = fwd ? brc * cf : 0.5 - brc * cf + 0.5;
+    return o;
+}
 static __host__ __device__ __noinline__ double pnbinom_mu_ni(double x, double size, double mu) { return pnbinom_mu(x, size, mu); }
 static __host__ __device__ __noinline__ double qnbinom_mu_ni(double p, double size, double mu) { return qnbinom_mu(p, size, mu); }
 template <bool NI> CBS_HD NbCdf nb_cdf_pmf_t(double k, double size, double prob, double q) {
