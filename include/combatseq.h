@@ -75,6 +75,13 @@ int         cbs_fp64_mma_peak(double* tflops);   /* same for the FP64 tensor pip
  *                  contraction with the Chebyshev expansion of the lgamma term
  *   "mc_tail_tol"  largest accepted Chebyshev tail estimate in log-likelihood units (default 1e-8); a batch that
  *                  exceeds it is redone with the direct kernel when mc_algo = 0
+ *   "apl_fast"     1 (default) = lgamma tables, hoisted log/lgamma of 1/phi and product-form mu in the APL kernel
+ *                  (last-place differences); 0 = one call per sample
+ *   "glm_scr"      1 (default) = Levenberg work arrays of the lane-group GLM kernel in shared memory; 0 = local memory
+ *                  (same bits)
+ *   "mq_rows"      thread mapping / call structure of match_quantiles: 3 (default) = warp per gene, continued fraction
+ *                  out of line; 2 = same, inlined; 1 = 8 x 32 tiles through shared memory; 4 = tiles, out of line
+ *                  (same bits; development A/B, tools/ab_time.py)
  * cbs_get_diag keys: "mc_tail" (largest tail estimate since the last reset), "mc_terms" (Chebyshev terms of the
  * last contraction launch); cbs_get_diag("reset", &x) clears them. */
 int         cbs_set_tuning(const char* key, double value);
