@@ -34,7 +34,8 @@ class CbsInput(C.Structure):
                 ("counts_f64", C.c_void_p), ("counts_i32", C.c_void_p), ("batch_idx", i32p), ("mod", f64p),
                 ("use_fallback", u8p), ("shrink", C.c_int32), ("shrink_disp", C.c_int32),
                 ("gene_subset_n", C.c_int32), ("seed", C.c_uint64), ("mc_mode", C.c_int32),
-                ("device", C.c_int32), ("comm", C.c_void_p), ("counts_on_device", C.c_int32)]
+                ("device", C.c_int32), ("comm", C.c_void_p), ("counts_on_device", C.c_int32),
+                ("n_gpus", C.c_int32)]
 
 
 class CbsOutput(C.Structure):
@@ -238,11 +239,13 @@ def comm_destroy(h):
 
 # ---- the whole pipeline ------------------------------------------------------------------------------------------
 def combat_seq_raw(counts, batch_idx, mod, shrink=False, shrink_disp=False, gene_subset_n=0, seed=0,
-                   mc_mode=CBS_MC_REFERENCE, use_fallback=None, device=-1, comm=None, want=("adjusted",),
+                   mc_mode=CBS_MC_REFERENCE, use_fallback=None, device=-1, comm=None, n_gpus=1, want=("adjusted",),
                    counts_dev_ptr=None, adjusted_dev_ptr=None, shape=None, adjusted_out=None):
     """cbs_combat_seq().  `want` selects the optional outputs; returns a dict.  counts may be float64 or int32
     (column-major is used as is; anything else is copied).  counts_dev_ptr/adjusted_dev_ptr (+ shape) run the
-    device-resident variant used by bench.py's kernel-only timing."""
+    device-resident variant used by bench.py's kernel-only timing.  n_gpus: 1 = one device, k > 1 = single-process
+    sharding over devices 0..k-1 (one host thread each inside the library), 0 = all visible devices.  With comm (one
+    process per GPU) only rows [row_begin, row_end) of the matrix outputs are this rank's; the rest is NaN."""
     inp = CbsInput(); out = CbsOutput()
     if counts_dev_ptr is not None:
         G0, N = shape
@@ -266,7 +269,7 @@ def combat_seq_raw(counts, batch_idx, mod, shrink=False, shrink_disp=False, gene
         fb = np.ascontiguousarray(use_fallback, dtype=np.uint8); inp.use_fallback = _p(fb, u8p)
     inp.shrink, inp.shrink_disp = int(bool(shrink)), int(bool(shrink_disp))
     inp.gene_subset_n, inp.seed, inp.mc_mode = int(gene_subset_n or 0), int(seed), int(mc_mode)
-    inp.device = int(device); inp.comm = comm
+    inp.device = int(device); inp.comm = comm; inp.n_gpus = int(n_gpus)
     res = {}
     shapes = dict(adjusted=(G0, N), phi_hat=(G0, B), gamma_hat=(G0, B), gamma_star=(G0, B), phi_star=(G0, B),
                   mu_hat=(G0, N))
@@ -278,7 +281,7 @@ def combat_seq_raw(counts, batch_idx, mod, shrink=False, shrink_disp=False, gene
                 assert adjusted_out.flags.f_contiguous and adjusted_out.dtype == np.float64 and adjusted_out.shape == (G0, N)
                 res[k] = adjusted_out
             else:
-                res[k] = np.empty(shapes[k], order="F")
+                res[k] = np.full(shapes[k], np.nan, order="F") if comm is not None else np.empty(shapes[k], order="F")
             setattr(out, k, res[k].ctypes.data_as(C.c_void_p) if k == "adjusted" else _p(res[k]))
     if adjusted_dev_ptr is not None:
         out.adjusted = C.c_void_p(adjusted_dev_ptr); out.adjusted_on_device = 1

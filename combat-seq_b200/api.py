@@ -19,15 +19,18 @@ _ERRORS = {
 
 
 def ComBat_seq(counts, batch, group=None, covar_mod=None, full_mod=True, shrink=False, shrink_disp=False,
-               gene_subset_n=None, *, seed=0, mc_mode="reference", device=-1, comm=None, verbose=True,
+               gene_subset_n=None, *, seed=0, mc_mode="reference", device=-1, n_gpus=1, comm=None, verbose=True,
                return_details=False):
     """Adjust a gene x sample count matrix for batch effects (negative-binomial ComBat).
 
     counts, batch, group, covar_mod, full_mod, shrink, shrink_disp (R: shrink.disp), gene_subset_n
     (R: gene.subset.n) have the reference's meaning.  Extras (keyword-only, defaults = reference behaviour):
-    seed (gene_subset_n sampling), mc_mode "reference" | "stable", device, comm (gene sharding), verbose
-    (the reference's cat() messages), return_details (also return every intermediate).
+    seed (gene_subset_n sampling), mc_mode "reference" | "stable", device, n_gpus (single-process sharding over
+    devices 0..n_gpus-1; 0 = all visible), comm (one process per GPU, see below), verbose (the reference's cat()
+    messages), return_details (also return every intermediate).
     Returns a float64 matrix with the shape of `counts` (ComBat_seq.R:199-203); pandas row/column labels are kept.
+    With comm= this process is one rank of a gene-sharded job and owns rows [row_begin, row_end) only: the function
+    then always returns the details dict (rows of other ranks are NaN; "row_begin"/"row_end" give the range).
     """
     def say(msg):
         if verbose:
@@ -65,14 +68,14 @@ def ComBat_seq(counts, batch, group=None, covar_mod=None, full_mod=True, shrink=
         res = _lib.combat_seq_raw(counts, d.batch_idx, d.mod, shrink=shrink, shrink_disp=shrink_disp,
                                   gene_subset_n=gene_subset_n or 0, seed=seed,
                                   mc_mode=_lib.CBS_MC_STABLE if mc_mode == "stable" else _lib.CBS_MC_REFERENCE,
-                                  device=device, comm=comm, want=want)
+                                  device=device, comm=comm, n_gpus=n_gpus, want=want)
     except _lib.CombatSeqError as e:
         raise _ERRORS.get(e.code, RuntimeError)(str(e)) from None
     adj = res["adjusted"]
     if labels is not None:
         import pandas as pd
         adj = pd.DataFrame(adj, index=labels[0], columns=labels[1])
-    if return_details:
+    if return_details or comm is not None:
         res["adjusted"] = adj
         res["design"] = d
         return res

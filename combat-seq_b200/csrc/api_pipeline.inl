@@ -38,7 +38,12 @@ __global__ void k_scatter_rows(const double* __restrict__ src, long G, const int
     if (i < G) dst[keep_idx[i] + (long)c * G0] = src[i + (long)c * G];
 }
 
-static int g_cache_device = -1;
+static const char* bad_counts_message(int bad) {
+    if (bad & 1) return "NA counts not allowed";                   // edgeR DGEList's wording
+    if (bad & 2) return "Negative counts not allowed";             // edgeR DGEList's wording
+    if (bad & 4) return "non-integer counts are not supported: this engine works on int32 counts (round them first)";
+    return "counts above 2^31 - 1 are not supported";
+}
 
 template <class T>
 static void pipeline(const cbs_input* in, cbs_output* out, const T* h_or_d_counts) {
@@ -50,7 +55,7 @@ static void pipeline(const cbs_input* in, cbs_output* out, const T* h_or_d_count
     double stage[CBS_N_STAGES] = {0};
     const double t_start = now_ms();
     double t0 = t_start;
-    cudaStream_t st = 0;
+    cudaStream_t st = t_ctx->st;
     auto lap = [&](int which) { CBS_CUDA(cudaStreamSynchronize(st)); const double t = now_ms(); stage[which] += t - t0; t0 = t; };
 
     // ---- H2D ----
@@ -60,18 +65,27 @@ static void pipeline(const cbs_input* in, cbs_output* out, const T* h_or_d_count
     int* d_bidx = upload(g_dev, "batch_idx", in->batch_idx, (size_t)N, st);
     lap(CBS_ST_H2D);
 
-    // ---- a1: zero filter (ComBat_seq.R:33-40) ----
+    // ---- a1: zero filter (ComBat_seq.R:33-40) + input validation ----
     unsigned char* d_keep = g_dev.get<unsigned char>("keep", (size_t)G0);
-    CBS_LAUNCH(k_keep_mask<T>, grid1(G0, 128), 128, 0, st, d_in, G0, N, d_bidx, B, d_keep);
+    int* d_bad = g_dev.get<int>("bad_counts", 1);
+    CBS_CUDA(cudaMemsetAsync(d_bad, 0, sizeof(int), st));
+    CBS_LAUNCH(k_keep_mask<T>, grid1(G0, 128), 128, 0, st, d_in, G0, N, d_bidx, B, d_keep, d_bad);
     std::vector<unsigned char> keep(G0);
+    int bad = 0;
     CBS_CUDA(cudaMemcpyAsync(keep.data(), d_keep, (size_t)G0, cudaMemcpyDeviceToHost, st));
+    CBS_CUDA(cudaMemcpyAsync(&bad, d_bad, sizeof(int), cudaMemcpyDeviceToHost, st));
     CBS_CUDA(cudaStreamSynchronize(st));
+    if (bad) { fail(CBS_EINVAL, "%s", bad_counts_message(bad)); throw CbsError{CBS_EINVAL}; }
     std::vector<int> keep_idx;
     keep_idx.reserve(G0);
     for (long g = 0; g < G0; ++g) if (keep[g]) keep_idx.push_back((int)g);
     const long G = (long)keep_idx.size();
     if (out->keep) memcpy(out->keep, keep.data(), (size_t)G0);
     if (G == 0) { fail(CBS_EINVAL, "no genes left after the zero filter"); throw CbsError{CBS_EINVAL}; }
+    if (in->shrink && in->gene_subset_n > 0 && in->gene_subset_n > G - 1) {     // sample(1:(nrow(dat)-1), n)  helper_seq.R:19
+        fail(CBS_EINVAL, "cannot take a sample larger than the population when 'replace = FALSE'");
+        throw CbsError{CBS_EINVAL};
+    }
     int* d_keep_idx = upload(g_dev, "keep_idx", keep_idx.data(), (size_t)G, st);
 
     // ---- a1/a2: int32 compaction + library sizes (DGEList, ComBat_seq.R:43) ----
@@ -157,16 +171,8 @@ static void pipeline(const cbs_input* in, cbs_output* out, const T* h_or_d_count
         allgather_rows(d_phi_hat, G, B, g0, g1, comm, st);
         d_gamma_star = g_dev.get<double>("gamma_star", (size_t)G * B);
         double* d_ps = g_dev.get<double>("phi_star_mat", (size_t)G * B);
-        unsigned long long* d_nfb = g_dev.get<unsigned long long>("mc_nfb", (size_t)B);
-        CBS_CUDA(cudaMemsetAsync(d_nfb, 0, (size_t)B * sizeof(unsigned long long), st));
-        for (int b = 0; b < B; ++b) {
-            int* d_cols = upload(g_dev, "mc_cols", bcols[b].data(), bcols[b].size(), st);
-            run_mc_batch(d_cnt, G, (int)bcols[b].size(), d_cols, g0, g1, d_mu_hat, d_gamma_hat + (size_t)b * G,
-                         d_phi_hat + (size_t)b * G, in->mc_mode, in->gene_subset_n > 0 ? in->gene_subset_n : 0,
-                         in->seed + (uint64_t)b, d_gamma_star + (size_t)b * G, d_ps + (size_t)b * G, d_nfb + b, st, comm);
-            CBS_CUDA(cudaStreamSynchronize(st));      // mc_cols / mc_* scratch is reused by the next batch
-        }
-        CBS_CUDA(cudaMemcpy(nfb.data(), d_nfb, (size_t)B * sizeof(unsigned long long), cudaMemcpyDeviceToHost));
+        run_mc_stage(d_cnt, G, B, bcols, g0, g1, d_mu_hat, d_gamma_hat, d_phi_hat, in->mc_mode,
+                     in->gene_subset_n > 0 ? in->gene_subset_n : 0, in->seed, d_gamma_star, d_ps, nfb.data(), st, comm);
         if (in->shrink_disp) d_phi_star_mat = d_ps;                                // ComBat_seq.R:162-165
     }
     if (out->n_mc_fallback) for (int b = 0; b < B; ++b) out->n_mc_fallback[b] = (int64_t)nfb[b];
@@ -189,18 +195,8 @@ static void pipeline(const cbs_input* in, cbs_output* out, const T* h_or_d_count
             order.reserve(N);
             for (int b = 0; b < B; ++b) order.insert(order.end(), bcols[b].begin(), bcols[b].end());
             int* d_order = upload(g_dev, "mq_order", order.data(), (size_t)N, st);
-            if (g_mq_rows == 3)
-                CBS_LAUNCH(k_match_quantiles_warp<true>, dim3((unsigned)((g1 - g0 + 3) / 4), (unsigned)((N + 31) / 32)), 128, 0, st, d_cnt, G,
-                           g0, g1, d_mu_hat, d_bidx, d_order, N, d_phi_hat, d_gamma_star, d_phi_star, d_keep_idx, G0, d_adj);
-            else if (g_mq_rows == 2)
-                CBS_LAUNCH(k_match_quantiles_warp<false>, dim3((unsigned)((g1 - g0 + 3) / 4), (unsigned)((N + 31) / 32)), 128, 0, st, d_cnt, G,
-                           g0, g1, d_mu_hat, d_bidx, d_order, N, d_phi_hat, d_gamma_star, d_phi_star, d_keep_idx, G0, d_adj);
-            else if (g_mq_rows == 4)
-                CBS_LAUNCH(k_match_quantiles_rows<true>, dim3((unsigned)((g1 - g0 + 7) / 8), (unsigned)((N + 31) / 32)), 256, 0, st, d_cnt, G,
-                           g0, g1, d_mu_hat, d_bidx, d_order, N, d_phi_hat, d_gamma_star, d_phi_star, d_keep_idx, G0, d_adj);
-            else
-                CBS_LAUNCH(k_match_quantiles_rows<false>, dim3((unsigned)((g1 - g0 + 7) / 8), (unsigned)((N + 31) / 32)), 256, 0, st, d_cnt, G,
-                           g0, g1, d_mu_hat, d_bidx, d_order, N, d_phi_hat, d_gamma_star, d_phi_star, d_keep_idx, G0, d_adj);
+            launch_match_quantiles(d_cnt, G, g0, g1, d_mu_hat, d_bidx, d_order, N, d_phi_hat, d_gamma_star, d_phi_star,
+                                   d_keep_idx, G0, d_adj, st);
         }
     }
     lap(CBS_ST_MATCH_QUANTILES);
@@ -234,6 +230,74 @@ static void pipeline(const cbs_input* in, cbs_output* out, const T* h_or_d_count
     if (out->stage_ms) memcpy(out->stage_ms, stage, sizeof stage);
 }
 
+// ---- single-process multi-GPU (cbs_input.n_gpus): one host thread per device, an NCCL communicator kept per process ----
+struct InprocComms { int n = 0; std::vector<cbs_comm> ranks; };
+static InprocComms g_inproc;
+
+void release_inproc_comms() {
+    NcclApi* a = g_inproc.n ? nccl_api() : nullptr;
+    for (auto& c : g_inproc.ranks) if (a && c.nccl) { cudaSetDevice(c.device); a->CommDestroy(c.nccl); }
+    g_inproc.ranks.clear();
+    g_inproc.n = 0;
+}
+
+static void ensure_inproc_comms(int n) {
+    if (g_inproc.n == n) return;
+    release_inproc_comms();
+    NcclApi* a = nccl_api();
+    if (!a) throw CbsError{CBS_ENCCL};
+    Id128 id;
+    CBS_NCCL(a->GetUniqueId(&id));
+    g_inproc.ranks.assign(n, cbs_comm{nullptr, 0, n, 0});
+    std::vector<int> rc(n, 0);
+    std::vector<std::thread> th;
+    for (int r = 0; r < n; ++r)
+        th.emplace_back([&, r] {
+            if (cudaSetDevice(r) != cudaSuccess) { rc[r] = -1; return; }
+            void* c = nullptr;
+            rc[r] = a->CommInitRank(&c, n, id, r);
+            g_inproc.ranks[r] = cbs_comm{c, r, n, r};
+        });
+    for (auto& t : th) t.join();
+    for (int r = 0; r < n; ++r)
+        if (rc[r] != 0) {
+            fail(CBS_ENCCL, "ncclCommInitRank failed on device %d (%d)", r, rc[r]);
+            g_inproc.n = n; release_inproc_comms();
+            throw CbsError{CBS_ENCCL};
+        }
+    g_inproc.n = n;
+}
+
+template <class T>
+static int pipeline_inproc(const cbs_input* in, cbs_output* out, const T* counts, int n) {
+    ensure_inproc_comms(n);
+    for (int r = 0; r < n; ++r) ctx_for_device(r);              // contexts are created under the library mutex
+    std::vector<int> code(n, CBS_OK);
+    std::vector<std::string> msg(n);
+    std::vector<cbs_output> outs(n, *out);
+    std::vector<std::thread> th;
+    for (int r = 0; r < n; ++r)
+        th.emplace_back([&, r] {
+            try {
+                enter_device(r);
+                cbs_input ir = *in;
+                ir.comm = &g_inproc.ranks[r];
+                ir.device = r;
+                if (r != 0) {                                   // per-call vectors come from rank 0; matrices are written by row range
+                    outs[r].keep = nullptr; outs[r].lib_size = nullptr; outs[r].disp_common = nullptr;
+                    outs[r].stage_ms = nullptr; outs[r].n_mc_fallback = nullptr;
+                }
+                pipeline<T>(&ir, &outs[r], counts);
+                CBS_CUDA(cudaStreamSynchronize(t_ctx->st));
+            } catch (const CbsError& e) { code[r] = e.code; msg[r] = g_err; cudaDeviceSynchronize(); cudaGetLastError(); }
+              catch (const std::exception& e) { code[r] = CBS_EINVAL; msg[r] = e.what(); }
+        });
+    for (auto& t : th) t.join();
+    for (int r = 0; r < n; ++r) if (code[r] != CBS_OK) return fail(code[r], "%s", msg[r].c_str());
+    out->row_begin = 0; out->row_end = in->G0;
+    return CBS_OK;
+}
+
 }  // namespace cbs
 
 extern "C" int cbs_shard_range(int64_t G, int32_t rank, int32_t world, int64_t* g0, int64_t* g1) {
@@ -253,6 +317,9 @@ extern "C" int cbs_combat_seq(const cbs_input* in, cbs_output* out) {
     if (!in->batch_idx || !in->mod) return fail(CBS_EINVAL, "batch_idx and mod are required");
     if (in->B < 2) return fail(CBS_EINVAL, "ComBat-seq needs at least 2 batches");
     if (in->B > 128) return fail(CBS_EINVAL, "at most 128 batches are supported");
+    if (in->n_gpus < 0) return fail(CBS_EINVAL, "n_gpus must be >= 0");
+    if (in->n_gpus != 1 && (in->comm || in->counts_on_device || out->adjusted_on_device))
+        return fail(CBS_EINVAL, "n_gpus != 1 (single-process multi-GPU) needs comm == NULL and host buffers");
     const int p = in->B + in->p_mod - 1;
     if (p > PMAX) return fail(CBS_EINVAL, "design has %d columns; this build supports up to %d", p, PMAX);
     std::vector<int> nb(in->B, 0);
@@ -279,12 +346,20 @@ extern "C" int cbs_combat_seq(const cbs_input* in, cbs_output* out) {
         }
     }
     CBS_NEED_GPU();
-    CBS_ENTRY_BEGIN
-    int dev = in->comm ? in->comm->device : in->device;
-    if (dev >= 0) CBS_CUDA(cudaSetDevice(dev));
-    CBS_CUDA(cudaGetDevice(&dev));
-    if (g_cache_device != dev) { g_dev.release(); g_cache_device = dev; }
-    if (in->counts_f64) pipeline<double>(in, out, in->counts_f64);
-    else pipeline<int32_t>(in, out, in->counts_i32);
+    std::lock_guard<std::mutex> lock_(g_mutex);
+    try {
+        int n = in->n_gpus;
+        if (n == 0) n = cbs_device_count();
+        if (n > cbs_device_count()) return fail(CBS_EINVAL, "n_gpus = %d but only %d CUDA devices are visible", n, cbs_device_count());
+        if (n > 1) {
+            int cur = 0;
+            cudaGetDevice(&cur);
+            const int rc = in->counts_f64 ? pipeline_inproc<double>(in, out, in->counts_f64, n) : pipeline_inproc<int32_t>(in, out, in->counts_i32, n);
+            cudaSetDevice(cur);
+            return rc;
+        }
+        enter_device(in->comm ? in->comm->device : in->device);
+        if (in->counts_f64) pipeline<double>(in, out, in->counts_f64);
+        else pipeline<int32_t>(in, out, in->counts_i32);
     CBS_ENTRY_END
 }

@@ -1,5 +1,4 @@
 // api_subsystems.inl — per-subsystem C-ABI entry points (host buffers in/out).  Included by combatseq.cu.
-#include "stages.inl"
 
 namespace cbs {
 
@@ -25,7 +24,7 @@ static int nb_elementwise(int what, int64_t n, const double* a, const double* si
     double* ds = upload(g_dev, "ew_size", size, (size_t)n);
     double* dm = upload(g_dev, "ew_mu", mu, (size_t)n);
     double* dout = g_dev.get<double>("ew_out", (size_t)n);
-    CBS_LAUNCH(k_nb_elementwise, grid1(n, 128), 128, 0, 0, what, (long)n, da, ds, dm, dout);
+    launch_nb_elementwise(what, (long)n, da, ds, dm, dout, 0);
     CBS_CUDA(cudaMemcpy(out, dout, (size_t)n * sizeof(double), cudaMemcpyDeviceToHost));
     CBS_ENTRY_END
 }
@@ -163,23 +162,20 @@ int cbs_mc_int(int64_t G, int32_t n, const int32_t* counts, const double* mu, co
                int64_t* n_fallback) {
     CBS_NEED_GPU();
     if (G < 1 || n < 1 || !counts || !mu || !gamma || !phi || !gamma_star || !phi_star) return fail(CBS_EINVAL, "null pointer / bad size");
+    if (gene_subset_n > 0 && gene_subset_n > G - 1) return fail(CBS_EINVAL, "cannot take a sample larger than the population when 'replace = FALSE'");
     CBS_ENTRY_BEGIN
     int32_t* d_cnt = upload(g_dev, "cnt", counts, (size_t)G * n);
     double* d_mu = upload(g_dev, "mu_hat", mu, (size_t)G * n);
     double* d_g = upload(g_dev, "gamma_hat", gamma, (size_t)G);
     double* d_p = upload(g_dev, "phi_hat", phi, (size_t)G);
-    std::vector<int> cols(n);
-    std::iota(cols.begin(), cols.end(), 0);
-    int* d_cols = upload(g_dev, "mc_cols", cols.data(), (size_t)n);
+    std::vector<std::vector<int>> bcols(1, std::vector<int>(n));
+    std::iota(bcols[0].begin(), bcols[0].end(), 0);
     double* d_gs = g_dev.get<double>("gamma_star", (size_t)G);
     double* d_ps = g_dev.get<double>("phi_star_mat", (size_t)G);
-    unsigned long long* d_nfb = g_dev.get<unsigned long long>("mc_nfb", 1);
-    CBS_CUDA(cudaMemset(d_nfb, 0, sizeof(unsigned long long)));
-    run_mc_batch(d_cnt, G, n, d_cols, 0, G, d_mu, d_g, d_p, mc_mode, gene_subset_n > 0 ? gene_subset_n : 0, seed, d_gs, d_ps, d_nfb, 0);
+    unsigned long long nfb = 0;
+    run_mc_stage(d_cnt, G, 1, bcols, 0, G, d_mu, d_g, d_p, mc_mode, gene_subset_n > 0 ? gene_subset_n : 0, seed, d_gs, d_ps, &nfb, 0, nullptr);
     CBS_CUDA(cudaMemcpy(gamma_star, d_gs, (size_t)G * sizeof(double), cudaMemcpyDeviceToHost));
     CBS_CUDA(cudaMemcpy(phi_star, d_ps, (size_t)G * sizeof(double), cudaMemcpyDeviceToHost));
-    unsigned long long nfb = 0;
-    CBS_CUDA(cudaMemcpy(&nfb, d_nfb, sizeof nfb, cudaMemcpyDeviceToHost));
     if (n_fallback) *n_fallback = (int64_t)nfb;
     CBS_ENTRY_END
 }
@@ -197,8 +193,7 @@ int cbs_match_quantiles(int64_t G, int32_t n, const int32_t* counts, const doubl
     double* d_ophi = upload(g_dev, "phi_hat", old_phi, (size_t)G);
     double* d_nphi = upload(g_dev, "phi_star", new_phi, (size_t)G);
     double* d_out = g_dev.get<double>("adjusted", (size_t)G * n);
-    CBS_LAUNCH(k_match_quantiles_plain, dim3((unsigned)((G + 127) / 128), (unsigned)n), 128, 0, 0, d_cnt, (long)G, (int)n,
-               d_omu, d_ophi, d_nmu, d_nphi, d_out);
+    launch_match_quantiles_plain(d_cnt, (long)G, (int)n, d_omu, d_ophi, d_nmu, d_nphi, d_out, 0);
     CBS_CUDA(cudaMemcpy(adjusted, d_out, (size_t)G * n * sizeof(double), cudaMemcpyDeviceToHost));
     CBS_ENTRY_END
 }

@@ -3,34 +3,37 @@
 // Drop-in numeric body of ComBat_seq() (/root/reference/ComBat_seq.R:33-203) and of its helpers
 // monte_carlo_int_NB / match_quantiles (/root/reference/helper_seq.R:8-64).  There is no CPU path: without a
 // CUDA device every compute entry returns CBS_ENOGPU.
-#include "common.cuh"
-#include "host_design.hpp"
-#include "kernels.cuh"
-#include "mc.cuh"
-#include "mc_gemm.cuh"
+#include "engine.hpp"
+#include "prep_kernels.cuh"
 #include <dlfcn.h>
 #include <chrono>
 #include <mutex>
-#include <numeric>
+#include <thread>
+#include <memory>
 
 namespace cbs {
 
 thread_local char g_err[1024] = "";
 std::atomic<uint64_t> g_launches{0};
 static std::mutex g_mutex;          // one call at a time per process (the R caller is single-threaded anyway)
-static DevCache g_dev;
-static PinCache g_pin;
+Tuning g_tune;
+Diag g_diag;
+thread_local DevCtx* t_ctx = nullptr;
+static std::map<int, std::unique_ptr<DevCtx>> g_ctx;        // one context per device ordinal (guarded by g_mutex)
 
-// ---- tuning knobs (cbs_set_tuning) ----------------------------------------------------------------------------
-static int g_mc_algo = 0;            // 0 = auto (tensor-core contraction when gene.subset.n is NULL), 1 = direct, 2 = contraction
-static int g_glm_scr = 1;            // 1 = Levenberg work arrays of the lane-group GLM kernel in shared memory (one copy per gene)
-static int g_mq_rows = 3;            // match_quantiles: 3 = warp per gene, out-of-line continued fraction (fastest, same bits); 2 = same, inlined;
-                                     // 1 = 8x32 tiles via shared memory, inlined; 4 = tiles, out-of-line
-static int g_apl_fast = 1;           // 1 = lgamma(y+1) table + hoisted log(r)/lgamma(r) in the APL kernel (same bits), 0 = per-sample calls
-static double g_mc_tail_tol = 1e-8;  // largest accepted Chebyshev tail estimate (log-likelihood units)
-static double g_last_mc_tail = 0;    // diagnostics: largest tail estimate of the last Monte-Carlo stage
-static int g_last_mc_kc = 0;         // diagnostics: Chebyshev terms used by the last contraction launch
+void release_inproc_comms();
 
+DevCtx* ctx_for_device(int device) {
+    auto& p = g_ctx[device];
+    if (!p) { p.reset(new DevCtx); p->device = device; }
+    return p.get();
+}
+// make `device` (or the current device when < 0) current and select its context for this thread
+static void enter_device(int device) {
+    if (device >= 0) CBS_CUDA(cudaSetDevice(device));
+    CBS_CUDA(cudaGetDevice(&device));
+    t_ctx = ctx_for_device(device);
+}
 
 static double now_ms() {
     using namespace std::chrono;
@@ -62,18 +65,6 @@ NcclApi* nccl_api() {
     }
     return &api;
 }
-#define CBS_NCCL(call)                                                                              \
-    do {                                                                                            \
-        int r_ = (call);                                                                            \
-        if (r_ != 0) {                                                                              \
-            NcclApi* a_ = nccl_api();                                                               \
-            fail(CBS_ENCCL, "NCCL error %d (%s) at %s:%d", r_,                                      \
-                 (a_ && a_->GetErrorString) ? a_->GetErrorString(r_) : "?", __FILE__, __LINE__);    \
-            throw CbsError{CBS_ENCCL};                                                              \
-        }                                                                                           \
-    } while (0)
-constexpr int NCCL_INT8 = 0, NCCL_UINT64 = 5, NCCL_FLOAT64 = 8, NCCL_SUM = 0, NCCL_MAX = 2;   // ncclDataType_t / ncclRedOp_t values (nccl.h)
-
 static bool have_gpu() {
     int n = 0;
     if (cudaGetDeviceCount(&n) != cudaSuccess) { cudaGetLastError(); return false; }
@@ -82,54 +73,45 @@ static bool have_gpu() {
 #define CBS_NEED_GPU() do { if (!have_gpu()) return fail(CBS_ENOGPU, "no CUDA device visible: libcombatseq has no CPU path"); } while (0)
 
 // ---------------------------------------------------------------------------------------------------
-// Device copy of a HostDesign: one packed allocation per design (a few KB), tracked for release after the call.
-struct DesignSet {
-    std::vector<void*> allocs;
-    DesignDev* d_array = nullptr;      // device array of DesignDev
-    std::vector<DesignDev> h_array;
-    ~DesignSet() { for (void* p : allocs) cudaFree(p); }
-    void add(const HostDesign& h) {
-        auto up = [&](const void* src, size_t bytes) -> void* {
-            void* p = nullptr;
-            CBS_CUDA(cudaMalloc(&p, bytes ? bytes : 8));
-            allocs.push_back(p);
-            if (bytes) CBS_CUDA(cudaMemcpy(p, src, bytes, cudaMemcpyHostToDevice));
-            return p;
-        };
-        DesignDev d;
-        d.n = h.n; d.p = h.p; d.oneway = h.oneway; d.ncls = h.ncls;
-        d.col = (const int*)up(h.col.data(), h.col.size() * sizeof(int));
-        d.cell_start = (const int*)up(h.cell_start.data(), h.cell_start.size() * sizeof(int));
-        d.minv = (const double*)up(h.minv.data(), h.minv.size() * sizeof(double));
-        d.rowptr = (const int*)up(h.rowptr.data(), h.rowptr.size() * sizeof(int));
-        d.cidx = (const int*)up(h.cidx.data(), h.cidx.size() * sizeof(int));
-        d.cval = (const double*)up(h.cval.data(), h.cval.size() * sizeof(double));
-        d.start = (const double*)up(h.start.data(), h.start.size() * sizeof(double));
-        h_array.push_back(d);
-    }
-    void finish() {
+void DesignSet::add(const HostDesign& h) {
+    auto up = [&](const void* src, size_t bytes) -> void* {
         void* p = nullptr;
-        CBS_CUDA(cudaMalloc(&p, h_array.size() * sizeof(DesignDev) + 8));
+        CBS_CUDA(cudaMalloc(&p, bytes ? bytes : 8));
         allocs.push_back(p);
-        CBS_CUDA(cudaMemcpy(p, h_array.data(), h_array.size() * sizeof(DesignDev), cudaMemcpyHostToDevice));
-        d_array = (DesignDev*)p;
-    }
-};
-
-template <class T>
-static T* upload(DevCache& c, const std::string& name, const T* src, size_t count, cudaStream_t st = 0) {
-    T* p = c.get<T>(name, count ? count : 1);
-    if (count) CBS_CUDA(cudaMemcpyAsync(p, src, count * sizeof(T), cudaMemcpyHostToDevice, st));
-    return p;
+        if (bytes) CBS_CUDA(cudaMemcpy(p, src, bytes, cudaMemcpyHostToDevice));
+        return p;
+    };
+    DesignDev d;
+    d.n = h.n; d.p = h.p; d.oneway = h.oneway; d.ncls = h.ncls;
+    d.col = (const int*)up(h.col.data(), h.col.size() * sizeof(int));
+    d.cell_start = (const int*)up(h.cell_start.data(), h.cell_start.size() * sizeof(int));
+    d.minv = (const double*)up(h.minv.data(), h.minv.size() * sizeof(double));
+    d.rowptr = (const int*)up(h.rowptr.data(), h.rowptr.size() * sizeof(int));
+    d.cidx = (const int*)up(h.cidx.data(), h.cidx.size() * sizeof(int));
+    d.cval = (const double*)up(h.cval.data(), h.cval.size() * sizeof(double));
+    d.start = (const double*)up(h.start.data(), h.start.size() * sizeof(double));
+    h_array.push_back(d);
+}
+void DesignSet::finish() {
+    void* p = nullptr;
+    CBS_CUDA(cudaMalloc(&p, h_array.size() * sizeof(DesignDev) + 8));
+    allocs.push_back(p);
+    CBS_CUDA(cudaMemcpy(p, h_array.data(), h_array.size() * sizeof(DesignDev), cudaMemcpyHostToDevice));
+    d_array = (DesignDev*)p;
 }
 
-static inline dim3 grid1(long n, int block) { return dim3((unsigned)((n + block - 1) / block)); }
+void shard_range(long G, int rank, int world, long* g0, long* g1) {
+    long per = (G + world - 1) / world;
+    per = (per + APL_CHUNK - 1) / APL_CHUNK * APL_CHUNK;
+    *g0 = std::min(G, (long)rank * per);
+    *g1 = std::min(G, (long)(rank + 1) * per);
+}
 
 }  // namespace cbs
 
 using namespace cbs;
 
-#define CBS_ENTRY_BEGIN std::lock_guard<std::mutex> lock_(g_mutex); try {
+#define CBS_ENTRY_BEGIN std::lock_guard<std::mutex> lock_(g_mutex); try { enter_device(-1);
 #define CBS_ENTRY_END                                                                               \
     } catch (const CbsError& e) { cudaDeviceSynchronize(); cudaGetLastError(); return e.code; }     \
       catch (const std::bad_alloc&) { return fail(CBS_ENOMEM, "host allocation failed"); }          \
@@ -148,7 +130,21 @@ const char* cbs_last_error(void) { return g_err; }
 uint64_t cbs_kernel_launches(void) { return g_launches.load(); }
 int cbs_shutdown(void) {
     std::lock_guard<std::mutex> lock_(g_mutex);
-    if (have_gpu()) { cudaDeviceSynchronize(); g_dev.release(); g_pin.release(); }
+    release_inproc_comms();
+    if (have_gpu()) {
+        int cur = 0;
+        cudaGetDevice(&cur);
+        for (auto& kv : g_ctx) {
+            cudaSetDevice(kv.first);
+            cudaDeviceSynchronize();
+            kv.second->cache.release(); kv.second->pin.release();
+            for (auto& e : kv.second->events) cudaEventDestroy(e.second);
+            kv.second->events.clear();
+        }
+        cudaSetDevice(cur);
+    }
+    g_ctx.clear();
+    t_ctx = nullptr;
     return CBS_OK;
 }
 

@@ -51,7 +51,7 @@ struct CbsError { int code; };   // thrown inside the library only; every extern
 cudaEvent_t prof_begin(const char* name, cudaStream_t st);   // nullptr when profiling is off
 void prof_end(cudaEvent_t begin, cudaStream_t st);
 
-// Grow-only cache of named device buffers (per process, current device).  Released by cbs_shutdown().
+// Grow-only cache of named device buffers (one per device context).  Released by cbs_shutdown().
 class DevCache {
   public:
     void* get(const std::string& name, size_t bytes) {
@@ -122,3 +122,38 @@ struct cbs_comm {
     void* nccl;        // ncclComm_t
     int rank, world, device;
 };
+
+namespace cbs {
+
+// Everything the library keeps per CUDA device: the buffer cache, the stream the stages run on and the set of
+// kernels whose function attributes have been set on THIS device (function attributes are per device, so a
+// process-wide "done" flag would leave the second device of an in-process multi-GPU call unconfigured).
+struct DevCtx {
+    int device = -1;
+    cudaStream_t st = 0;
+    DevCache cache;
+    PinCache pin;
+    std::map<std::string, cudaEvent_t> events;               // named events (no timing), created on first use
+    cudaEvent_t event(const std::string& name) {
+        auto it = events.find(name);
+        if (it != events.end()) return it->second;
+        cudaEvent_t e = nullptr;
+        CBS_CUDA(cudaEventCreateWithFlags(&e, cudaEventDisableTiming));
+        events[name] = e;
+        return e;
+    }
+    std::map<std::pair<const void*, int>, int> func_attr;    // (kernel, attribute) -> value set on this device
+    void set_func_attr(const void* func, cudaFuncAttribute attr, int value) {
+        auto key = std::make_pair(func, (int)attr);
+        auto it = func_attr.find(key);
+        if (it != func_attr.end() && it->second >= value) return;
+        CBS_CUDA(cudaFuncSetAttribute(func, attr, value));
+        func_attr[key] = value;
+    }
+};
+extern thread_local DevCtx* t_ctx;        // context of the device this host thread is driving (set by the C-ABI entry)
+DevCtx* ctx_for_device(int device);       // creates the context on first use; caller holds the library mutex
+
+}  // namespace cbs
+#define g_dev (cbs::t_ctx->cache)
+#define g_pin (cbs::t_ctx->pin)

@@ -124,17 +124,25 @@ __global__ void __launch_bounds__(256)
 k_mc_direct(const int32_t* __restrict__ cnt, long G, int n, const int* __restrict__ cols, long i0, long i1,
             const double* __restrict__ A, const double* __restrict__ cj, const double* __restrict__ rj,
             const double* __restrict__ lgr, const double* __restrict__ di, const double* __restrict__ gamma,
-            const double* __restrict__ phi, int stable, int subset_n, uint64_t seed,
+            const double* __restrict__ phi, int stable, int subset_n, uint64_t seed, int xs_shared,
             double* __restrict__ gamma_star, double* __restrict__ phi_star, unsigned long long* __restrict__ n_fallback) {
-    extern __shared__ double xs[];                    // [MC_TI][n]
+    extern __shared__ double xs[];                    // [MC_TI][n] when xs_shared (64 n bytes), else unused
     __shared__ McAcc red[8][MC_TI];
     const long ib = i0 + (long)blockIdx.x * MC_TI;
-    for (int k = threadIdx.x; k < MC_TI * n; k += blockDim.x) {
-        const int ti = k / n, t = k - ti * n;
-        const long i = ib + ti;
-        xs[k] = (i < i1) ? (double)cnt[i + (long)cols[t] * G] : 0.0;
+    if (xs_shared) {
+        for (int k = threadIdx.x; k < MC_TI * n; k += blockDim.x) {
+            const int ti = k / n, t = k - ti * n;
+            const long i = ib + ti;
+            xs[k] = (i < i1) ? (double)cnt[i + (long)cols[t] * G] : 0.0;
+        }
     }
     __syncthreads();
+    // count of target ti at the batch's t-th sample (batches too wide for shared memory: straight from L1/L2)
+    auto xat = [&](int ti, int t) -> double {
+        if (xs_shared) return xs[ti * n + t];
+        const long i = ib + ti;
+        return (i < i1) ? (double)cnt[i + (long)cols[t] * G] : 0.0;
+    };
     McAcc acc[MC_TI];
 #pragma unroll
     for (int ti = 0; ti < MC_TI; ++ti) { acc[ti].m = stable ? -INFINITY : 0.0; acc[ti].sw = acc[ti].sg = acc[ti].sp = 0.0; }
@@ -149,7 +157,7 @@ k_mc_direct(const int32_t* __restrict__ cnt, long G, int n, const int* __restric
                 const double a = A[(long)t * G + j];
 #pragma unroll
                 for (int ti = 0; ti < MC_TI; ++ti) {
-                    const double x = xs[ti * n + t];
+                    const double x = xat(ti, t);
                     L[ti] += x * a + (x == 0.0 ? lg0 : lgamma_pos(x + r));
                 }
             }
@@ -173,7 +181,7 @@ k_mc_direct(const int32_t* __restrict__ cnt, long G, int n, const int* __restric
                 const double r = rj[j], lg0 = lgr[j];
                 double L = 0.0;
                 for (int t = 0; t < n; ++t) {
-                    const double x = xs[ti * n + t];
+                    const double x = xat(ti, t);
                     L += x * A[(long)t * G + j] + (x == 0.0 ? lg0 : lgamma_pos(x + r));
                 }
                 mc_add(acc[ti], L + cj[j] + di[i], gamma[j], phi[j], stable);

@@ -30,12 +30,10 @@
 #include <cstdint>
 #include <cmath>
 #include "mc.cuh"
+#include "mc_shape.hpp"
 
 namespace cbs {
 
-constexpr int MCG_TILE = 128;        // source tile (and the row block of the P/Q layout): 128 genes
-constexpr int MCG_TI = 64;           // target rows per CTA: CTA tile = 64 targets x 128 sources, two CTAs per SM
-constexpr int MCG_KC = 8;            // k-chunk (doubles): the unit of the global layout and of one bulk copy
 #ifndef MCG_SUB_N                    // (development builds override the ring geometry: tools/build_variants.sh)
 #define MCG_SUB_N 2
 #endif
@@ -49,7 +47,6 @@ constexpr int MCG_STAGES = MCG_STAGES_N;
 #endif
 constexpr int MCG_GPBUF = MCG_GPBUF_N;       // buffers of the per-source-tile (gamma, phi) pairs
 constexpr int MCG_MAX_KC = 64;       // max Chebyshev terms
-constexpr int MCG_SHIFT = 4;         // c: counts below c use the one-hot table
 constexpr int MCG_MT = 2;            // 8-row DMMA tiles per warp along the targets (warp tile = 8*MCG_MT x 8*MCG_NT)
 #ifndef MCG_NT_N                     // (development builds: 4 = 64 x 64 CTA tiles, 16 x 32 warp tiles, three CTAs per SM)
 #define MCG_NT_N 8
@@ -58,23 +55,6 @@ constexpr int MCG_NT = MCG_NT_N;     // 8-column DMMA tiles per warp along the s
 constexpr int MCG_TJ = 2 * 8 * MCG_NT;   // source columns per CTA tile (two warps side by side): 128
 constexpr int MCG_CTAS = MCG_NT == 8 ? 2 : 3;   // CTAs per SM the kernel is sized for
 constexpr int MCG_THREADS = 32 * (MCG_TI / (8 * MCG_MT)) * 2;     // warps: (64 / warp rows) x 2 = 8
-
-struct McgShape {
-    int n;          // samples in the batch
-    int Kc;         // Chebyshev terms
-    int KT;         // n + Kc + MCG_SHIFT + 1
-    int KTP;        // KT rounded up to a multiple of MCG_KC (the last hand-over of a source tile may hold one k-chunk)
-    long rows;      // matrix rows, G rounded up to a multiple of MCG_TILE
-    double ulo, uhi;   // range of u = log(r + c)
-};
-
-// Storage of P and Q: chunk-major, [kc][row][8] doubles with an XOR swizzle of the in-chunk column so that the
-// m8n8k4 fragment loads (8 rows x 4 columns per warp) are shared-memory bank-conflict free at a dense row stride
-// of 8 doubles, and so that one (tile, chunk) block of 128 rows is 8 KB contiguous in global memory = one bulk copy.
-__host__ __device__ __forceinline__ size_t mcg_index(long rows, long row, int k) {
-    const int kc = k >> 3, kk = (k & 7) ^ ((int)((row >> 1) & 1) << 2);
-    return ((size_t)kc * rows + row) * 8 + kk;
-}
 
 // lgamma(x + r) - lgamma(x + 1) for integer-valued x >= 0, r > 0, without cancellation for large x
 __device__ __forceinline__ double lgamma_diff(double x, double r) {
@@ -109,10 +89,12 @@ k_mcg_phi_range(const double* __restrict__ phi, long G, double* __restrict__ out
 
 // ---- source side: row j of Q -------------------------------------------------------------------------------
 // cols[t] = global column of the batch's t-th sample; phi, gamma = this batch's columns of phi_hat / gamma_hat.
+// Row j of P and Q is gene perm[j] (the batch's abundance order, see k_mcg_sort_key): genes with similar expression sit
+// in neighbouring rows, so the pairs that carry weight form a band around the diagonal.
 // Rows j >= G are padding: zeros with c_j = MC_LOG_ZERO, so their weight is exactly 0.
 __global__ void __launch_bounds__(128)
 k_mcg_prep_src(const double* __restrict__ mu_hat, long G, const int* __restrict__ cols, const double* __restrict__ phi,
-               McgShape sh, double* __restrict__ Q) {
+               const int* __restrict__ perm, McgShape sh, double* __restrict__ Q) {
     const long j = (long)blockIdx.x * blockDim.x + threadIdx.x;
     if (j >= sh.rows) return;
     const int n = sh.n, Kc = sh.Kc;
@@ -120,10 +102,11 @@ k_mcg_prep_src(const double* __restrict__ mu_hat, long G, const int* __restrict_
         for (int k = 0; k < sh.KTP; ++k) Q[mcg_index(sh.rows, j, k)] = (k == sh.KT - 1) ? MC_LOG_ZERO : 0.0;
         return;
     }
-    const double r = 1.0 / phi[j];
+    const long gj = perm[j];
+    const double r = 1.0 / phi[gj];
     double c = 0;
     for (int t = 0; t < n; ++t) {
-        const double mu = mu_hat[j + (long)cols[t] * G];
+        const double mu = mu_hat[gj + (long)cols[t] * G];
         double a, l;
         if (mu == 0) { a = MC_LOG_ZERO; l = 0; }
         else {
@@ -161,17 +144,18 @@ k_mcg_node_table(McgShape sh, double* __restrict__ tab) {          // grid (MCG_
 }
 
 __global__ void __launch_bounds__(128)
-k_mcg_prep_nodes(const int32_t* __restrict__ cnt, long G, const int* __restrict__ cols, McgShape sh, long ip0, long ip1,
-                 const double* __restrict__ tab, double* __restrict__ Fnode) {
-    const long i = ip0 + (long)blockIdx.x * blockDim.x + threadIdx.x;     // targets [ip0, ip1): this rank's rows of P
+k_mcg_prep_nodes(const int32_t* __restrict__ cnt, long G, const int* __restrict__ cols, const int* __restrict__ perm,
+                 McgShape sh, McgOwn own, const double* __restrict__ tab, double* __restrict__ Fnode) {
+    const long i = own.row((long)blockIdx.x * blockDim.x + threadIdx.x);     // sorted row of one of this rank's targets
     const int m = blockIdx.y;
-    if (i >= G || i >= ip1) return;
+    if (i >= G) return;
+    const long gi = perm[i];
     const double tn = cospi((m + 0.5) / sh.Kc);
     const double r = exp(0.5 * (sh.ulo + sh.uhi) + 0.5 * (sh.uhi - sh.ulo) * tn) - (double)MCG_SHIFT;
     const double* __restrict__ t_m = tab + (long)m * MCG_LGTAB;
     double f = 0;
     for (int t = 0; t < sh.n; ++t) {
-        const int x = cnt[i + (long)cols[t] * G];
+        const int x = cnt[gi + (long)cols[t] * G];
         if (x >= MCG_LGTAB) f += lgamma_diff((double)x, r);
         else if (x >= MCG_SHIFT) f += __ldg(t_m + x);
     }
@@ -182,21 +166,22 @@ k_mcg_prep_nodes(const int32_t* __restrict__ cnt, long G, const int* __restrict_
 // dct is the Kc x Kc table dct[k*Kc + m] = (k ? 2 : 1)/Kc * cos(pi k (m + 1/2)/Kc).  tail_bits: atomicMax of the
 // bit pattern of |C_{Kc-1}| + |C_{Kc-2}| (non-negative doubles order like their bit patterns).
 __global__ void __launch_bounds__(128)
-k_mcg_prep_tgt(const int32_t* __restrict__ cnt, long G, const int* __restrict__ cols, McgShape sh,
-               long ip0, long ip1, const double* __restrict__ Fnode, const double* __restrict__ dct, double* __restrict__ P,
-               unsigned long long* __restrict__ tail_bits) {
-    const long i = ip0 + (long)blockIdx.x * blockDim.x + threadIdx.x;
-    if (i >= ip1) return;
+k_mcg_prep_tgt(const int32_t* __restrict__ cnt, long G, const int* __restrict__ cols, const int* __restrict__ perm,
+               McgShape sh, McgOwn own, const double* __restrict__ Fnode, const double* __restrict__ dct,
+               double* __restrict__ P, unsigned long long* __restrict__ tail_bits) {
+    const long i = own.row((long)blockIdx.x * blockDim.x + threadIdx.x);
+    if (i >= sh.rows) return;
     const int n = sh.n, Kc = sh.Kc;
     if (i >= G) {
         for (int k = 0; k < sh.KTP; ++k) P[mcg_index(sh.rows, i, k)] = 0.0;
         return;
     }
+    const long gi = perm[i];
     int hot[MCG_SHIFT];
 #pragma unroll
     for (int v = 0; v < MCG_SHIFT; ++v) hot[v] = 0;
     for (int t = 0; t < n; ++t) {
-        const int x = cnt[i + (long)cols[t] * G];
+        const int x = cnt[gi + (long)cols[t] * G];
         P[mcg_index(sh.rows, i, t)] = (double)x;
 #pragma unroll
         for (int v = 0; v < MCG_SHIFT; ++v) hot[v] += (x == v);
@@ -256,7 +241,6 @@ __device__ __forceinline__ void dmma884(double& c0, double& c1, double a, double
 // In reference mode McAcc::m is only this running maximum; the weights themselves stay exp(L), unshifted, so that
 // they underflow exactly where R's prod(dnbinom) does.  In stable mode the sums are kept relative to exp(m)
 // (online log-sum-exp, rescaled once per source tile when the maximum moves).
-constexpr double MCG_PRUNE = 40.0;
 
 __device__ __forceinline__ void mbar_arrive(uint64_t* bar) {
     asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(smem_u32(bar)) : "memory");
@@ -323,10 +307,16 @@ static_assert(MCG_THREADS == MCG_CONSUMER_WARPS * 32, "consumer thread count");
 // leave a stage issues the copies that refill it.  A warp that is folding the weights of a finished source tile
 // (FP64 pipe) therefore never holds up the refills the other warps are waiting for, and the other warp of its
 // scheduler keeps the tensor pipe busy meanwhile.  part[(split*rows + i)] receives the partial sums of target row i.
+// Work items: items[w] = (target tile, segment); segment s of target tile t covers entries [s*MCG_SEG, ...) of the tile's
+// source-tile list srclist[t*NJ ..] (count[t] entries, ascending; built by the screening pass, or all NJ tiles).  The
+// decomposition depends on the lists only, never on the number of GPUs, and the partials of a target tile are merged in
+// segment order (k_mcg_finalize): results are bit-identical for every sharding.
+constexpr int MCG_SEG = 8;           // source tiles per work item
 template <int STABLE>
 __global__ void __launch_bounds__(MCG_BLOCK, MCG_CTAS)
 k_mc_gemm(const double* __restrict__ P, const double* __restrict__ Q, const double2* __restrict__ gp, McgShape sh,
-          long tile0, McAcc* __restrict__ part) {
+          const int2* __restrict__ items, const int* __restrict__ srclist, const int* __restrict__ count,
+          McAcc* __restrict__ part) {
     extern __shared__ __align__(128) unsigned char smem_raw[];
     double* stage_base = reinterpret_cast<double*>(smem_raw);
     double2* gp_s = reinterpret_cast<double2*>(smem_raw + MCG_STAGES * MCG_SMEM_STAGE);
@@ -337,13 +327,16 @@ k_mc_gemm(const double* __restrict__ P, const double* __restrict__ Q, const doub
 
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     const int wi = warp % MCG_WI, wj = warp / MCG_WI;
-    const long itile = tile0 + blockIdx.x;
+    const int2 item = items[blockIdx.x];
+    const long itile = item.x;
     const long NJ = sh.rows / MCG_TJ;
-    const long jt0 = NJ * blockIdx.y / gridDim.y, jt1 = NJ * (blockIdx.y + 1) / gridDim.y;
+    const int nsrc = min(MCG_SEG, count[itile] - item.y * MCG_SEG);       // source tiles of this work item
+    __shared__ int src_s[MCG_SEG];
+    if (threadIdx.x < MCG_SEG) src_s[threadIdx.x] = threadIdx.x < nsrc ? srclist[itile * NJ + (long)item.y * MCG_SEG + threadIdx.x] : 0;
     const int NCH = sh.KTP / MCG_KC;                              // k-chunks per source tile
     const int NKS = (NCH + MCG_SUB - 1) / MCG_SUB;                // hand-overs (stages) per source tile
     const int last_sub = NCH - (NKS - 1) * MCG_SUB;               // k-chunks in a tile's last hand-over (1..MCG_SUB)
-    const long total = (jt1 - jt0) * NKS;
+    const long total = (long)nsrc * NKS;
 
     if (tid == 0) {
         for (int s = 0; s < MCG_STAGES; ++s) { mbar_init(&full[s], 1); done[s] = 0; }
@@ -365,12 +358,12 @@ k_mc_gemm(const double* __restrict__ P, const double* __restrict__ Q, const doub
             const size_t kc = (size_t)nks * MCG_SUB + u;
             double* su = sb + u * (MCG_TI + MCG_TJ) * MCG_KC;
             bulk_g2s(su, P + (kc * sh.rows + itile * MCG_TI) * MCG_KC, p_bytes, &full[ns]);
-            bulk_g2s(su + MCG_TI * MCG_KC, Q + (kc * sh.rows + (jt0 + njl) * MCG_TJ) * MCG_KC, q_bytes, &full[ns]);
+            bulk_g2s(su + MCG_TI * MCG_KC, Q + (kc * sh.rows + (long)src_s[njl] * MCG_TJ) * MCG_KC, q_bytes, &full[ns]);
         }
         // gamma/phi of source tile njl go to buffer njl % MCG_GPBUF, last read in the epilogue of tile njl - MCG_GPBUF,
         // which every warp has finished before it leaves hand-over njl * NKS - MCG_STAGES
         // ((MCG_GPBUF - 1) * NKS >= MCG_STAGES + 1 is guaranteed by the host: KTP >= 2 stages).
-        if (nks == 0) bulk_g2s(gp_s + (njl % MCG_GPBUF) * MCG_TJ, gp + (jt0 + njl) * MCG_TJ, MCG_TJ * sizeof(double2), &full[ns]);
+        if (nks == 0) bulk_g2s(gp_s + (njl % MCG_GPBUF) * MCG_TJ, gp + (long)src_s[njl] * MCG_TJ, MCG_TJ * sizeof(double2), &full[ns]);
     };
     if (tid == 0)
         for (long c = 0; c < total && c < MCG_STAGES; ++c) issue(c);
@@ -426,7 +419,7 @@ k_mc_gemm(const double* __restrict__ P, const double* __restrict__ Q, const doub
             if (++st == MCG_STAGES) { st = 0; phase ^= 1u; }
 
             if (++kc == NKS) {                               // last k-chunk of source tile jl: fold the weights in
-                const long jt = jt0 + jl;
+                const long jt = src_s[jl];
                 const double2* g2 = gp_s + (jl % MCG_GPBUF) * MCG_TJ;
                 if (jt == (itile * MCG_TI) / MCG_TJ) {     // mu[-i,]: the gene itself is not a source  helper_seq.R:11-14
                     const int ioff = (int)((itile * MCG_TI) % MCG_TJ);
@@ -462,47 +455,6 @@ k_mc_gemm(const double* __restrict__ P, const double* __restrict__ Q, const doub
                 // RNA-seq-like data), so every lane group has work: the 8 elements of a column group are evaluated
                 // branch-free and independently (8 interleaved mcg_exp chains keep the FP64 pipe busy) and masked;
                 // one warp vote skips a column group whose 256 pairs are all pruned (far-apart genes).
-#ifdef MCG_EPI_COMPACT
-                // Compacted fold (development build): about one pair in eight survives the pruning, so instead of 32
-                // masked exp() per thread every lane walks the list of its own survivors; the warp loops until the
-                // lane with the most survivors is done.  The accumulators are parked in local memory for the walk
-                // (registers cannot be indexed by a run-time value).
-#pragma unroll
-                for (int mt = 0; mt < MCG_MT; ++mt) {
-                    double la[MCG_NT * 2];
-                    unsigned mask = 0;
-#pragma unroll
-                    for (int nt = 0; nt < MCG_NT; ++nt)
-#pragma unroll
-                        for (int e = 0; e < 2; ++e) {
-                            const double L = acc[mt][nt][e];
-                            la[nt * 2 + e] = L;
-                            mask |= (L > thr[mt]) ? (1u << (nt * 2 + e)) : 0u;
-                            acc[mt][nt][e] = 0.0;
-                        }
-                    const double mref = STABLE ? racc[mt].m : 0.0;
-                    double sw = racc[mt].sw, sg = racc[mt].sg, sp = racc[mt].sp;
-                    while (__any_sync(0xffffffffu, mask != 0u)) {
-                        if (mask != 0u) {
-                            const int q = __ffs(mask) - 1;
-                            mask &= mask - 1u;
-                            const double L = la[q];
-                            const double2 gq = g2[wj * (8 * MCG_NT) + (q >> 1) * 8 + 2 * fcol + (q & 1)];
-                            const double w = mcg_exp(L - mref, exp_tab);
-                            sw += w; sg = fma(w, gq.x, sg); sp = fma(w, gq.y, sp);
-                        }
-                    }
-                    racc[mt].sw = sw; racc[mt].sg = sg; racc[mt].sp = sp;
-                }
-                if (false)
-#endif
-#ifdef MCG_DIAG_NO_EPILOGUE                                  // diagnostic build: what the contraction costs without the fold
-#pragma unroll
-                for (int nt = 0; nt < MCG_NT; ++nt)
-#pragma unroll
-                    for (int mt = 0; mt < MCG_MT; ++mt) { racc[mt].sw += acc[mt][nt][0] + acc[mt][nt][1]; acc[mt][nt][0] = acc[mt][nt][1] = 0.0; }
-                if (false)
-#endif
 #pragma unroll
                 for (int nt = 0; nt < MCG_NT; ++nt) {
                     bool need = false;
@@ -547,31 +499,135 @@ k_mc_gemm(const double* __restrict__ P, const double* __restrict__ Q, const doub
     if (tid < MCG_TI) {
         McAcc a = red[tid];
         mc_merge(a, red[MCG_TI + tid], STABLE);
-        part[(size_t)blockIdx.y * sh.rows + itile * MCG_TI + tid] = a;
+        part[(size_t)blockIdx.x * MCG_TI + tid] = a;
     }
 }
 
-// merge the source-split partials of targets [i0, i1) in split order and apply helper_seq.R:30-33
-__global__ void __launch_bounds__(128)
-k_mcg_finalize(const McAcc* __restrict__ part, long rows, int nsplit, long i0, long i1, int stable,
-               const double* __restrict__ gamma, const double* __restrict__ phi, double* __restrict__ gamma_star,
-               double* __restrict__ phi_star, unsigned long long* __restrict__ n_fallback) {
-    const long i = i0 + (long)blockIdx.x * blockDim.x + threadIdx.x;
-    if (i >= i1) return;
-    McAcc a = part[i];
-    for (int s = 1; s < nsplit; ++s) mc_merge(a, part[(size_t)s * rows + i], stable);
+// merge the work-item partials of every target row this rank owns, in segment order, and apply helper_seq.R:30-33.
+// Row i of the sorted order is gene perm[i]; gamma/phi/gamma_star/phi_star are indexed by gene.
+// grid: one block of MCG_TI threads per owned target tile (tiles[] lists them).
+__global__ void __launch_bounds__(MCG_TI)
+k_mcg_finalize(const McAcc* __restrict__ part, const int* __restrict__ tiles, const int* __restrict__ item_start,
+               const int* __restrict__ perm, long G, int stable, const double* __restrict__ gamma,
+               const double* __restrict__ phi, double* __restrict__ gamma_star, double* __restrict__ phi_star,
+               unsigned long long* __restrict__ n_fallback) {
+    const int t = tiles[blockIdx.x];
+    const long i = (long)t * MCG_TI + threadIdx.x;
+    if (i >= G) return;
+    const int w0 = item_start[blockIdx.x], w1 = item_start[blockIdx.x + 1];
+    McAcc a;
+    a.m = -INFINITY; a.sw = a.sg = a.sp = 0.0;
+    for (int w = w0; w < w1; ++w) mc_merge(a, part[(size_t)w * MCG_TI + threadIdx.x], stable);
+    const long gi = perm[i];
     if (a.sw == 0 || !(a.sw == a.sw)) {
-        gamma_star[i] = gamma[i]; phi_star[i] = phi[i];
+        gamma_star[gi] = gamma[gi]; phi_star[gi] = phi[gi];
         atomicAdd(n_fallback, 1ull);
     } else {
-        gamma_star[i] = a.sg / a.sw; phi_star[i] = a.sp / a.sw;
+        gamma_star[gi] = a.sg / a.sw; phi_star[gi] = a.sp / a.sw;
     }
 }
 
-__global__ void k_mcg_pack_gp(const double* __restrict__ gamma, const double* __restrict__ phi, long G, long rows,
-                              double2* __restrict__ gp) {
+__global__ void k_mcg_pack_gp(const double* __restrict__ gamma, const double* __restrict__ phi, const int* __restrict__ perm,
+                              long G, long rows, double2* __restrict__ gp) {
     const long j = (long)blockIdx.x * blockDim.x + threadIdx.x;
-    if (j < rows) gp[j] = (j < G) ? make_double2(gamma[j], phi[j]) : make_double2(0.0, 0.0);
+    if (j < rows) gp[j] = (j < G) ? make_double2(gamma[perm[j]], phi[perm[j]]) : make_double2(0.0, 0.0);
+}
+
+// ---- abundance order ------------------------------------------------------------------------------------------------
+// key[g] = mean over the batch's samples of log(mu_hat[g, s]); the stable radix sort of the keys gives perm[].
+__global__ void __launch_bounds__(128)
+k_mcg_sort_key(const double* __restrict__ mu_hat, long G, int n, const int* __restrict__ cols, float* __restrict__ key,
+               int* __restrict__ idx) {
+    const long g = (long)blockIdx.x * blockDim.x + threadIdx.x;
+    if (g >= G) return;
+    double s = 0;
+    for (int t = 0; t < n; ++t) s += log(fmax(mu_hat[g + (long)cols[t] * G], 1e-300));
+    key[g] = (float)(s / n);
+    idx[g] = (int)g;
+}
+__global__ void k_mcg_iota(int* __restrict__ idx, long G) {
+    const long g = (long)blockIdx.x * blockDim.x + threadIdx.x;
+    if (g < G) idx[g] = (int)g;
+}
+
+// ---- source-tile lists -------------------------------------------------------------------------------------------------
+// Without screening every target tile visits every source tile.  grid (ntiles64), block 128.
+__global__ void k_mcg_list_all(int NJ, int* __restrict__ srclist, int* __restrict__ count) {
+    const int t = blockIdx.x;
+    for (int j = threadIdx.x; j < NJ; j += blockDim.x) srclist[(long)t * NJ + j] = j;
+    if (threadIdx.x == 0) count[t] = NJ;
+}
+
+// With screening (tu_screen.cu): hi[J*rows + i] is an upper bound of max_{j in source tile J} log LH_ij and lo[J*rows + i] a
+// lower bound of the same maximum over j != i.  Source tile J is kept for target tile t when some row of t can have a
+// pair in J within MCG_PRUNE of the row's best pair:  hi[J][i] >= max_J' lo[J'][i] - MCG_PRUNE.  Whatever is dropped is
+// below e^-40 of the row's largest weight, the bound the fold in k_mc_gemm applies anyway.  grid (ntiles64), block 256,
+// NJ bytes of dynamic shared memory.  The 4 thread groups of a block split the source tiles.
+__global__ void __launch_bounds__(256)
+k_mcg_list_screened(const float* __restrict__ hi, const float* __restrict__ lo, long rows, int NJ, float prune,
+                    int* __restrict__ srclist, int* __restrict__ count) {
+    extern __shared__ unsigned char flag_s[];                  // [NJ]
+    __shared__ float mx[4][MCG_TI];
+    const int t = blockIdx.x, r = threadIdx.x & (MCG_TI - 1), q = threadIdx.x / MCG_TI;
+    const long i = (long)t * MCG_TI + r;
+    float m = -INFINITY;
+#pragma unroll 4
+    for (int J = q; J < NJ; J += 4) m = fmaxf(m, lo[(long)J * rows + i]);
+    mx[q][r] = m;
+    for (int J = threadIdx.x; J < NJ; J += 256) flag_s[J] = 0;
+    __syncthreads();
+    m = fmaxf(fmaxf(mx[0][r], mx[1][r]), fmaxf(mx[2][r], mx[3][r]));
+    const float thr = m - prune;                               // -inf when the row has no finite pair: everything is kept
+#pragma unroll 4
+    for (int J = q; J < NJ; J += 4) if (!(hi[(long)J * rows + i] < thr)) flag_s[J] = 1;      // (NaN counts as kept)
+    __syncthreads();
+    if (threadIdx.x < 32) {
+        const int lane = threadIdx.x;
+        int n = 0;
+        for (int J0 = 0; J0 < NJ; J0 += 32) {
+            const int J = J0 + lane;
+            const bool k = J < NJ && flag_s[J];
+            const unsigned b = __ballot_sync(0xffffffffu, k);
+            if (k) srclist[(long)t * NJ + n + __popc(b & ((1u << lane) - 1u))] = J;
+            n += __popc(b);
+        }
+        if (lane == 0) count[t] = n;
+    }
+}
+
+// Work items of the target tiles this rank owns, in tile order: tiles[k], item_start[k] .. item_start[k+1], items[w] =
+// (tile, segment).  One block of 1024 threads, one tile per thread and round, block-wide exclusive scans of (owned,
+// segments).  out[0] = number of items, out[1] = number of owned tiles, out[2] = sum of count[] over the owned tiles.
+__global__ void __launch_bounds__(1024)
+k_mcg_items(const int* __restrict__ count, int ntiles64, McgOwn own, int* __restrict__ tiles,
+            int* __restrict__ item_start, int2* __restrict__ items, int* __restrict__ out) {
+    __shared__ int s_k[1024], s_w[1024], s_c[1024];
+    __shared__ int base_k, base_w, base_c;
+    if (threadIdx.x == 0) { base_k = 0; base_w = 0; base_c = 0; }
+    __syncthreads();
+    for (int t0 = 0; t0 < ntiles64; t0 += 1024) {
+        const int t = t0 + threadIdx.x;
+        const bool mine = t < ntiles64 && own.owns_tile64(t);
+        const int c = mine ? count[t] : 0, nseg = (c + MCG_SEG - 1) / MCG_SEG;
+        s_k[threadIdx.x] = mine ? 1 : 0; s_w[threadIdx.x] = nseg; s_c[threadIdx.x] = c;
+        __syncthreads();
+        for (int o = 1; o < 1024; o <<= 1) {                  // inclusive Hillis-Steele scans
+            int ak = 0, aw = 0, ac = 0;
+            if ((int)threadIdx.x >= o) { ak = s_k[threadIdx.x - o]; aw = s_w[threadIdx.x - o]; ac = s_c[threadIdx.x - o]; }
+            __syncthreads();
+            s_k[threadIdx.x] += ak; s_w[threadIdx.x] += aw; s_c[threadIdx.x] += ac;
+            __syncthreads();
+        }
+        if (mine) {
+            const int k = base_k + s_k[threadIdx.x] - 1, w = base_w + s_w[threadIdx.x] - nseg;
+            tiles[k] = t; item_start[k] = w;
+            for (int sgm = 0; sgm < nseg; ++sgm) items[w + sgm] = make_int2(t, sgm);
+        }
+        __syncthreads();
+        if (threadIdx.x == 1023) { base_k += s_k[1023]; base_w += s_w[1023]; base_c += s_c[1023]; }
+        __syncthreads();
+    }
+    if (threadIdx.x == 0) { item_start[base_k] = base_w; out[0] = base_w; out[1] = base_k; out[2] = base_c; }
 }
 
 }  // namespace cbs

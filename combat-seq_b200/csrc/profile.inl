@@ -6,6 +6,7 @@ static bool g_prof_on = false;
 static std::vector<ProfRec> g_prof_pending;
 static std::map<std::string, std::pair<double, long>> g_prof_acc;     // name -> (total ms, launches)
 static std::vector<cudaEvent_t> g_prof_pool;
+static std::mutex g_prof_mutex;       // launches come from one host thread per device in single-process multi-GPU calls
 
 static cudaEvent_t prof_event() {
     if (!g_prof_pool.empty()) { cudaEvent_t e = g_prof_pool.back(); g_prof_pool.pop_back(); return e; }
@@ -15,6 +16,7 @@ static cudaEvent_t prof_event() {
 }
 cudaEvent_t prof_begin(const char* name, cudaStream_t st) {
     if (!g_prof_on) return nullptr;
+    std::lock_guard<std::mutex> lk(g_prof_mutex);
     ProfRec r{name, prof_event(), prof_event()};
     cudaEventRecord(r.e0, st);
     g_prof_pending.push_back(r);
@@ -22,7 +24,9 @@ cudaEvent_t prof_begin(const char* name, cudaStream_t st) {
 }
 void prof_end(cudaEvent_t begin, cudaStream_t st) {
     if (!begin) return;
-    cudaEventRecord(g_prof_pending.back().e1, st);
+    std::lock_guard<std::mutex> lk(g_prof_mutex);
+    for (auto it = g_prof_pending.rbegin(); it != g_prof_pending.rend(); ++it)
+        if (it->e0 == begin) { cudaEventRecord(it->e1, st); break; }
 }
 static void prof_collect() {
     if (g_prof_pending.empty()) return;
@@ -54,22 +58,6 @@ __global__ void __launch_bounds__(256) k_fp64_peak(double* out, double a, double
     if (s == 123.456) out[0] = s;
 }
 
-// 16 independent DMMA.8x8x4 accumulator tiles per warp, 256 rounds
-__global__ void __launch_bounds__(256) k_fp64_mma_peak(double* out, double a, double b) {
-    double c[16][2];
-#pragma unroll
-    for (int t = 0; t < 16; ++t) { c[t][0] = threadIdx.x; c[t][1] = t; }
-#pragma unroll 1
-    for (int i = 0; i < 256; ++i) {
-#pragma unroll
-        for (int t = 0; t < 16; ++t) dmma884(c[t][0], c[t][1], a, b);
-    }
-    double s = 0;
-#pragma unroll
-    for (int t = 0; t < 16; ++t) s += c[t][0] + c[t][1];
-    if (s == 123.456) out[0] = s;
-}
-
 }  // namespace cbs
 
 extern "C" {
@@ -77,19 +65,21 @@ extern "C" {
 int cbs_set_tuning(const char* key, double value) {
     std::lock_guard<std::mutex> lock_(g_mutex);
     if (!key) return fail(CBS_EINVAL, "null key");
-    if (!strcmp(key, "mc_algo")) { if (value < 0 || value > 2) return fail(CBS_EINVAL, "mc_algo must be 0, 1 or 2"); g_mc_algo = (int)value; return CBS_OK; }
-    if (!strcmp(key, "mc_tail_tol")) { g_mc_tail_tol = value; return CBS_OK; }
-    if (!strcmp(key, "apl_fast")) { g_apl_fast = value != 0; return CBS_OK; }
-    if (!strcmp(key, "glm_scr")) { g_glm_scr = value != 0; return CBS_OK; }
-    if (!strcmp(key, "mq_rows")) { g_mq_rows = (int)value; return CBS_OK; }
+    if (!strcmp(key, "mc_algo")) { if (value < 0 || value > 2) return fail(CBS_EINVAL, "mc_algo must be 0, 1 or 2"); g_tune.mc_algo = (int)value; return CBS_OK; }
+    if (!strcmp(key, "mc_band")) { g_tune.mc_band = value != 0; return CBS_OK; }
+    if (!strcmp(key, "mc_tail_tol")) { g_tune.mc_tail_tol = value; return CBS_OK; }
+    if (!strcmp(key, "apl_fast")) { g_tune.apl_fast = value != 0; return CBS_OK; }
+    if (!strcmp(key, "glm_scr")) { g_tune.glm_scr = value != 0; return CBS_OK; }
     return fail(CBS_EINVAL, "unknown tuning key '%s'", key);
 }
 int cbs_get_diag(const char* key, double* value) {
     std::lock_guard<std::mutex> lock_(g_mutex);
     if (!key || !value) return fail(CBS_EINVAL, "null pointer");
-    if (!strcmp(key, "mc_tail")) { *value = g_last_mc_tail; return CBS_OK; }
-    if (!strcmp(key, "mc_terms")) { *value = g_last_mc_kc; return CBS_OK; }
-    if (!strcmp(key, "reset")) { g_last_mc_tail = 0; g_last_mc_kc = 0; *value = 0; return CBS_OK; }
+    if (!strcmp(key, "mc_tail")) { *value = g_diag.mc_tail; return CBS_OK; }
+    if (!strcmp(key, "mc_terms")) { *value = g_diag.mc_kc; return CBS_OK; }
+    if (!strcmp(key, "mc_tiles_done")) { *value = g_diag.mc_tiles_done; return CBS_OK; }
+    if (!strcmp(key, "mc_tiles_all")) { *value = g_diag.mc_tiles_all; return CBS_OK; }
+    if (!strcmp(key, "reset")) { g_diag = Diag(); *value = 0; return CBS_OK; }
     return fail(CBS_EINVAL, "unknown diagnostics key '%s'", key);
 }
 
@@ -97,26 +87,7 @@ int cbs_fp64_mma_peak(double* tflops) {
     CBS_NEED_GPU();
     if (!tflops) return fail(CBS_EINVAL, "null pointer");
     CBS_ENTRY_BEGIN
-    int dev = 0, sms = 0;
-    CBS_CUDA(cudaGetDevice(&dev));
-    CBS_CUDA(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev));
-    double* d = g_dev.get<double>("fp64_peak", 8);
-    const int blocks = sms * 16;
-    cudaEvent_t e0, e1;
-    CBS_CUDA(cudaEventCreate(&e0)); CBS_CUDA(cudaEventCreate(&e1));
-    double best = 0;
-    for (int rep = 0; rep < 6; ++rep) {
-        CBS_CUDA(cudaEventRecord(e0, 0));
-        CBS_LAUNCH(k_fp64_mma_peak, dim3(blocks), 256, 0, 0, d, 0.999999, 1e-6);
-        CBS_CUDA(cudaEventRecord(e1, 0));
-        CBS_CUDA(cudaEventSynchronize(e1));
-        float ms = 0;
-        CBS_CUDA(cudaEventElapsedTime(&ms, e0, e1));
-        const double flop = 2.0 * 256 /*fma per mma*/ * 16 * 256 * 8 /*warps*/ * (double)blocks;
-        if (rep > 0) best = std::max(best, flop / (ms * 1e-3) / 1e12);
-    }
-    cudaEventDestroy(e0); cudaEventDestroy(e1);
-    *tflops = best;
+    *tflops = fp64_mma_peak_tflops();
     CBS_ENTRY_END
 }
 

@@ -25,7 +25,7 @@
 extern "C" {
 #endif
 
-#define CBS_VERSION 100
+#define CBS_VERSION 200
 
 enum {
     CBS_OK = 0,
@@ -67,23 +67,25 @@ uint64_t    cbs_kernel_launches(void);        /* kernels launched by this librar
 int         cbs_profile_enable(int on);
 int         cbs_profile_dump(char* buf, size_t len);
 int         cbs_fp64_peak(double* tflops);
-int         cbs_fp64_mma_peak(double* tflops);   /* same for the FP64 tensor pipe (mma.sync m8n8k4 f64, DMMA) */
+int         cbs_fp64_mma_peak(double* tflops);   /* same for the FP64 tensor pipe (mma.sync m8n8k4 f64, DMMA), operands from
+                                                    shared memory as in the contraction kernel */
 
 /* ---- tuning knobs and diagnostics ---------------------------------------------------------------------------
  * Defaults reproduce the reference; none of them changes what is computed beyond the stated tolerance.
  *   "mc_algo"      0 = auto, 1 = direct pairwise kernel (every lgamma evaluated), 2 = FP64 tensor-core
  *                  contraction with the Chebyshev expansion of the lgamma term
+ *   "mc_band"      1 (default) = the contraction visits, per 64-gene target tile, only the 128-gene source tiles that
+ *                  the tcgen05 screening pass cannot rule out (pairs more than 40 nats below the row's best pair carry
+ *                  < 4e-18 of the weight and are pruned either way); 0 = every source tile
  *   "mc_tail_tol"  largest accepted Chebyshev tail estimate in log-likelihood units (default 1e-8); a batch that
  *                  exceeds it is redone with the direct kernel when mc_algo = 0
  *   "apl_fast"     1 (default) = lgamma tables, hoisted log/lgamma of 1/phi and product-form mu in the APL kernel
  *                  (last-place differences); 0 = one call per sample
  *   "glm_scr"      1 (default) = Levenberg work arrays of the lane-group GLM kernel in shared memory; 0 = local memory
  *                  (same bits)
- *   "mq_rows"      thread mapping / call structure of match_quantiles: 3 (default) = warp per gene, continued fraction
- *                  out of line; 2 = same, inlined; 1 = 8 x 32 tiles through shared memory; 4 = tiles, out of line
- *                  (same bits; development A/B, tools/ab_time.py)
  * cbs_get_diag keys: "mc_tail" (largest tail estimate since the last reset), "mc_terms" (Chebyshev terms of the
- * last contraction launch); cbs_get_diag("reset", &x) clears them. */
+ * last contraction launch), "mc_tiles_done" / "mc_tiles_all" (source tiles visited / available, summed over the target
+ * tiles of rank 0 since the last reset); cbs_get_diag("reset", &x) clears them. */
 int         cbs_set_tuning(const char* key, double value);
 int         cbs_get_diag(const char* key, double* value);
 
@@ -95,7 +97,7 @@ typedef struct cbs_comm cbs_comm;
 int cbs_comm_unique_id(void* id128);
 int cbs_comm_create(const void* id128, int rank, int world, int device, cbs_comm** out);
 int cbs_comm_destroy(cbs_comm* comm);
-/* Kept-gene rows [g0, g1) owned by `rank` of `world`: contiguous blocks rounded up to the 1024-gene reduction chunk, so
+/* Kept-gene rows [g0, g1) owned by `rank` of `world`: contiguous blocks rounded up to the 128-gene reduction chunk, so
  * that the chunk partial sums of the common-dispersion objective (and everything downstream) do not depend on the
  * number of GPUs.  Host-only (needs no device). */
 int cbs_shard_range(int64_t G, int32_t rank, int32_t world, int64_t* g0, int64_t* g1);
@@ -103,18 +105,22 @@ int cbs_shard_range(int64_t G, int32_t rank, int32_t world, int64_t* g0, int64_t
 /* ---- the whole ComBat_seq() numeric body (ComBat_seq.R:33-203) -------------------------------------- */
 typedef struct {
     int32_t G0, N, B, p_mod;        /* genes, samples, batches, ncol(mod) incl. the intercept column      */
-    const double*  counts_f64;      /* G0 x N, integer-valued; exactly one of counts_f64/counts_i32 set   */
+    const double*  counts_f64;      /* G0 x N, non-negative integers below 2^31 (NA, negative or fractional values are
+                                       rejected with CBS_EINVAL); exactly one of counts_f64/counts_i32 set        */
     const int32_t* counts_i32;      /* G0 x N                                                             */
     const int32_t* batch_idx;       /* N, 0-based level index of as.factor(batch)       ComBat_seq.R:28   */
     const double*  mod;             /* N x p_mod, column 0 is the intercept             ComBat_seq.R:57-73 */
     const uint8_t* use_fallback;    /* B, or NULL: library evaluates ComBat_seq.R:101 itself              */
     int32_t shrink, shrink_disp;    /* ComBat_seq.R:141,162                                               */
     int32_t gene_subset_n;          /* <= 0 means NULL (all genes)                      helper_seq.R:17    */
-    uint64_t seed;                  /* RNG seed for gene_subset_n sampling (Philox, not R's stream)       */
+    uint64_t seed;                  /* seed of the gene_subset_n sampler (keyed Feistel permutation, not R's stream) */
     int32_t mc_mode;                /* CBS_MC_REFERENCE / CBS_MC_STABLE                                    */
     int32_t device;                 /* CUDA device ordinal for single-process use; <0 = current           */
     cbs_comm* comm;                 /* NULL = single GPU; else this process is one rank of a gene-sharded job */
     int32_t counts_on_device;       /* non-zero: counts_i32 is a DEVICE pointer (kernel-only benchmarking) */
+    int32_t n_gpus;                 /* single-process multi-GPU (the R caller is one process): 1 = one device (`device`),
+                                       k > 1 = genes sharded over devices 0..k-1 by one host thread each, 0 = all visible
+                                       devices.  Needs comm == NULL and host buffers.  Results are bit-identical for every k. */
 } cbs_input;
 
 typedef struct {                    /* every pointer optional (NULL = not wanted); caller-allocated        */

@@ -25,7 +25,8 @@ class CbsInput(C.Structure):
                 ("counts_f64", f64p), ("counts_i32", i32p), ("batch_idx", i32p), ("mod", f64p),
                 ("use_fallback", u8p), ("shrink", C.c_int32), ("shrink_disp", C.c_int32),
                 ("gene_subset_n", C.c_int32), ("seed", C.c_uint64), ("mc_mode", C.c_int32),
-                ("device", C.c_int32), ("comm", C.c_void_p), ("counts_on_device", C.c_int32)]
+                ("device", C.c_int32), ("comm", C.c_void_p), ("counts_on_device", C.c_int32),
+                ("n_gpus", C.c_int32)]
 
 
 class CbsOutput(C.Structure):
@@ -197,7 +198,7 @@ def combat_seq(counts, batch_idx, mod, shrink=False, shrink_disp=False, gene_sub
         fb = np.ascontiguousarray(use_fallback, dtype=np.uint8); inp.use_fallback = fb.ctypes.data_as(u8p)
     inp.shrink, inp.shrink_disp = int(shrink), int(shrink_disp)
     inp.gene_subset_n, inp.seed, inp.mc_mode = int(gene_subset_n or 0), int(seed), int(mc_mode)
-    inp.device = -1; inp.comm = None; inp.counts_on_device = 0
+    inp.device = -1; inp.comm = None; inp.counts_on_device = 0; inp.n_gpus = 1
     res = dict(adjusted=np.empty((G0, N), order="F"), keep=np.zeros(G0, np.uint8), lib_size=np.empty(N),
                disp_common=np.empty(B), phi_hat=np.empty((G0, B), order="F"), gamma_hat=np.empty((G0, B), order="F"),
                gamma_star=np.empty((G0, B), order="F"), phi_star=np.empty((G0, B), order="F"),

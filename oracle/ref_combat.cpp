@@ -23,6 +23,28 @@
 using namespace ref;
 static const double kNaN = std::numeric_limits<double>::quiet_NaN();
 
+// The engine's gene.subset.n sampler (include/combatseq.h, cbs_input.seed): a keyed 4-round Feistel permutation of
+// [0, G-1) with cycle walking; source k of target i is perm(k), shifted past i.  Same distribution as R's
+// sample(1:(G-1), n) (a uniformly random n-subset without replacement, redrawn per target gene, helper_seq.R:17-21);
+// R's Mersenne-Twister stream itself is not reproduced (PARITY UNPINNED for this option).
+static inline uint32_t feistel_mix(uint32_t x, uint32_t k) {
+    x ^= k; x *= 0x9E3779B1u; x ^= x >> 15; x *= 0x85EBCA77u; x ^= x >> 13; x *= 0xC2B2AE3Du; x ^= x >> 16;
+    return x;
+}
+static inline uint32_t feistel_perm(uint32_t idx, uint32_t m, int hb, uint64_t key) {
+    const uint32_t mask = (1u << hb) - 1u;
+    uint32_t v = idx;
+    do {
+        uint32_t l = v >> hb, r = v & mask;
+        for (int rd = 0; rd < 4; ++rd) {
+            const uint32_t f = feistel_mix(r, (uint32_t)(key >> (16 * rd)) + 0x632BE5ABu * (rd + 1) + (uint32_t)(key >> 32)) & mask;
+            const uint32_t nl = r; r = l ^ f; l = nl;
+        }
+        v = (l << hb) | r;
+    } while (v >= m);
+    return v;
+}
+
 // helper_seq.R:8-42 monte_carlo_int_NB for one batch.  dat G x n, mu G x n, gamma/phi G.
 // `targets` (optional) restricts the outer loop to a subset of target genes (for bounded CPU timing).
 static void mc_int_ref(long G, int n, const double* dat, const double* mu, const double* gamma, const double* phi,
@@ -35,18 +57,18 @@ static void mc_int_ref(long G, int n, const double* dat, const double* mu, const
 #endif
     for (long ti = 0; ti < nt; ++ti) {
         const long i = targets ? targets[ti] : ti;
-        // subset of source genes (helper_seq.R:17-21); the R stream (sample()) is not reproduced: seeded
-        // partial Fisher-Yates over 1..G-1 with a per-(seed,i) engine.
+        // subset of source genes (helper_seq.R:17-21), drawn with the engine's sampler (see feistel_perm above)
         std::vector<long> src;
         if (gene_subset_n > 0 && gene_subset_n < G - 1) {
-            std::vector<long> pool(G - 1);
-            for (long j = 0, k = 0; j < G; ++j) if (j != i) pool[k++] = j;
-            std::mt19937_64 eng(seed * 0x9E3779B97F4A7C15ULL + (uint64_t)i);
+            int hb = 1;
+            while ((1ull << (2 * hb)) < (unsigned long long)(G - 1)) ++hb;
+            const uint64_t key = seed * 0x9E3779B97F4A7C15ULL + (uint64_t)i * 0xD1B54A32D192ED03ULL + 0x2545F4914F6CDD1DULL;
+            src.resize(gene_subset_n);
             for (int k = 0; k < gene_subset_n; ++k) {
-                std::uniform_int_distribution<long> d(k, G - 2);
-                std::swap(pool[k], pool[d(eng)]);
+                long j = feistel_perm((uint32_t)k, (uint32_t)(G - 1), hb, key);
+                if (j >= i) ++j;
+                src[k] = j;
             }
-            src.assign(pool.begin(), pool.begin() + gene_subset_n);
         }
         const long ns = src.empty() ? G : (long)src.size();
         long double sumLH = 0, sumG = 0, sumP = 0;      // R's sum() accumulates in long double

@@ -30,7 +30,7 @@ def test_library_exports_every_declared_symbol(pkg):
     for n in names:
         assert hasattr(lib, n), "libcombatseq.so does not export %s" % n
     assert set(names) == set(pkg._lib.EXPORTS), "the ctypes binding and the header list different entry points"
-    assert lib.cbs_version() == 100
+    assert lib.cbs_version() == 200
 
 
 def test_struct_layout_matches_header(pkg):
@@ -97,7 +97,7 @@ def test_shard_range_partitions_in_reduction_chunks(pkg):
             for (a0, a1), (b0, b1) in zip(edges, edges[1:]):
                 assert a1 == b0 and a0 <= a1
             for g0, g1 in edges:
-                assert g0 % 1024 == 0 or g0 == G                # shard starts on a reduction-chunk boundary
+                assert g0 % 128 == 0 or g0 == G                 # shard starts on a reduction-chunk boundary
     with pytest.raises(L.CombatSeqError):
         L.shard_range(10, 2, 2)
 

@@ -17,7 +17,7 @@ import numpy as np
 import pytest
 
 ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
-CHUNK = 1024
+CHUNK = 128
 
 
 def _free_port():
@@ -54,7 +54,7 @@ def _worker(rank, world, port, out_dir):
     os.environ["MASTER_PORT"] = str(port)
     dist.init_process_group("gloo", rank=rank, world_size=world)
     try:
-        case = synth.c5(G=2600, n=4, B=3)                        # 3 reduction chunks: shards of 2048 and ~500 genes
+        case = synth.c5(G=2600, n=4, B=3)                        # 21 reduction chunks of 128 genes: shards of 1408 and ~1190 genes
         d = pkg.design.build_design(case.counts.shape[1], case.batch, case.group, case.covar_mod, case.full_mod)
         counts = case.counts.astype(np.float64)
         bidx, mod = d.batch_idx, d.mod
