@@ -86,7 +86,7 @@ int cbs_apl(int64_t G, int32_t n, const int32_t* counts, const double* design, i
     for (int d = 0; d < D; ++d) jobs[d] = {0, disp_per_gene ? 0.0 : disp[d]};
     double* d_pg = disp_per_gene ? upload(g_dev, "apl_phi_gene", disp, (size_t)G * D) : nullptr;
     double* d_apl = g_dev.get<double>("apl_grid", (size_t)G * D);
-    launch_apl(d_cnt, G, 0, G, d_logoff, ds.d_array, nullptr, d_pg, jobs, d_apl, 0);
+    launch_apl(d_cnt, G, 0, G, d_logoff, ds.d_array, nullptr, d_pg, jobs, d_apl, 0, &ds.h_array);
     CBS_CUDA(cudaMemcpy(apl, d_apl, (size_t)G * D * sizeof(double), cudaMemcpyDeviceToHost));
     CBS_ENTRY_END
 }

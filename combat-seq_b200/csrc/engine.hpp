@@ -16,6 +16,8 @@ struct Tuning {
     int mc_band = 1;             // 1 = abundance-sorted sources + screened source-tile lists for the contraction, 0 = all tiles
     int glm_scr = 1;             // 1 = Levenberg work arrays of the lane-group GLM kernel in shared memory (one copy per gene)
     int apl_fast = 1;            // 1 = lgamma tables + hoisted invariants in the APL kernel (same bits), 0 = per-sample calls
+    int apl_lanes = 1;           // 1 = lane-group APL kernel with the batch row staged in shared memory (one-way designs), 0 = k_apl
+    int glm_hist = 0;            // 1 = histogram of Levenberg iterations per gene (diagnostics; cbs_get_diag "glm_iter_*")
     double mc_tail_tol = 1e-8;   // largest accepted Chebyshev tail estimate (log-likelihood units)
 };
 struct Diag {
@@ -68,7 +70,8 @@ struct AplJob { int design; double phi; };
 
 // tu_apl.cu
 void launch_apl(const int32_t* cnt, long G, long g0, long g1, const double* logoff, const DesignDev* designs,
-                const unsigned char* sel, const double* phi_gene, const std::vector<AplJob>& jobs, double* d_apl, cudaStream_t st);
+                const unsigned char* sel, const double* phi_gene, const std::vector<AplJob>& jobs, double* d_apl, cudaStream_t st,
+                const std::vector<DesignDev>* h_designs = nullptr);     // host copies of `designs` (enables the lane-group kernel)
 void run_common_disp(const int32_t* cnt, long G, long g0, long g1, const double* logoff, const DesignSet& ds,
                      const unsigned char* sel, cbs_comm* comm, cudaStream_t st, std::vector<double>& common, int* n_steps);
 void run_tagwise_disp(const int32_t* cnt, long G, long g0, long g1, const double* logoff, const DesignSet& ds,

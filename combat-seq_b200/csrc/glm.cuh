@@ -15,6 +15,7 @@
 #include <cuda_runtime.h>
 #include <cstdint>
 #include <cmath>
+#include "fastmath.cuh"
 
 namespace cbs {
 
@@ -54,7 +55,9 @@ struct Row {
     const RowSrc& s; long g; double goff;
     __device__ Row(const RowSrc& s_, long g_, double goff_) : s(s_), g(g_), goff(goff_) {}
     __device__ __forceinline__ double y(int c) const {
-        const double v = (double)s.cnt[g + (long)c * s.G];
+        // counts are non-negative and below 2^31: 2^52 + x is exact in the low mantissa word, one DADD instead of I2F.F64
+        // (the conversion sits in every sweep of the fitters; I2F.F64 was the top stall of the GLM kernel, ncu round 1)
+        const double v = __hiloint2double(0x43300000, s.cnt[g + (long)c * s.G]) - 4503599627370496.0;
         return s.yadd ? v + s.yadd[c] : v;
     }
     __device__ __forceinline__ double off(int c) const { return s.logoff[2 * c] + goff; }
@@ -109,7 +112,7 @@ __device__ inline double fit_one_group(const DesignDev& d, const Row& r, int t0,
         const double ec = exp(cur) * eg;
         for (int t = t0 + ln; t < t1; t += LANES) {
             const int c = d.col[t];
-            const double mu = ec * r.lib(c), inv = 1.0 / (1 + mu * r.phi(c));
+            const double mu = ec * r.lib(c), inv = rcp_pos(1 + mu * r.phi(c));
             dl += (r.y(c) - mu) * inv;
             info += mu * inv;
         }
@@ -130,8 +133,9 @@ __device__ __forceinline__ double unit_nb_deviance(double y, double mu, double p
     }
     const double product = mu * phi;
     if (product > 1e6) return 2 * ((y - mu) / mu - log(y / mu)) * mu / (1 + product);
-    const double invphi = 1 / phi;
-    return 2 * (y * log(y / mu) + (y + invphi) * log((mu + invphi) / (y + invphi)));
+    // main branch: 1e-8 <= y < 2^31, 1e-8 <= mu <= 1e10, 1e-4 <= phi: every quotient is a positive normal number
+    const double invphi = rcp_pos(phi), ypr = y + invphi;
+    return 2 * (y * log_pos(y * rcp_pos(mu)) + ypr * log_pos((mu + invphi) * rcp_pos(ypr)));
 }
 
 __device__ __forceinline__ double lin_pred(const DesignDev& d, const Row& r, int t, const double* beta) {
@@ -161,7 +165,7 @@ __device__ inline double lev_sweep(const DesignDev& d, const Row& r, const doubl
                 const int col = d.col[t];
                 const double mu = E * r.lib(col), y = r.y(col), phi = r.phi(col);
                 dev += unit_nb_deviance(y, mu, phi);
-                const double inv = 1.0 / (1 + mu * phi);
+                const double inv = rcp_pos(1 + mu * phi);
                 sw += mu * inv; sz += (y - mu) * inv;
             }
             if (LANES > 1) { sw = lane_sum<LANES>(sw, gm); sz = lane_sum<LANES>(sz, gm); }
@@ -180,7 +184,7 @@ __device__ inline double lev_sweep(const DesignDev& d, const Row& r, const doubl
         const int c = d.col[t];
         const double mu = exp(lin_pred(d, r, t, beta)), y = r.y(c), phi = r.phi(c);
         dev += unit_nb_deviance(y, mu, phi);
-        const double inv = 1.0 / (1 + mu * phi), W = mu * inv, z = (y - mu) * inv;
+        const double inv = rcp_pos(1 + mu * phi), W = mu * inv, z = (y - mu) * inv;
         for (int k = d.rowptr[t]; k < d.rowptr[t + 1]; ++k) {
             const int ik = d.cidx[k];
             const double vk = d.cval[k];
@@ -217,7 +221,8 @@ __device__ inline void chol_solve_packed(const double* a, int p, double* b) {
     for (int i = p - 1; i >= 0; --i) { double s = b[i]; for (int k = i + 1; k < p; ++k) s -= a[tri(k, i)] * b[k]; b[i] = s / a[tri(i, i)]; }
 }
 
-// edgeR glm_levenberg::fit with the "null" start.  beta (out, p).  Returns false when y is all zero (beta = NaN, mu = 0).
+// edgeR glm_levenberg::fit with the "null" start.  beta (out, p).  Returns the number of iterations, or -1 when y is all
+// zero (beta = NaN, mu = 0).
 // Work arrays of one Levenberg fit: 3 packed p x p triangles and 4 p-vectors.  One thread per gene keeps them in local
 // memory.  A lane group can share ONE copy in shared memory (SCR = true, `scr` = lev_scratch_doubles<PM>() doubles owned
 // by the group): outside the sample sweeps every lane of the group executes the same instructions on bit-identical
@@ -230,8 +235,8 @@ __host__ __device__ constexpr int lev_scratch_doubles() {
     return (3 * (PM * (PM + 1) / 2) + 4 * PM + 3) / 8 * 8 + 4;
 }
 template <int LANES = 1, int PM = PMAX, bool SCR = false>
-__device__ inline bool fit_levenberg(const DesignDev& d, const Row& r, double* beta, int ln = 0, unsigned gm = 0xffffffffu,
-                                     int maxit = 250, double tolerance = 1e-6, double* scr = nullptr) {
+__device__ inline int fit_levenberg(const DesignDev& d, const Row& r, double* beta, int ln = 0, unsigned gm = 0xffffffffu,
+                                    int maxit = 250, double tolerance = 1e-6, double* scr = nullptr) {
     constexpr int PT = PM * (PM + 1) / 2;
     constexpr int LT = SCR ? 1 : PT, LV = SCR ? 1 : PM;
     const int p = d.p, pt = p * (p + 1) / 2;
@@ -254,7 +259,7 @@ __device__ inline bool fit_levenberg(const DesignDev& d, const Row& r, double* b
         sum_weight += w;
     }
     if (LANES > 1) { ymax = lane_max<LANES>(ymax, gm); sum_exprs = lane_sum<LANES>(sum_exprs, gm); sum_weight = lane_sum<LANES>(sum_weight, gm); }
-    if (ymax < CBS_LOW_VALUE) { for (int i = 0; i < p; ++i) beta[i] = nan(""); return false; }
+    if (ymax < CBS_LOW_VALUE) { for (int i = 0; i < p; ++i) beta[i] = nan(""); return -1; }
     const double c0 = log(sum_exprs / sum_weight);
     for (int i = 0; i < p; ++i) beta[i] = d.start[i] * c0;
     double dev = lev_sweep<LANES>(d, r, beta, xtwx, dl, ln, gm);
@@ -294,14 +299,14 @@ __device__ inline bool fit_levenberg(const DesignDev& d, const Row& r, double* b
         for (int i = 0; i < pt; ++i) xtwx[i] = xtwx_new[i];     // information at the accepted coefficients
         for (int i = 0; i < p; ++i) dl[i] = dl_new[i];
     }
-    return true;
+    return iter;
 }
 
 // glmFit.default's plain fit of one gene: coefficients beta[p]; cellbeta[p] additionally for one-way designs.
-// Returns the mode used so that the caller can form fitted values with fitted_at().
+// Returns the Levenberg iteration count (0 for one-way designs, -1 for an all-zero row).
 template <int LANES = 1, int PM = PMAX>
-__device__ inline void fit_gene(const DesignDev& d, const Row& r, double* beta, double* cellbeta, int ln = 0,
-                                unsigned gm = 0xffffffffu, double* scr = nullptr) {
+__device__ inline int fit_gene(const DesignDev& d, const Row& r, double* beta, double* cellbeta, int ln = 0,
+                               unsigned gm = 0xffffffffu, double* scr = nullptr) {
     if (d.oneway) {
         for (int l = 0; l < d.p; ++l) {
             const double b = fit_one_group<LANES>(d, r, d.cell_start[l], d.cell_start[l + 1], 50, 1e-10, ln, gm);
@@ -313,9 +318,10 @@ __device__ inline void fit_gene(const DesignDev& d, const Row& r, double* beta, 
             beta[k] = s;
         }
     } else {
-        if (LANES > 1 && scr != nullptr && d.ncls > 0) fit_levenberg<LANES, PM, true>(d, r, beta, ln, gm, 250, 1e-6, scr);
-        else fit_levenberg<LANES, PM, false>(d, r, beta, ln, gm);
+        if (LANES > 1 && scr != nullptr && d.ncls > 0) return fit_levenberg<LANES, PM, true>(d, r, beta, ln, gm, 250, 1e-6, scr);
+        return fit_levenberg<LANES, PM, false>(d, r, beta, ln, gm);
     }
+    return 0;
 }
 
 // LAPACK dsytf2 (uplo = 'L', Bunch-Kaufman) on a packed lower triangle; the diagonal of D is left on the diagonal
@@ -414,14 +420,14 @@ __device__ inline double apl_gene(const DesignDev& d, const Row& r, const double
         double loglik;
         const double lgy1 = (lgfact && y < (double)LGFACT_N && !r.s.yadd) ? lgfact[(int)y] : lgamma(y + 1);
         if (phi > 0) {
-            const double rr = scalar_phi ? rr_c : 1 / phi, logmur = log(mu + rr);
+            const double rr = scalar_phi ? rr_c : 1 / phi, logmur = log_pos(mu + rr);
             const double logrr = scalar_phi ? logrr_c : log(rr), lgrr = scalar_phi ? lgrr_c : lgamma(rr);
             const double lgyr = (scalar_phi && lgr && y < (double)LGFACT_N && !r.s.yadd) ? lgr[(int)y] : lgamma(y + rr);
             loglik = y * logmu - y * logmur + rr * logrr - rr * logmur + lgyr - lgy1 - lgrr;
         } else {
             loglik = y * logmu - mu - lgy1;
         }
-        const double W = mu / (1 + phi * mu);
+        const double W = mu * rcp_pos(1 + phi * mu);
         sum_loglik += loglik;
         sumw += W;
         if (p > 1)

@@ -432,9 +432,47 @@ CBS_HD double nb_quantile_fast(double p, double size, double prob) {
     return nb_search_exact<NI>(y, nb_cdf_pmf_t<NI>(y, size, prob, q).F, pp, size, prob, q);
 }
 
-// match_quantiles for one element (helper_seq.R:46-64)
+// Small counts: both distribution functions by direct summation of the pmf recurrence from 0,
+//   pmf(0) = prob^size,  pmf(j+1) = pmf(j) (j + size)/(j + 1) q,   F(k) = sum_{j<=k} pmf(j),
+// four FP64 instructions per term with the reciprocals 1/(j+1) from a table, against ~1500 for one continued fraction:
+// p = F_old(x - 1) costs x terms and the quantile is found by summing the NEW distribution until it reaches
+// p (1 - 64 eps) (no Cornish-Fisher start, no refinement).  Each sum carries a relative error below 1e-13 (term
+// recurrence + exp(size log prob)); whenever a decision (the |p - 1| < 1e-4 pass-through, F_new(y) >= p') is closer than
+// 1e-12 the element is handed to the continued-fraction routines below, so the answer is the one they give.
+// inv[j] = 1/j for 1 <= j < MQ_INV_N.  Returns false when the element was not decided here.
+constexpr int MQ_INV_N = 1024;
+constexpr double MQ_SMALL_X = 320.0;
+CBS_HD bool match_small(double x, double old_mu, double so, double new_mu, double sn, const double* __restrict__ inv, double* out) {
+    const int xi = (int)x;                                       // 2 <= x <= MQ_SMALL_X
+    const double qo = old_mu / (so + old_mu);
+    double f = exp(-so * log1p(old_mu / so));                    // pmf_old(0) = (so / (so + mu))^so
+    if (!(f > 1e-250)) return false;
+    double F = f;
+    for (int j = 0; j < xi - 1; ++j) { f *= (j + so) * inv[j + 1] * qo; F += f; }      // F = P_old(X <= x - 1)
+    const double d1 = fabs(F - 1);
+    if (fabs(d1 - 1e-4) < 1e-11 || !(F > 0)) return false;
+    if (d1 < 1e-4) { *out = x; return true; }                    // helper_seq.R:54-56
+    const double qn = new_mu / (sn + new_mu);
+    double g = exp(-sn * log1p(new_mu / sn));
+    if (!(g > 1e-250)) return false;
+    const double pp = F * (1 - 64 * DBL_EPSILON);
+    double Fn = g, Fm = 0;
+    int y = 0;
+    while (Fn < pp) {
+        if (y >= MQ_INV_N - 2) return false;
+        g *= (y + sn) * inv[y + 1] * qn;
+        ++y; Fm = Fn; Fn += g;
+    }
+    const double tol = 1e-12 * fmax(Fn, pp);
+    if (fabs(Fn - pp) <= tol || (y > 0 && fabs(Fm - pp) <= tol)) return false;
+    *out = 1 + (double)y;                                        // helper_seq.R:58
+    return true;
+}
+
+// match_quantiles for one element (helper_seq.R:46-64); inv (optional): the reciprocal table of match_small
 template <bool NI = false>
-CBS_HD double match_one_fast(double x, double old_mu, double old_phi, double new_mu, double new_phi) {
+CBS_HD double match_one_fast(double x, double old_mu, double old_phi, double new_mu, double new_phi,
+                             const double* __restrict__ inv = nullptr) {
     if (x <= 1) return x;                                      // helper_seq.R:50-51
     const double so = 1.0 / old_phi, sn = 1.0 / new_phi;
     if (!(old_mu > 0) || !(new_mu > 0) || !isfinite(old_mu) || !isfinite(new_mu) || !(so > 0) || !(sn > 0) ||
@@ -442,6 +480,10 @@ CBS_HD double match_one_fast(double x, double old_mu, double old_phi, double new
         const double tmp_p = NI ? pnbinom_mu_ni(x - 1, so, old_mu) : pnbinom_mu(x - 1, so, old_mu);
         if (fabs(tmp_p - 1) < 1e-4) return x;
         return 1 + (NI ? qnbinom_mu_ni(tmp_p, sn, new_mu) : qnbinom_mu(tmp_p, sn, new_mu));
+    }
+    if (inv != nullptr && x <= MQ_SMALL_X) {
+        double r;
+        if (match_small(x, old_mu, so, new_mu, sn, inv, &r)) return r;
     }
     const double tmp_p = nb_cdf_pmf_t<NI>(x - 1, so, so / (so + old_mu), old_mu / (so + old_mu)).F;     // helper_seq.R:53
     if (fabs(tmp_p - 1) < 1e-4) return x;                      // helper_seq.R:54-56

@@ -69,6 +69,15 @@ int cbs_set_tuning(const char* key, double value) {
     if (!strcmp(key, "mc_band")) { g_tune.mc_band = value != 0; return CBS_OK; }
     if (!strcmp(key, "mc_tail_tol")) { g_tune.mc_tail_tol = value; return CBS_OK; }
     if (!strcmp(key, "apl_fast")) { g_tune.apl_fast = value != 0; return CBS_OK; }
+    if (!strcmp(key, "apl_lanes")) { g_tune.apl_lanes = value != 0; return CBS_OK; }
+    if (!strcmp(key, "glm_hist")) {
+        g_tune.glm_hist = value != 0;
+        if (g_tune.glm_hist && have_gpu()) {
+            try { enter_device(-1); CBS_CUDA(cudaMemset(g_dev.get<int>("glm_iter_hist", 256), 0, 256 * sizeof(int))); }
+            catch (const CbsError& e) { return e.code; }
+        }
+        return CBS_OK;
+    }
     if (!strcmp(key, "glm_scr")) { g_tune.glm_scr = value != 0; return CBS_OK; }
     return fail(CBS_EINVAL, "unknown tuning key '%s'", key);
 }
@@ -79,6 +88,17 @@ int cbs_get_diag(const char* key, double* value) {
     if (!strcmp(key, "mc_terms")) { *value = g_diag.mc_kc; return CBS_OK; }
     if (!strcmp(key, "mc_tiles_done")) { *value = g_diag.mc_tiles_done; return CBS_OK; }
     if (!strcmp(key, "mc_tiles_all")) { *value = g_diag.mc_tiles_all; return CBS_OK; }
+    if (!strncmp(key, "glm_iter_", 9)) {        // "glm_iter_<k>": genes whose Levenberg fit took k iterations (k = 255: 255 or more), summed over the launches
+        const int k = atoi(key + 9);
+        if (k < 0 || k > 255 || !g_tune.glm_hist || !have_gpu()) return fail(CBS_EINVAL, "glm_iter_<0..255> needs the glm_hist knob");
+        try {
+            enter_device(-1);
+            int h = 0;
+            CBS_CUDA(cudaMemcpy(&h, g_dev.get<int>("glm_iter_hist", 256) + k, sizeof(int), cudaMemcpyDeviceToHost));
+            *value = h;
+        } catch (const CbsError& e) { return e.code; }
+        return CBS_OK;
+    }
     if (!strcmp(key, "reset")) { g_diag = Diag(); *value = 0; return CBS_OK; }
     return fail(CBS_EINVAL, "unknown diagnostics key '%s'", key);
 }

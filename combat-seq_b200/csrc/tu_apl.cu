@@ -81,11 +81,193 @@ __global__ void k_fill_apl(double* __restrict__ p, long n, double v) {
     if (i < n) p[i] = v;
 }
 
+// ---- a5/a6, one-way designs: lane groups with the batch's counts staged once per gene ---------------------------------
+// One gene = LANES consecutive lanes (2 for cells of up to 128 samples: every lane redoes the exp, the division and the
+// butterfly of a Newton step, so short cells want few lanes; 8 for longer ones); a block stages the batch's row of its
+// 128 / LANES genes in shared memory as doubles
+// (converted once), together with the batch's library sizes, and then evaluates EVERY dispersion of the group (11 grid
+// points, or the batch's current Brent abscissa) on the staged row: the counts are read from memory once per launch
+// instead of once per evaluation, the Newton sweeps of glm_one_group run on shared-memory operands with the samples of
+// a cell split over the lanes (XOR-butterfly sums: every lane of a gene holds the same bits, so the data-dependent
+// iteration stays uniform inside the group), and everything that does not depend on the dispersion (start values,
+// sum of lgamma(y + 1)) is computed once per gene.  Used when the batch's design is one-way (every within-batch design of
+// the BASELINE configs but C3b), p <= APLL_PM cells and n <= APLL_MAXN samples; anything else takes k_apl.
+constexpr int APLL_PM = 4, APLL_MAXN = 512;
+struct AplGroups { int n; int start[APL_MAX_EVALS + 1]; };      // evaluations [start[k], start[k+1]) share one design
+__host__ __device__ inline int apll_row_stride(int n, int lanes) { return (n + 15) / 16 * 16 + lanes; }     // = lanes mod 16: the 16 / lanes genes of a half-warp hit disjoint banks
+
+template <int APLL_LANES>
+__global__ void __launch_bounds__(128)
+k_apl_lanes(const int32_t* __restrict__ cnt, long G, long g0, long g1, const double* __restrict__ logoff,
+            const DesignDev* __restrict__ designs, const unsigned char* __restrict__ sel, AplLaunch L, AplGroups GR,
+            double* __restrict__ apl, const double* __restrict__ lgfact, const double* __restrict__ lgr) {
+    constexpr int APLL_GENES = 128 / APLL_LANES;
+    extern __shared__ double apl_sm[];
+    const int e0 = GR.start[blockIdx.y], e1 = GR.start[blockIdx.y + 1];
+    const int di = L.design[e0];
+    const DesignDev d = designs[di];
+    const int n = d.n, p = d.p, ns = apll_row_stride(n, APLL_LANES);
+    double* y_s = apl_sm;                       // [genes][ns]
+    double* lib_s = apl_sm + APLL_GENES * ns;   // [n] library sizes, [n] log library sizes (design order)
+    double* off_s = lib_s + n;
+    const long gbase = g0 + (long)blockIdx.x * APLL_GENES;
+    for (int k = threadIdx.x; k < APLL_GENES * n; k += blockDim.x) {        // consecutive genes per sample: whole sectors
+        const int gi = k & (APLL_GENES - 1), t = k / APLL_GENES;
+        const long g = gbase + gi;
+        y_s[gi * ns + t] = g < g1 ? (double)cnt[g + (long)d.col[t] * G] : 0.0;
+    }
+    for (int t = threadIdx.x; t < n; t += blockDim.x) { const int c = d.col[t]; off_s[t] = logoff[2 * c]; lib_s[t] = logoff[2 * c + 1]; }
+    __syncthreads();
+    const int gslot = threadIdx.x / APLL_LANES, ln = threadIdx.x % APLL_LANES;
+    const long g = gbase + gslot;
+    if (g >= g1) return;
+    const unsigned gm = ((1u << APLL_LANES) - 1u) << ((threadIdx.x & 31) - ln);
+    if (sel && !sel[(long)di * G + g]) {
+        for (int e = e0 + ln; e < e1; e += APLL_LANES) apl[(long)e * G + g] = 0.0;
+        return;
+    }
+    const double* y = y_s + gslot * ns;
+    // dispersion-independent: glm_one_group's start value per cell and sum_s lgamma(y_s + 1)
+    double start0[APLL_PM];
+    double sum_lgy1 = 0;
+#pragma unroll
+    for (int l = 0; l < APLL_PM; ++l) {
+        if (l >= p) break;
+        const int t0 = d.cell_start[l], t1 = d.cell_start[l + 1];
+        double cur = 0, nz = 0;
+        for (int t = t0 + ln; t < t1; t += APLL_LANES) {
+            const double yy = y[t];
+            if (yy > CBS_LOW_VALUE) { cur += yy / lib_s[t]; nz = 1; }
+            sum_lgy1 += (lgfact && yy < (double)LGFACT_N) ? lgfact[(int)yy] : lgamma(yy + 1);
+        }
+        cur = lane_sum<APLL_LANES>(cur, gm); nz = lane_max<APLL_LANES>(nz, gm);
+        start0[l] = nz > 0 ? log(cur / (double)(t1 - t0)) : -INFINITY;
+    }
+    sum_lgy1 = lane_sum<APLL_LANES>(sum_lgy1, gm);
+
+    for (int e = e0; e < e1; ++e) {
+        const double phi = L.phi[e];
+        const double* lgr_e = lgr ? lgr + (long)e * LGFACT_N : nullptr;
+        const double rr = phi > 0 ? 1 / phi : 0.0, logrr = phi > 0 ? log(rr) : 0.0, lgrr = phi > 0 ? lgamma(rr) : 0.0;
+        double Wc[APLL_PM];
+        double ll = 0, nlive = 0, sumw = 0;
+#pragma unroll
+        for (int l = 0; l < APLL_PM; ++l) {
+            if (l >= p) break;
+            const int t0 = d.cell_start[l], t1 = d.cell_start[l + 1];
+            // edgeR glm_one_group: Newton on the cell's coefficient, maxit 50, |step| < 1e-10
+            double cur = start0[l];
+            if (cur > -INFINITY) {
+                for (int it = 0; it < 50; ++it) {
+                    const double ec = exp(cur);
+                    double dl = 0, info = 0;
+                    for (int t = t0 + ln; t < t1; t += APLL_LANES) {
+                        const double mu = ec * lib_s[t], inv = rcp_pos(1 + mu * phi);
+                        dl += (y[t] - mu) * inv;
+                        info += mu * inv;
+                    }
+                    dl = lane_sum<APLL_LANES>(dl, gm); info = lane_sum<APLL_LANES>(info, gm);
+                    const double step = dl / info;
+                    cur += step;
+                    if (fabs(step) < 1e-10) break;
+                }
+            }
+            const double cb = fmax(cur, -1e8);                   // mglmOneWay: pmax(beta, -1e8)
+            const double ecell = exp(cb);
+            double w = 0;
+            for (int t = t0 + ln; t < t1; t += APLL_LANES) {
+                const double mu = ecell * lib_s[t];
+                if (mu == 0) continue;
+                const double yy = y[t], logmu = cb + off_s[t];
+                if (phi > 0) {
+                    const double logmur = log_pos(mu + rr);
+                    const double lgyr = (lgr_e && yy < (double)LGFACT_N) ? lgr_e[(int)yy] : lgamma(yy + rr);
+                    ll += yy * logmu - yy * logmur - rr * logmur + lgyr;
+                } else {
+                    ll += yy * logmu - mu;
+                }
+                nlive += 1;
+                w += mu * rcp_pos(1 + phi * mu);
+            }
+            w = lane_sum<APLL_LANES>(w, gm);
+            Wc[l] = w;
+            sumw += w;
+        }
+        ll = lane_sum<APLL_LANES>(ll, gm); nlive = lane_sum<APLL_LANES>(nlive, gm);
+        const double sum_loglik = ll + nlive * (rr * logrr - lgrr) - sum_lgy1;      // (samples with mu == 0 have y == 0: lgamma(1) = 0)
+        double adj;
+        if (p == 1) adj = log(fabs(sumw)) / 2;
+        else {
+            double wm[APLL_PM * (APLL_PM + 1) / 2];
+            for (int i = 0; i < p * (p + 1) / 2; ++i) wm[i] = 0;
+#pragma unroll
+            for (int l = 0; l < APLL_PM; ++l) {                    // X'WX from the cell sums of W (one design row per cell)
+                if (l >= p) break;
+                const int t0 = d.cell_start[l];
+                for (int k = d.rowptr[t0]; k < d.rowptr[t0 + 1]; ++k)
+                    for (int k2 = d.rowptr[t0]; k2 <= k; ++k2) wm[tri(d.cidx[k], d.cidx[k2])] += d.cval[k] * d.cval[k2] * Wc[l];
+            }
+            sytf2_packed(wm, p);
+            const double log_low = log(CBS_LOW_VALUE);
+            double sld = 0;
+            for (int i = 0; i < p; ++i) {
+                const double v = wm[tri(i, i)];
+                sld += (v < CBS_LOW_VALUE || !isfinite(v)) ? log_low : log(v);
+            }
+            adj = sld * 0.5;
+        }
+        if (ln == 0) apl[(long)e * G + g] = sum_loglik - adj;
+    }
+}
+
 // APL of genes [g0,g1) for every job -> d_apl[job*G + g]
 void launch_apl(const int32_t* cnt, long G, long g0, long g1, const double* logoff, const DesignDev* designs,
                 const unsigned char* sel, const double* phi_gene, const std::vector<AplJob>& jobs, double* d_apl,
-                cudaStream_t st) {
+                cudaStream_t st, const std::vector<DesignDev>* h_designs) {
     if (g1 <= g0) return;
+    // lane-group kernel: scalar dispersions, every design of the launch one-way with few cells and a batch that fits shared memory
+    bool lanes_ok = g_tune.apl_lanes && !phi_gene && h_designs != nullptr && !jobs.empty();
+    int nmax = 0;
+    if (lanes_ok)
+        for (const AplJob& j : jobs) {
+            const DesignDev& hd = (*h_designs)[j.design];
+            lanes_ok = lanes_ok && hd.oneway && hd.p <= APLL_PM && hd.n <= APLL_MAXN && j.phi > 0;
+            nmax = std::max(nmax, hd.n);
+        }
+    const int lanes = nmax <= 256 ? 2 : 8, genes = 128 / lanes;          // (cells are at most as long as the batch)
+    lanes_ok = lanes_ok && ((size_t)genes * apll_row_stride(nmax, lanes) + 2 * (size_t)nmax) * sizeof(double) <= 200 * 1024;
+    if (lanes_ok) {
+        double* lgfact = g_dev.get<double>("lgfact", (size_t)LGFACT_N);
+        CBS_LAUNCH(k_lgfact_init, grid1(LGFACT_N, 256), 256, 0, st, lgfact);
+        const size_t smem = ((size_t)genes * apll_row_stride(nmax, lanes) + 2 * (size_t)nmax) * sizeof(double);
+        t_ctx->set_func_attr((const void*)k_apl_lanes<2>, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024);
+        t_ctx->set_func_attr((const void*)k_apl_lanes<8>, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024);
+        for (size_t e0 = 0; e0 < jobs.size();) {
+            AplLaunch L; AplGroups GR;
+            L.n_evals = 0; GR.n = 0;
+            // whole groups (runs of equal design) per launch
+            while (e0 < jobs.size()) {
+                size_t e1 = e0;
+                while (e1 < jobs.size() && jobs[e1].design == jobs[e0].design && e1 - e0 < 16) ++e1;
+                if (L.n_evals + (int)(e1 - e0) > APL_MAX_EVALS) break;
+                GR.start[GR.n++] = L.n_evals;
+                for (size_t e = e0; e < e1; ++e) { L.design[L.n_evals] = jobs[e].design; L.phi[L.n_evals] = jobs[e].phi; ++L.n_evals; }
+                e0 = e1;
+            }
+            GR.start[GR.n] = L.n_evals;
+            const size_t first = e0 - (size_t)L.n_evals;
+            double* t = g_dev.get<double>("lgr", (size_t)APL_MAX_EVALS * LGFACT_N);
+            CBS_LAUNCH(k_lgr_init, dim3(LGFACT_N / 256, (unsigned)L.n_evals), 256, 0, st, L, t);
+            dim3 grid((unsigned)((g1 - g0 + genes - 1) / genes), (unsigned)GR.n);
+            if (lanes == 2)
+                CBS_LAUNCH(k_apl_lanes<2>, grid, 128, smem, st, cnt, G, g0, g1, logoff, designs, sel, L, GR, d_apl + first * G,
+                           (const double*)lgfact, (const double*)t);
+            else
+                CBS_LAUNCH(k_apl_lanes<8>, grid, 128, smem, st, cnt, G, g0, g1, logoff, designs, sel, L, GR, d_apl + first * G,
+                           (const double*)lgfact, (const double*)t);
+        }
+        return;
+    }
     double* lgfact = g_dev.get<double>("lgfact", (size_t)LGFACT_N);
     CBS_LAUNCH(k_lgfact_init, grid1(LGFACT_N, 256), 256, 0, st, lgfact);
     for (size_t e0 = 0; e0 < jobs.size(); e0 += APL_MAX_EVALS) {
@@ -151,7 +333,7 @@ void run_common_disp(const int32_t* cnt, long G, long g0, long g1, const double*
         for (int b = 0; b < nb; ++b)
             if (active[b] && !br[b].done) { const double x = br[b].query(); jobs.push_back({b, x * x * x * x}); who.push_back(b); }
         if (jobs.empty()) break;
-        launch_apl(cnt, G, g0, g1, logoff, ds.d_array, sel, nullptr, jobs, d_apl, st);
+        launch_apl(cnt, G, g0, g1, logoff, ds.d_array, sel, nullptr, jobs, d_apl, st, &ds.h_array);
         std::vector<double> sums;
         apl_sums(d_apl, G, g0, g1, sel, jobs, comm, st, sums);
         for (size_t k = 0; k < who.size(); ++k) br[who[k]].feed(-sums[k]);     // optimize(maximum = TRUE)
@@ -176,7 +358,7 @@ void run_tagwise_disp(const int32_t* cnt, long G, long g0, long g1, const double
         for (int k = 0; k < 11; ++k) jobs.push_back({b, common[b] * std::pow(2.0, -6.0 + k * (12.0 / 10))});
     }
     double* d_apl = jobs.empty() ? nullptr : g_dev.get<double>("apl_grid", jobs.size() * (size_t)G);
-    if (!jobs.empty()) launch_apl(cnt, G, g0, g1, logoff, ds.d_array, sel, nullptr, jobs, d_apl, st);
+    if (!jobs.empty()) launch_apl(cnt, G, g0, g1, logoff, ds.d_array, sel, nullptr, jobs, d_apl, st, &ds.h_array);
     for (int b = 0; b < nb; ++b) {
         if (do_batch[b]) {
             CBS_LAUNCH(k_tagwise_max, grid1(g1 - g0, 128), 128, 0, st, d_apl + (size_t)job0[b] * G, G, g0, g1,

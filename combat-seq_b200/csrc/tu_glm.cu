@@ -60,7 +60,7 @@ k_glm_fit_lanes(const int32_t* __restrict__ cnt, long G, long g0, long g1, const
                 const double* __restrict__ yadd, double two_prior_over_meanlib, const double* __restrict__ phi,
                 const int* __restrict__ phi_col, const DesignDev* __restrict__ design, const double* __restrict__ goff_in,
                 int mode, double* __restrict__ coef, double* __restrict__ fitted, const double* __restrict__ alpha_w,
-                int n_alpha, double* __restrict__ alpha_out, int use_scr) {
+                int n_alpha, double* __restrict__ alpha_out, int use_scr, int* __restrict__ iter_hist) {
     const long slot = ((long)blockIdx.x * blockDim.x + threadIdx.x) / GLM_LANES;
     const long g = g0 + slot;
     const int ln = threadIdx.x % GLM_LANES;
@@ -74,7 +74,8 @@ k_glm_fit_lanes(const int32_t* __restrict__ cnt, long G, long g0, long g1, const
     double beta[PM], cellbeta[PM];
     extern __shared__ __align__(16) double glm_scr[];       // lev_scratch_doubles<PM>() per lane group, or nothing
     double* scr = use_scr ? glm_scr + (threadIdx.x / GLM_LANES) * lev_scratch_doubles<PM>() : nullptr;
-    fit_gene<GLM_LANES, PM>(d, r, beta, cellbeta, ln, gm, scr);
+    const int n_iter = fit_gene<GLM_LANES, PM>(d, r, beta, cellbeta, ln, gm, scr);
+    if (iter_hist && ln == 0) atomicAdd(&iter_hist[max(0, min(n_iter, 255))], 1);      // diagnostics: Levenberg iterations per gene
     if (coef) for (int k = ln; k < d.p; k += GLM_LANES) coef[g + (long)k * G] = beta[k];
     if (alpha_out && ln == 0) {
         double a = 0;
@@ -117,6 +118,7 @@ void run_glm_fit(const int32_t* cnt, long G, long g0, long g1, int N, const doub
     }
     // designs with few columns go to the lane-group kernel (GLM_LANES lanes per gene); wider ones stay one thread per gene
     const bool lanes = h_p <= GLM_LANES_PMAX;
+    int* d_hist = g_tune.glm_hist ? g_dev.get<int>("glm_iter_hist", 256) : nullptr;     // zeroed by cbs_get_diag("reset")
     const dim3 lgrid = grid1((g1 - g0) * GLM_LANES, 128);
     auto launch = [&](const double* yadd, double tp, int mode, double* coef, double* fitted, double* alpha) {
         // one shared-memory copy of the Levenberg work arrays per gene (16 genes per block)
@@ -125,7 +127,7 @@ void run_glm_fit(const int32_t* cnt, long G, long g0, long g1, int N, const doub
             t_ctx->set_func_attr((const void*)k_glm_fit_lanes<PM_>, cudaFuncAttributeMaxDynamicSharedMemorySize, \
                                  (int)((128 / GLM_LANES) * lev_scratch_doubles<PM_>() * sizeof(double))); \
             CBS_LAUNCH(k_glm_fit_lanes<PM_>, lgrid, 128, smem, st, cnt, G, g0, g1, d_logoff, yadd, tp, d_phi, \
-                       d_phi_col, d_design, d_goff, mode, coef, fitted, d_alpha_w, n_alpha, alpha, g_tune.glm_scr ? 1 : 0); } while (0)
+                       d_phi_col, d_design, d_goff, mode, coef, fitted, d_alpha_w, n_alpha, alpha, g_tune.glm_scr ? 1 : 0, d_hist); } while (0)
         if (lanes) {
             if (h_p <= 4) CBS_GLM_LANES(4); else if (h_p <= 8) CBS_GLM_LANES(8); else if (h_p <= 12) CBS_GLM_LANES(12); else CBS_GLM_LANES(16);
         } else

@@ -21,6 +21,9 @@ k_match_quantiles_warp(const int32_t* __restrict__ cnt, long G, long g0, long g1
                        const double* __restrict__ phi_hat, const double* __restrict__ gamma_star,
                        const double* __restrict__ phi_star, const int* __restrict__ keep_idx, long G0,
                        double* __restrict__ out) {
+    __shared__ double inv_s[MQ_INV_N];                          // 1/j for the small-count path (nbmath.cuh match_small)
+    for (int j = threadIdx.x; j < MQ_INV_N; j += blockDim.x) inv_s[j] = j ? 1.0 / (double)j : 0.0;
+    __syncthreads();
     const long g = g0 + (long)blockIdx.x * 4 + (threadIdx.x >> 5);
     const int si = blockIdx.y * 32 + (threadIdx.x & 31);
     if (g >= g1 || si >= N) return;
@@ -28,7 +31,7 @@ k_match_quantiles_warp(const int32_t* __restrict__ cnt, long G, long g0, long g1
     const double x = (double)cnt[g + (long)s * G];
     const double old_mu = mu_hat[g + (long)s * G];
     const double new_mu = exp(log(old_mu) - gamma_star[g + (long)b * G]);     // ComBat_seq.R:176
-    out[(keep_idx ? (long)keep_idx[g] : g) + (long)s * G0] = match_one_fast<true>(x, old_mu, phi_hat[g + (long)b * G], new_mu, phi_star[g]);
+    out[(keep_idx ? (long)keep_idx[g] : g) + (long)s * G0] = match_one_fast<true>(x, old_mu, phi_hat[g + (long)b * G], new_mu, phi_star[g], inv_s);
 }
 
 // generic per-batch form used by cbs_match_quantiles (explicit new_mu)
@@ -36,11 +39,14 @@ __global__ void __launch_bounds__(128)
 k_match_quantiles_plain(const int32_t* __restrict__ cnt, long G, int n, const double* __restrict__ old_mu,
                         const double* __restrict__ old_phi, const double* __restrict__ new_mu,
                         const double* __restrict__ new_phi, double* __restrict__ out) {
+    __shared__ double inv_s[MQ_INV_N];
+    for (int j = threadIdx.x; j < MQ_INV_N; j += blockDim.x) inv_s[j] = j ? 1.0 / (double)j : 0.0;
+    __syncthreads();
     const long g = (long)blockIdx.x * blockDim.x + threadIdx.x;
     const int s = blockIdx.y;
     if (g >= G) return;
     const long k = g + (long)s * G;
-    out[k] = match_one_fast<true>((double)cnt[k], old_mu[k], old_phi[g], new_mu[k], new_phi[g]);
+    out[k] = match_one_fast<true>((double)cnt[k], old_mu[k], old_phi[g], new_mu[k], new_phi[g], inv_s);
 }
 
 // ---- elementwise NB primitives (cbs_nb_logpmf / cbs_nb_cdf / cbs_nb_quantile) ----------------------------

@@ -280,8 +280,8 @@ k_scr_mma(const __nv_bfloat16* __restrict__ Pt, const __nv_bfloat16* __restrict_
             tc_fence_before();
             __syncwarp();
             if (lane == 0) sbar_arrive(&acc_empty[as]);
-            hi[(long)J * ss.rows + grow] = mhi;
-            lo[(long)J * ss.rows + grow] = mlo;
+            __stcs(&hi[(long)J * ss.rows + grow], mhi);            // streamed: read once by k_mcg_list_screened, keep L2 for the operands
+            __stcs(&lo[(long)J * ss.rows + grow], mlo);
         }
     }
     tc_fence_before();
@@ -292,14 +292,18 @@ k_scr_mma(const __nv_bfloat16* __restrict__ Pt, const __nv_bfloat16* __restrict_
     }
 }
 
-// work items of the screening kernel: every owned target block x source-tile ranges of about `chunk` tiles
+// Work items of the screening kernel: every owned target block x source-tile ranges of NJ / nchunk tiles, ordered
+// range-major: the CTAs that are resident at the same time stream the SAME range of source tiles (a few MB), so the B
+// operand is read from HBM once per range and served from L2 to the other SMs; block-major order has every SM streaming a
+// different part of the 70 MB operand and the pass runs at HBM speed.
 __global__ void k_scr_items(McgOwn own, long nrb, int NJ, int nchunk, int3* __restrict__ items) {
     const long lb = (long)blockIdx.x * blockDim.x + threadIdx.x;
-    if (lb >= own.nblocks(nrb * SCR_BM)) return;
+    const long nb = own.nblocks(nrb * SCR_BM);
+    if (lb >= nb) return;
     const int blk = (int)(lb * own.world + own.rank);
     for (int c = 0; c < nchunk; ++c) {
         const int a = (int)((long)NJ * c / nchunk), b = (int)((long)NJ * (c + 1) / nchunk);
-        items[lb * nchunk + c] = make_int3(blk, a, b - a);
+        items[(long)c * nb + lb] = make_int3(blk, a, b - a);
     }
 }
 
@@ -329,8 +333,9 @@ bool mc_screen(const double* P, const double* Q, const McgShape& sh, McgOwn own,
     CBS_LAUNCH(k_scr_convert, grid1(sh.rows * cpr, 256), 256, 0, st, Q, sh, ss, 1, own, sh.rows, Qt, cq);
     int sms = 148;
     cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
-    // about 8 waves of CTAs; every CTA re-loads its 128-row A operand once, so ranges should not be too short either
-    int nchunk = (int)std::min<long>(std::max<long>(1, (8L * sms + own_blocks - 1) / std::max<long>(own_blocks, 1)), std::max(1, ss.NJ / 8));
+    // about 8 waves of CTAs and at least 4 ranges; every CTA re-loads its 128-row A operand once, so ranges should not be
+    // too short either
+    int nchunk = (int)std::min<long>(std::max<long>(4, (8L * sms + own_blocks - 1) / std::max<long>(own_blocks, 1)), std::max(1, ss.NJ / 8));
     int3* items = (int3*)g_dev.get<int>("mcs_items" + sfx, (size_t)3 * own_blocks * nchunk + 3);
     CBS_LAUNCH(k_scr_items, grid1(own_blocks, 128), 128, 0, st, own, nrb, ss.NJ, nchunk, items);
     t_ctx->set_func_attr((const void*)k_scr_mma, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)ScrSmem::total);

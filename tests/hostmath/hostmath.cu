@@ -18,8 +18,11 @@ void hm_nb_quantile_fast(int64_t n, const double* p, const double* size, const d
     for (int64_t i = 0; i < n; ++i) out[i] = nb_quantile_fast(p[i], size[i], size[i] / (size[i] + mu[i]));
 }
 void hm_match_quantiles(int64_t n, const double* x, const double* omu, const double* ophi, const double* nmu, const double* nphi, double* out, int fast) {
+    static double inv[MQ_INV_N];
+    for (int j = 1; j < MQ_INV_N; ++j) inv[j] = 1.0 / (double)j;
     for (int64_t i = 0; i < n; ++i) {
-        if (fast) out[i] = match_one_fast(x[i], omu[i], ophi[i], nmu[i], nphi[i]);
+        if (fast == 2) out[i] = match_one_fast(x[i], omu[i], ophi[i], nmu[i], nphi[i], inv);      // with the small-count path
+        else if (fast) out[i] = match_one_fast(x[i], omu[i], ophi[i], nmu[i], nphi[i]);
         else {
             if (x[i] <= 1) { out[i] = x[i]; continue; }
             const double tp = pnbinom_mu(x[i] - 1, 1.0 / ophi[i], omu[i]);
@@ -27,4 +30,9 @@ void hm_match_quantiles(int64_t n, const double* x, const double* omu, const dou
         }
     }
 }
+}
+#include "../../combat-seq_b200/csrc/fastmath.cuh"
+extern "C" {
+void hm_log_pos(int64_t n, const double* x, double* out) { for (int64_t i = 0; i < n; ++i) out[i] = cbs::log_pos(x[i]); }
+void hm_rcp_pos(int64_t n, const double* x, double* out) { for (int64_t i = 0; i < n; ++i) out[i] = cbs::rcp_pos(x[i]); }
 }

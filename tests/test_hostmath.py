@@ -18,7 +18,8 @@ def hm():
     src = os.path.join(HERE, "hostmath", "hostmath.cu")
     out = os.path.join(HERE, "hostmath", "libhostmath.so")
     hdr = os.path.join(HERE, "..", "combat-seq_b200", "csrc", "nbmath.cuh")
-    if not os.path.exists(out) or os.path.getmtime(out) < max(os.path.getmtime(src), os.path.getmtime(hdr)):
+    hdr2 = os.path.join(HERE, "..", "combat-seq_b200", "csrc", "fastmath.cuh")
+    if not os.path.exists(out) or os.path.getmtime(out) < max(os.path.getmtime(src), os.path.getmtime(hdr), os.path.getmtime(hdr2)):
         nvcc = os.environ.get("NVCC", "/usr/local/cuda/bin/nvcc")
         subprocess.run([nvcc, "-O2", "-std=c++17", "-shared", "-Xcompiler", "-fPIC", "-Wno-deprecated-gpu-targets",
                         "-o", out, src], check=True)
@@ -84,15 +85,32 @@ def test_device_match_quantiles_fast_equals_plain_and_oracle(hm, oracle):
     plain = hm("hm_match_quantiles", x, old_mu, old_phi, new_mu, new_phi, extra=(C.c_int(0),))
     ref = np.array([oracle.match_quantiles(np.array([[xi]]), np.array([[om]]), np.array([op]), np.array([[nm]]), np.array([np_]))[0, 0]
                     for xi, om, op, nm, np_ in zip(x[:3000], old_mu[:3000], old_phi[:3000], new_mu[:3000], new_phi[:3000])])
+    small = hm("hm_match_quantiles", x, old_mu, old_phi, new_mu, new_phi, extra=(C.c_int(2),))
     assert np.array_equal(fast, plain)
+    assert np.array_equal(small, plain)                      # direct pmf summation for small counts: same integers
     assert np.array_equal(fast[:3000], ref)
     # Same distribution on both sides: the identity, thanks to qnbinom's 64 eps fuzz — except where R's own two cdf
     # parametrisations (pnbinom_mu for p, pnbinom(size, prob) inside qnbinom, whose 1 - prob rounds) differ by more
     # than the fuzz (size >> mu).  The device routine must reproduce exactly the oracle's set of exceptions.
     ident = hm("hm_match_quantiles", x, old_mu, old_phi, old_mu, old_phi, extra=(C.c_int(1),))
+    assert np.array_equal(ident, hm("hm_match_quantiles", x, old_mu, old_phi, old_mu, old_phi, extra=(C.c_int(2),)))
     bad = np.flatnonzero(ident != x)
     assert bad.size <= 1e-3 * n
     for i in bad:
         one = oracle.match_quantiles(np.array([[x[i]]]), np.array([[old_mu[i]]]), np.array([old_phi[i]]),
                                      np.array([[old_mu[i]]]), np.array([old_phi[i]]))[0, 0]
         assert one == ident[i]
+
+
+def test_fast_log_for_positive_normal_arguments(hm):
+    # combat-seq_b200/csrc/fastmath.cuh (host compilation of the same series): within 2 ulp of libm over 600 binades
+    rng = np.random.default_rng(5)
+    x = np.concatenate([np.exp(rng.uniform(-200, 200, 200000)), 1 + rng.uniform(-0.3, 0.42, 100000),
+                        1 + rng.normal(0, 1e-6, 50000), 2.0 ** rng.integers(-300, 300, 1000),
+                        np.sqrt(2) * (1 + rng.normal(0, 1e-7, 20000))])
+    got, ref = hm("hm_log_pos", x), np.log(x)
+    ulp = np.spacing(np.abs(ref))
+    err = np.abs(got - ref) / np.maximum(ulp, 5e-324)
+    m = ref != 0
+    assert err[m].max() <= 2.0, err[m].max()
+    assert np.all(got[~m] == 0)
