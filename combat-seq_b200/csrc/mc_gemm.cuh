@@ -130,32 +130,46 @@ k_mcg_prep_src(const double* __restrict__ mu_hat, long G, const int* __restrict_
     for (int k = sh.KT; k < sh.KTP; ++k) Q[mcg_index(sh.rows, j, k)] = 0.0;
 }
 
-// ---- target side, step 1: F_i at the Chebyshev nodes.  grid (ceil(G/128), Kc); Fnode is [m*G + i] ----------
+// ---- target side, step 0: the batch's counts of this rank's target rows in abundance order, xs[t * own_rows + local row] ----
+// (one gathered read per count; the kernels below then read coalesced)
+__global__ void __launch_bounds__(256)
+k_mcg_gather_counts(const int32_t* __restrict__ cnt, long G, const int* __restrict__ cols, const int* __restrict__ perm,
+                    McgShape sh, McgOwn own, long own_rows, int32_t* __restrict__ xs) {       // grid (own_rows/256, n)
+    const long lr = (long)blockIdx.x * blockDim.x + threadIdx.x;
+    const int t = blockIdx.y;
+    if (lr >= own_rows) return;
+    const long i = own.row(lr);
+    xs[(long)t * own_rows + lr] = i < G ? cnt[perm[i] + (long)cols[t] * G] : 0;
+}
+
+// ---- target side, step 1: F_i at the Chebyshev nodes.  grid (own_rows/128, Kc); Fnode is [m*G + i] ----------
 // The summand depends on the count and the node only, so it is tabulated once per batch for counts below MCG_LGTAB
 // (k_mcg_node_table: Kc x MCG_LGTAB evaluations instead of Kc x G x n_b; the table holds the bits the direct call
-// returns) and the sweep over the samples becomes a lookup.  Larger counts take the direct call.
+// returns; one 64 KB table per node stays in L1 for the block that uses it) and the sweep over the samples becomes a
+// lookup.  Larger counts take the direct call.
 constexpr int MCG_LGTAB = 8192;
+__device__ __forceinline__ double mcg_node_r(const McgShape& sh, int m) {
+    const double tn = cospi((m + 0.5) / sh.Kc);
+    return exp(0.5 * (sh.ulo + sh.uhi) + 0.5 * (sh.uhi - sh.ulo) * tn) - (double)MCG_SHIFT;
+}
 __global__ void __launch_bounds__(256)
 k_mcg_node_table(McgShape sh, double* __restrict__ tab) {          // grid (MCG_LGTAB / 256, Kc)
     const int x = blockIdx.x * blockDim.x + threadIdx.x, m = blockIdx.y;
-    const double tn = cospi((m + 0.5) / sh.Kc);
-    const double r = exp(0.5 * (sh.ulo + sh.uhi) + 0.5 * (sh.uhi - sh.ulo) * tn) - (double)MCG_SHIFT;
-    tab[(long)m * MCG_LGTAB + x] = x >= MCG_SHIFT ? lgamma_diff((double)x, r) : 0.0;
+    tab[(long)m * MCG_LGTAB + x] = x >= MCG_SHIFT ? lgamma_diff((double)x, mcg_node_r(sh, m)) : 0.0;
 }
 
 __global__ void __launch_bounds__(128)
-k_mcg_prep_nodes(const int32_t* __restrict__ cnt, long G, const int* __restrict__ cols, const int* __restrict__ perm,
-                 McgShape sh, McgOwn own, const double* __restrict__ tab, double* __restrict__ Fnode) {
-    const long i = own.row((long)blockIdx.x * blockDim.x + threadIdx.x);     // sorted row of one of this rank's targets
+k_mcg_prep_nodes(const int32_t* __restrict__ xs, long G, McgShape sh, McgOwn own, long own_rows,
+                 const double* __restrict__ tab, double* __restrict__ Fnode) {
+    const long lr = (long)blockIdx.x * blockDim.x + threadIdx.x;
+    const long i = own.row(lr);                                    // sorted row of one of this rank's targets
     const int m = blockIdx.y;
-    if (i >= G) return;
-    const long gi = perm[i];
-    const double tn = cospi((m + 0.5) / sh.Kc);
-    const double r = exp(0.5 * (sh.ulo + sh.uhi) + 0.5 * (sh.uhi - sh.ulo) * tn) - (double)MCG_SHIFT;
+    if (lr >= own_rows || i >= G) return;
+    const double r = mcg_node_r(sh, m);
     const double* __restrict__ t_m = tab + (long)m * MCG_LGTAB;
     double f = 0;
     for (int t = 0; t < sh.n; ++t) {
-        const int x = cnt[gi + (long)cols[t] * G];
+        const int x = xs[(long)t * own_rows + lr];
         if (x >= MCG_LGTAB) f += lgamma_diff((double)x, r);
         else if (x >= MCG_SHIFT) f += __ldg(t_m + x);
     }
@@ -166,22 +180,23 @@ k_mcg_prep_nodes(const int32_t* __restrict__ cnt, long G, const int* __restrict_
 // dct is the Kc x Kc table dct[k*Kc + m] = (k ? 2 : 1)/Kc * cos(pi k (m + 1/2)/Kc).  tail_bits: atomicMax of the
 // bit pattern of |C_{Kc-1}| + |C_{Kc-2}| (non-negative doubles order like their bit patterns).
 __global__ void __launch_bounds__(128)
-k_mcg_prep_tgt(const int32_t* __restrict__ cnt, long G, const int* __restrict__ cols, const int* __restrict__ perm,
-               McgShape sh, McgOwn own, const double* __restrict__ Fnode, const double* __restrict__ dct,
+k_mcg_prep_tgt(const int32_t* __restrict__ xs, long G, McgShape sh, McgOwn own, long own_rows,
+               const double* __restrict__ Fnode, const double* __restrict__ dct,
                double* __restrict__ P, unsigned long long* __restrict__ tail_bits) {
-    const long i = own.row((long)blockIdx.x * blockDim.x + threadIdx.x);
+    const long lr = (long)blockIdx.x * blockDim.x + threadIdx.x;
+    if (lr >= own_rows) return;
+    const long i = own.row(lr);
     if (i >= sh.rows) return;
     const int n = sh.n, Kc = sh.Kc;
     if (i >= G) {
         for (int k = 0; k < sh.KTP; ++k) P[mcg_index(sh.rows, i, k)] = 0.0;
         return;
     }
-    const long gi = perm[i];
     int hot[MCG_SHIFT];
 #pragma unroll
     for (int v = 0; v < MCG_SHIFT; ++v) hot[v] = 0;
     for (int t = 0; t < n; ++t) {
-        const int x = cnt[gi + (long)cols[t] * G];
+        const int x = xs[(long)t * own_rows + lr];
         P[mcg_index(sh.rows, i, t)] = (double)x;
 #pragma unroll
         for (int v = 0; v < MCG_SHIFT; ++v) hot[v] += (x == v);
@@ -558,8 +573,8 @@ __global__ void k_mcg_list_all(int NJ, int* __restrict__ srclist, int* __restric
     if (threadIdx.x == 0) count[t] = NJ;
 }
 
-// With screening (tu_screen.cu): hi[J*rows + i] is an upper bound of max_{j in source tile J} log LH_ij and lo[J*rows + i] a
-// lower bound of the same maximum over j != i.  Source tile J is kept for target tile t when some row of t can have a
+// With screening (tu_screen.cu): hi[(2J+h)*rows + i] is an upper bound of max_{j in half h of source tile J} log LH_ij and
+// lo[..] a lower bound of the same maximum over j != i.  Source tile J is kept for target tile t when some row of t can have a
 // pair in J within MCG_PRUNE of the row's best pair:  hi[J][i] >= max_J' lo[J'][i] - MCG_PRUNE.  Whatever is dropped is
 // below e^-40 of the row's largest weight, the bound the fold in k_mc_gemm applies anyway.  grid (ntiles64), block 256,
 // NJ bytes of dynamic shared memory.  The 4 thread groups of a block split the source tiles.
@@ -572,14 +587,15 @@ k_mcg_list_screened(const float* __restrict__ hi, const float* __restrict__ lo, 
     const long i = (long)t * MCG_TI + r;
     float m = -INFINITY;
 #pragma unroll 4
-    for (int J = q; J < NJ; J += 4) m = fmaxf(m, lo[(long)J * rows + i]);
+    for (int J = q; J < NJ; J += 4) m = fmaxf(m, fmaxf(lo[(long)(2 * J) * rows + i], lo[(long)(2 * J + 1) * rows + i]));
     mx[q][r] = m;
     for (int J = threadIdx.x; J < NJ; J += 256) flag_s[J] = 0;
     __syncthreads();
     m = fmaxf(fmaxf(mx[0][r], mx[1][r]), fmaxf(mx[2][r], mx[3][r]));
     const float thr = m - prune;                               // -inf when the row has no finite pair: everything is kept
 #pragma unroll 4
-    for (int J = q; J < NJ; J += 4) if (!(hi[(long)J * rows + i] < thr)) flag_s[J] = 1;      // (NaN counts as kept)
+    for (int J = q; J < NJ; J += 4)
+        if (!(fmaxf(hi[(long)(2 * J) * rows + i], hi[(long)(2 * J + 1) * rows + i]) < thr)) flag_s[J] = 1;
     __syncthreads();
     if (threadIdx.x < 32) {
         const int lane = threadIdx.x;

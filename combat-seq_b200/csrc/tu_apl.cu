@@ -167,7 +167,7 @@ k_apl_lanes(const int32_t* __restrict__ cnt, long G, long g0, long g1, const dou
                         info += mu * inv;
                     }
                     dl = lane_sum<APLL_LANES>(dl, gm); info = lane_sum<APLL_LANES>(info, gm);
-                    const double step = dl / info;
+                    const double step = dl / info;                // (info may be 0 or tiny for a degenerate cell: the full division)
                     cur += step;
                     if (fabs(step) < 1e-10) break;
                 }

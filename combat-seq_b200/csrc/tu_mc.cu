@@ -116,10 +116,12 @@ static McPlan plan_mc_gemm(const int32_t* cnt, long G, int n, const int* d_cols,
     CBS_LAUNCH(k_mcg_prep_src, grid1(sh.rows, 128), 128, 0, st, d_mu_hat, G, d_cols, d_phi, pl.perm, sh, pl.Q);
     CBS_LAUNCH(k_mcg_pack_gp, grid1(sh.rows, 256), 256, 0, st, d_gamma, d_phi, pl.perm, G, sh.rows, pl.gp);
     if (own_rows > 0) {                     // P is only needed for this rank's target blocks (Q for all sources)
+        int32_t* xs = g_dev.get<int32_t>(sl("mcg_xs", slot), (size_t)own_rows * n);
+        CBS_LAUNCH(k_mcg_gather_counts, dim3((unsigned)((own_rows + 255) / 256), (unsigned)n), 256, 0, st, cnt, G, d_cols, pl.perm, sh, own, own_rows, xs);
         double* d_lgtab = g_dev.get<double>(sl("mcg_lgtab", slot), (size_t)sh.Kc * MCG_LGTAB);
         CBS_LAUNCH(k_mcg_node_table, dim3(MCG_LGTAB / 256, (unsigned)sh.Kc), 256, 0, st, sh, d_lgtab);
-        CBS_LAUNCH(k_mcg_prep_nodes, dim3((unsigned)(own_rows / 128), (unsigned)sh.Kc), 128, 0, st, cnt, G, d_cols, pl.perm, sh, own, d_lgtab, Fn);
-        CBS_LAUNCH(k_mcg_prep_tgt, grid1(own_rows, 128), 128, 0, st, cnt, G, d_cols, pl.perm, sh, own, Fn, d_dct, pl.P, d_tail);
+        CBS_LAUNCH(k_mcg_prep_nodes, dim3((unsigned)(own_rows / 128), (unsigned)sh.Kc), 128, 0, st, xs, G, sh, own, own_rows, d_lgtab, Fn);
+        CBS_LAUNCH(k_mcg_prep_tgt, grid1(own_rows, 128), 128, 0, st, xs, G, sh, own, own_rows, Fn, d_dct, pl.P, d_tail);
     }
     // the series' tail is judged over ALL targets, so that every rank takes the decision a single GPU would
     if (comm && comm->world > 1) CBS_NCCL(nccl_api()->AllReduce(d_tail, d_tail, 1, NCCL_UINT64, NCCL_MAX, comm->nccl, st));
@@ -129,8 +131,8 @@ static McPlan plan_mc_gemm(const int32_t* cnt, long G, int n, const int* d_cols,
     pl.count = g_dev.get<int>(sl("mcg_count", slot), (size_t)ntiles64);
     bool screened = false;
     if (g_tune.mc_band && own_rows > 0) {
-        float* hi = g_dev.get<float>(sl("mcs_hi", slot), (size_t)NJ * sh.rows);
-        float* lo = g_dev.get<float>(sl("mcs_lo", slot), (size_t)NJ * sh.rows);
+        float* hi = g_dev.get<float>(sl("mcs_hi", slot), (size_t)2 * NJ * sh.rows);
+        float* lo = g_dev.get<float>(sl("mcs_lo", slot), (size_t)2 * NJ * sh.rows);
         screened = mc_screen(pl.P, pl.Q, sh, own, slot, hi, lo, st);
         if (screened) {
             t_ctx->set_func_attr((const void*)k_mcg_list_screened, cudaFuncAttributeMaxDynamicSharedMemorySize, 64 * 1024);

@@ -12,13 +12,22 @@
 // and reduces every 128 x 128 tile to per-row maxima of the upper bound S + SCR_EPS*D and of the lower bound S - SCR_EPS*D.
 // k_mcg_list_screened (mc_gemm.cuh) keeps a source tile for a target tile iff an upper bound reaches a row's best lower
 // bound - 40; the FP64 contraction then visits only those tiles.  tcgen05 has no FP64 kind, so the weights themselves stay on
-// the DMMA path; what runs here is 2 * 576 * G^2 bf16 flop per batch, a few per cent of the FP64 work it removes.
+// the DMMA path; what runs here is 40 tcgen05.mma (128 x 128 x 16) per tile pair, a few per cent of the FP64 work it removes.
 //
-// Kernel: one CTA = one 128-row target block x a range of 128-row source tiles.  Warp 0 streams the operand tiles with
-// bulk async copies (the global layout is the shared-memory image: 128 rows x 64 bf16, 128-byte swizzle, one 16 KB block
-// per copy); one lane of warp 1 issues tcgen05.mma (M = N = 128, K = 16 per instruction, A and B from shared memory
-// descriptors, accumulators S and D in TMEM, double buffered: 2 x 256 of the 512 columns); warps 2-5 read the
-// accumulators back with tcgen05.ld and fold them into the row maxima while the next tile is being multiplied.
+// Operand layout.  A row of P or Q is a sequence of 64-column k-tiles, each 4 sub-blocks of 16 columns (one MMA K step):
+//   sample part (x_is / A_js): chunk c of 16 samples lives in k-tile c / 2 as sub-blocks (hi, lo) [+2 for odd c];
+//   series part (Chebyshev orders >= 1 and the one-hot columns): chunk c lives in k-tile NXT + c as (hi, lo, |.|, 0).
+// The cross terms of the split are MMAs between different sub-blocks of the SAME pair of k-tiles (A descriptor at hi, B
+// descriptor at lo, ...), so no operand is stored or fetched twice; the sample part of D needs no operand of its own:
+// counts are >= 0 and A_js <= 0, so |x| |A| = x (-A): the hi x hi MMA again with the negate-B bit of the instruction descriptor.
+//
+// Kernel: one CTA = one 128-row target block x a range of 128-row source tiles.  The target block's k-tiles stay resident in
+// shared memory; warp 0 streams the source tiles' k-tiles through a ring with bulk async copies (the global layout is the
+// shared-memory image: 128 rows x 64 bf16, 128-byte swizzle, one 16 KB block per copy; the stream is latency-bound, so the
+// ring takes all the shared memory the resident operand leaves); one lane of warp 1 issues tcgen05.mma (M = N = 128, K = 16
+// per instruction, A and B from shared memory descriptors, accumulators S and D in TMEM, double buffered: 2 x 256 of the
+// 512 columns); warps 2-9 read the accumulators back with tcgen05.ld and fold them into the row maxima while the next tile
+// is being multiplied.
 #include "screen.hpp"
 #include <cuda_bf16.h>
 
@@ -28,57 +37,62 @@ constexpr int SCR_BM = 128;                 // target rows per CTA (UMMA M)
 constexpr int SCR_BN = 128;                 // source rows per tile (UMMA N) = MCG_TILE
 constexpr int SCR_KTILE = 64;               // bf16 per operand row and k-tile: 128 bytes, the swizzle span
 constexpr int SCR_TILE_BYTES = SCR_BM * SCR_KTILE * 2;      // 16 KB
-constexpr int SCR_MAX_KT = 9;               // k-tiles of the resident A operand (4 segments of <= 144 columns)
-constexpr int SCR_STAGES = 4;               // ring of B k-tiles
-constexpr int SCR_THREADS = 192;            // warp 0 producer, warp 1 MMA issuer, warps 2-5 epilogue
+constexpr int SCR_MAX_KT = 8;               // most k-tiles of an operand row the kernel supports (resident A: 128 KB)
+constexpr int SCR_SMEM_TILES = 13;          // 16 KB tiles that fit shared memory next to the barriers: resident A + ring of B
+constexpr int SCR_EPI_WARPS = 8;            // two warps per TMEM lane quarter, each folding half of the tile's columns
+constexpr int SCR_THREADS = 64 + 32 * SCR_EPI_WARPS;     // warp 0 producer, warp 1 MMA issuer, warps 2-9 epilogue
 constexpr float SCR_EPS = 3.1e-5f;          // error bound of S relative to D (see above), including 1 % for D's own rounding
 constexpr float SCR_EPS_C = 2.5e-7f;        // fp32 rounding of the per-source constant c_j added in the epilogue
 static_assert(SCR_BN == MCG_TILE, "screening tiles are the contraction's source tiles");
 
 struct ScrShape {
-    int K1;          // columns per segment: KS = KT - 2 screened columns (no order-0 Chebyshev term, no c_j), padded to 16
-    int nsteps_s;    // UMMA steps (K = 16) that accumulate into S: 3 * K1 / 16
-    int nsteps;      // all steps: 4 * K1 / 16
-    int nk;          // k-tiles: ceil(4 * K1 / 64)
+    int n, KS;       // samples; KS - n series columns (Chebyshev orders 1.., one-hot; no order-0 term, no c_j)
+    int nxc, nxt;    // 16-sample chunks and the k-tiles holding them (2 chunks per k-tile)
+    int ncc;         // 16-column chunks of the series part (1 per k-tile)
+    int nk;          // k-tiles per operand row = nxt + ncc
+    int stages;      // ring of B k-tiles = SCR_SMEM_TILES - nk
     long rows;       // rows of P / Q (multiple of 128)
     int NJ;          // source tiles
 };
 
 // ---- operand conversion: FP64 P / Q (mc_gemm.cuh layout) -> bf16 tiles in the shared-memory image ------------------
-// Segment s of an operand row holds K1 columns: s = 0: hi, 1: hi (P) / lo (Q), 2: lo (P) / hi (Q), 3: |hi|.
-// Element (row r, column c) lives in block [c / 64][r / 128] (16 KB each) at byte (r % 128) * 128 +
-// (((c % 64) / 8) ^ (r % 8)) * 16 + (c % 8) * 2: the 128-byte swizzle the UMMA descriptors below declare.
-// One thread writes one 16-byte chunk (8 columns).  is_q selects the source operand's segment rule; rows_used: P is only
-// built for the owned blocks, the other blocks are never read.
+// Element (row r, k-tile kt, column c of the k-tile) lives in block [kt][r / 128] (16 KB each) at byte (r % 128) * 128 +
+// ((c / 8) ^ (r % 8)) * 16 + (c % 8) * 2: the 128-byte swizzle the UMMA descriptors below declare.  One thread writes one
+// 16-byte chunk (8 columns = half a sub-block).  P is only built for the owned blocks, the other blocks are never read.
 __global__ void __launch_bounds__(256)
-k_scr_convert(const double* __restrict__ X, McgShape sh, ScrShape ss, int is_q, McgOwn own, long n_chunks_rows,
+k_scr_convert(const double* __restrict__ X, McgShape sh, ScrShape ss, int is_q, McgOwn own, long n_rows,
               __nv_bfloat16* __restrict__ out, float* __restrict__ cq) {
     const long t = (long)blockIdx.x * blockDim.x + threadIdx.x;
     const int chunks_per_row = ss.nk * 8;
     const long lr = t / chunks_per_row;
     const int ch = (int)(t - lr * chunks_per_row);
-    if (lr >= n_chunks_rows) return;
+    if (lr >= n_rows) return;
     const long r = is_q ? lr : own.row(lr);
-    const int KS = sh.KT - 2;
+    const int kt = ch >> 3, c8 = ch & 7, sb = c8 >> 1, half = c8 & 1;
+    int kind, col0;                                               // kind 0 hi, 1 lo, 2 |hi|, 3 zero; col0: first MC column, < 0 = none
+    if (kt < ss.nxt) {
+        const int c = 2 * kt + (sb >> 1);
+        kind = sb & 1;
+        col0 = c < ss.nxc ? c * 16 + half * 8 : -1;
+    } else {
+        kind = sb;
+        col0 = ss.n + 1 + (kt - ss.nxt) * 16 + half * 8;          // series columns start after the order-0 term at MC column n
+    }
+    const int lim = kt < ss.nxt ? ss.n : sh.KT - 1;               // exclusive end of the part in MC columns (c_j at KT - 1 is left out)
     __align__(16) __nv_bfloat16 v[8];
 #pragma unroll
     for (int e = 0; e < 8; ++e) {
-        const int c = ch * 8 + e;
-        const int seg = c / ss.K1, k = c - seg * ss.K1;
         float f = 0.f;
-        if (seg < 4 && k < KS) {
-            const int km = k < sh.n ? k : k + 1;                           // skip the order-0 Chebyshev column
-            const double x = X[mcg_index(sh.rows, r, km)];
-            const __nv_bfloat16 h = __double2bfloat16(x);
-            const bool want_lo = is_q ? (seg == 1) : (seg == 2);
-            if (seg == 3) f = fabsf(__bfloat162float(__double2bfloat16(fabs(x))));
-            else if (want_lo) f = (float)(x - (double)__bfloat162float(h));
-            else f = __bfloat162float(h);
+        const int k = col0 + e;
+        if (col0 >= 0 && kind < 3 && k < lim) {
+            const double x = X[mcg_index(sh.rows, r, k)];
+            const float h = __bfloat162float(__double2bfloat16(x));
+            f = kind == 0 ? h : kind == 1 ? (float)(x - (double)h) : fabsf(h);
         }
         v[e] = __float2bfloat16_rn(f);
     }
-    const long blk = (long)(ch / 8) * (sh.rows / SCR_BM) + r / SCR_BM;
-    const int rr = (int)(r % SCR_BM), c8 = ch % 8;
+    const long blk = (long)kt * (sh.rows / SCR_BM) + r / SCR_BM;
+    const int rr = (int)(r % SCR_BM);
     char* dst = reinterpret_cast<char*>(out) + blk * SCR_TILE_BYTES + rr * 128 + ((c8 ^ (rr & 7)) << 4);
     *reinterpret_cast<uint4*>(dst) = *reinterpret_cast<const uint4*>(v);
     if (is_q && ch == 0) cq[r] = (float)X[mcg_index(sh.rows, r, sh.KT - 1)];      // c_j, added in fp32 in the epilogue
@@ -149,30 +163,34 @@ __host__ __device__ constexpr uint32_t scr_idesc(bool neg_b) {
 }
 
 struct ScrSmem {
-    // [A k-tiles (resident)] [B ring] [c_j double buffer] [barriers] [tmem base]; the tiles need 1024-byte alignment
-    static constexpr size_t a_bytes = (size_t)SCR_MAX_KT * SCR_TILE_BYTES;
-    static constexpr size_t b_bytes = (size_t)SCR_STAGES * SCR_TILE_BYTES;
-    static constexpr size_t cq_off = a_bytes + b_bytes;
-    static constexpr size_t bar_off = cq_off + 2 * SCR_BN * sizeof(float);
-    static constexpr size_t total = bar_off + 16 * sizeof(uint64_t) + 16 + 1024 /*alignment slack*/;
+    // [SCR_SMEM_TILES x 16 KB: the resident A k-tiles, then the B ring] [c_j double buffer] [barriers] [tmem base];
+    // the tiles need 1024-byte alignment
+    static constexpr size_t tile_bytes = (size_t)SCR_SMEM_TILES * SCR_TILE_BYTES;
+    static constexpr size_t cq_off = tile_bytes;
+    static constexpr size_t bar_off = cq_off + 2 * SCR_BN * sizeof(float2);
+    static constexpr int max_stages = SCR_SMEM_TILES;
+    static constexpr size_t total = bar_off + (3 + 2 * max_stages + 4) * sizeof(uint64_t) + 16 + 1024 /*alignment slack*/;
 };
+static_assert(ScrSmem::total <= 227 * 1024, "screening kernel: shared memory");
 
-// items[w] = (target block, first source tile, number of source tiles).  hi / lo are [NJ][rows].
+// items[w] = (target block, first source tile, number of source tiles).  hi / lo are [2 NJ][rows]: one entry per half
+// (64 columns) of a source tile.
 __global__ void __launch_bounds__(SCR_THREADS, 1)
 k_scr_mma(const __nv_bfloat16* __restrict__ Pt, const __nv_bfloat16* __restrict__ Qt, const float* __restrict__ cq,
           ScrShape ss, const int3* __restrict__ items, float* __restrict__ hi, float* __restrict__ lo) {
     extern __shared__ unsigned char scr_raw[];
     unsigned char* smem = reinterpret_cast<unsigned char*>((reinterpret_cast<uintptr_t>(scr_raw) + 1023) & ~(uintptr_t)1023);
+    const int NST = ss.stages;
     unsigned char* a_s = smem;
-    unsigned char* b_s = smem + ScrSmem::a_bytes;
-    float* cq_s = reinterpret_cast<float*>(smem + ScrSmem::cq_off);                  // [2][128]
+    unsigned char* b_s = smem + (size_t)ss.nk * SCR_TILE_BYTES;
+    float2* cq_s = reinterpret_cast<float2*>(smem + ScrSmem::cq_off);                // [2][128] (c_j, SCR_EPS_C |c_j|)
     uint64_t* bars = reinterpret_cast<uint64_t*>(smem + ScrSmem::bar_off);
     uint64_t* a_full = bars;                    // 1
-    uint64_t* b_full = bars + 1;                // SCR_STAGES
-    uint64_t* b_empty = bars + 1 + SCR_STAGES;  // SCR_STAGES
-    uint64_t* acc_full = bars + 1 + 2 * SCR_STAGES;     // 2
-    uint64_t* acc_empty = bars + 3 + 2 * SCR_STAGES;    // 2
-    uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 16);
+    uint64_t* acc_full = bars + 1;              // 2
+    uint64_t* acc_empty = bars + 3;             // 2
+    uint64_t* b_full = bars + 5;                // NST
+    uint64_t* b_empty = bars + 5 + ScrSmem::max_stages;     // NST
+    uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 5 + 2 * ScrSmem::max_stages);
 
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     const int3 item = items[blockIdx.x];
@@ -182,8 +200,8 @@ k_scr_mma(const __nv_bfloat16* __restrict__ Pt, const __nv_bfloat16* __restrict_
 
     if (threadIdx.x == 0) {
         sbar_init(a_full, 1);
-        for (int s = 0; s < SCR_STAGES; ++s) { sbar_init(&b_full[s], 1); sbar_init(&b_empty[s], 1); }
-        for (int s = 0; s < 2; ++s) { sbar_init(&acc_full[s], 1); sbar_init(&acc_empty[s], 4); }
+        for (int s = 0; s < NST; ++s) { sbar_init(&b_full[s], 1); sbar_init(&b_empty[s], 1); }
+        for (int s = 0; s < 2; ++s) { sbar_init(&acc_full[s], 1); sbar_init(&acc_empty[s], SCR_EPI_WARPS); }
         asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
     }
     if (warp == 2) {                            // TMEM: all 512 columns (two accumulator stages of S and D)
@@ -209,7 +227,7 @@ k_scr_mma(const __nv_bfloat16* __restrict__ Pt, const __nv_bfloat16* __restrict_
                     sbar_expect_tx(&b_full[st], SCR_TILE_BYTES);
                     sbulk_g2s(b_s + (size_t)st * SCR_TILE_BYTES,
                               reinterpret_cast<const char*>(Qt) + ((size_t)kt * nrb + (j0 + jj)) * SCR_TILE_BYTES, SCR_TILE_BYTES, &b_full[st]);
-                    if (++st == SCR_STAGES) { st = 0; ph ^= 1u; }
+                    if (++st == NST) { st = 0; ph ^= 1u; }
                 }
             }
         }
@@ -225,63 +243,88 @@ k_scr_mma(const __nv_bfloat16* __restrict__ Pt, const __nv_bfloat16* __restrict_
                 sbar_wait(&acc_empty[as], ((uint32_t)(jj >> 1) & 1u) ^ 1u);
                 tc_fence_after();
                 const uint32_t d_s = tmem + (uint32_t)as * 256u, d_d = d_s + 128u;
+                bool s_started = false, d_started = false;
                 for (int kt = 0; kt < ss.nk; ++kt) {
                     sbar_wait(&b_full[st], ph);
                     tc_fence_after();
+                    const uint32_t at = a_addr + (uint32_t)kt * SCR_TILE_BYTES, bt = b_addr + (uint32_t)st * SCR_TILE_BYTES;
+                    auto mma = [&](int sa, int sb, bool to_d, bool neg) {          // sub-blocks of 16 columns: 32 bytes apart
+                        bool& started = to_d ? d_started : s_started;
+                        tc_mma_bf16(to_d ? d_d : d_s, scr_desc(at + (uint32_t)sa * 32u), scr_desc(bt + (uint32_t)sb * 32u),
+                                    scr_idesc(neg), started ? 1u : 0u);
+                        started = true;
+                    };
+                    if (kt < ss.nxt) {
 #pragma unroll
-                    for (int q = 0; q < SCR_KTILE / 16; ++q) {
-                        const int step = kt * (SCR_KTILE / 16) + q;
-                        if (step < ss.nsteps) {
-                            const uint64_t da = scr_desc(a_addr + (uint32_t)kt * SCR_TILE_BYTES + (uint32_t)q * 32u);
-                            const uint64_t db = scr_desc(b_addr + (uint32_t)st * SCR_TILE_BYTES + (uint32_t)q * 32u);
-                            const bool to_d = step >= ss.nsteps_s;
-                            const uint32_t acc = (step != 0 && step != ss.nsteps_s) ? 1u : 0u;
-                            tc_mma_bf16(to_d ? d_d : d_s, da, db, scr_idesc(false), acc);
+                        for (int h = 0; h < 2; ++h) {
+                            if (2 * kt + h < ss.nxc) {
+                                mma(2 * h, 2 * h, false, false);          // x_hi A_hi
+                                mma(2 * h, 2 * h + 1, false, false);      // x_hi A_lo
+                                mma(2 * h + 1, 2 * h, false, false);      // x_lo A_hi
+                                mma(2 * h, 2 * h, true, true);            // |x| |A| = x_hi (-A_hi)
+                            }
                         }
+                    } else {
+                        mma(0, 0, false, false);                          // C_hi T_hi
+                        mma(0, 1, false, false);                          // C_hi T_lo
+                        mma(1, 0, false, false);                          // C_lo T_hi
+                        mma(2, 2, true, false);                           // |C| |T|
                     }
                     tc_commit(&b_empty[st]);                      // the stage is free once these MMAs have read it
-                    if (++st == SCR_STAGES) { st = 0; ph ^= 1u; }
+                    if (++st == NST) { st = 0; ph ^= 1u; }
                 }
                 tc_commit(&acc_full[as]);                         // accumulators of tile jj complete
             }
         }
     } else {
-        // ===== epilogue: warps 2..5; warp w may touch TMEM lanes 32 (w % 4) .. +31 =====
-        const int q = warp & 3;
+        // ===== epilogue: warps 2..9; warp w may touch TMEM lanes 32 (w % 4) .. +31; the two warps of a lane quarter split the
+        // tile's columns.  The fold is latency-bound (max chains), so each warp keeps four independent running maxima per
+        // bound and the per-source constants come in as one 16-byte shared-memory load per two columns.
+        const int q = warp & 3, half = (warp - 2) >> 2;
         const int row = q * 32 + lane;                            // row of the target block = TMEM lane
         const long grow = iblk * SCR_BM + row;
-        const int et = threadIdx.x - 64;                          // 0..127
+        const int et = threadIdx.x - 64;                          // 0 .. 32 SCR_EPI_WARPS - 1
+        constexpr int HC = SCR_BN / 2;                            // columns per warp
         for (int jj = 0; jj < nj; ++jj) {
             const int as = jj & 1;
             const int J = j0 + jj;
-            cq_s[as * SCR_BN + et] = cq[(long)J * SCR_BN + et];
-            asm volatile("bar.sync 1, 128;" ::: "memory");        // the 4 epilogue warps
+            if (et < SCR_BN) { const float c = cq[(long)J * SCR_BN + et]; cq_s[as * SCR_BN + et] = make_float2(c, SCR_EPS_C * fabsf(c)); }
+            asm volatile("bar.sync 1, %0;" ::"n"(32 * SCR_EPI_WARPS) : "memory");        // the epilogue warps
             sbar_wait(&acc_full[as], (uint32_t)(jj >> 1) & 1u);
             tc_fence_after();
-            const uint32_t t_s = tmem + ((uint32_t)(q * 32) << 16) + (uint32_t)as * 256u, t_d = t_s + 128u;
+            const uint32_t t_s = tmem + ((uint32_t)(q * 32) << 16) + (uint32_t)as * 256u + (uint32_t)(half * HC), t_d = t_s + 128u;
             const bool diag = (long)J == iblk;
-            float mhi = -INFINITY, mlo = -INFINITY;
+            float mh[4] = {-INFINITY, -INFINITY, -INFINITY, -INFINITY}, ml[4] = {-INFINITY, -INFINITY, -INFINITY, -INFINITY};
 #pragma unroll 1
-            for (int c0 = 0; c0 < SCR_BN; c0 += 32) {
+            for (int c0 = 0; c0 < HC; c0 += 32) {
                 float s[32], d[32];
                 tc_ld32(t_s + (uint32_t)c0, s);
                 tc_ld32(t_d + (uint32_t)c0, d);
                 tc_ld_wait();
+                const float4* cp = reinterpret_cast<const float4*>(cq_s + as * SCR_BN + half * HC + c0);
 #pragma unroll
-                for (int c = 0; c < 32; ++c) {
-                    const float cj = cq_s[as * SCR_BN + c0 + c];
-                    const float v = s[c] + cj;
-                    const float e = fmaf(SCR_EPS, d[c], SCR_EPS_C * fabsf(cj));
-                    mhi = fmaxf(mhi, v + e);
-                    const float l = v - e;
-                    mlo = fmaxf(mlo, (diag && (c0 + c) == row) ? -INFINITY : l);
+                for (int c = 0; c < 32; c += 2) {
+                    const float4 ce = cp[c >> 1];                 // (c_j, e_j) of columns c, c + 1
+                    const float v0 = s[c] + ce.x, v1 = s[c + 1] + ce.z;
+                    const float e0 = fmaf(SCR_EPS, d[c], ce.y), e1 = fmaf(SCR_EPS, d[c + 1], ce.w);
+                    mh[c & 2] = fmaxf(mh[c & 2], v0 + e0);
+                    mh[(c & 2) + 1] = fmaxf(mh[(c & 2) + 1], v1 + e1);
+                    float l0 = v0 - e0, l1 = v1 - e1;
+                    if (diag) {                                   // j == i is not a source (mu[-i,], helper_seq.R:11-14)
+                        if (half * HC + c0 + c == row) l0 = -INFINITY;
+                        if (half * HC + c0 + c + 1 == row) l1 = -INFINITY;
+                    }
+                    ml[c & 2] = fmaxf(ml[c & 2], l0);
+                    ml[(c & 2) + 1] = fmaxf(ml[(c & 2) + 1], l1);
                 }
             }
             tc_fence_before();
             __syncwarp();
             if (lane == 0) sbar_arrive(&acc_empty[as]);
-            __stcs(&hi[(long)J * ss.rows + grow], mhi);            // streamed: read once by k_mcg_list_screened, keep L2 for the operands
-            __stcs(&lo[(long)J * ss.rows + grow], mlo);
+            const float mhi = fmaxf(fmaxf(mh[0], mh[1]), fmaxf(mh[2], mh[3])), mlo = fmaxf(fmaxf(ml[0], ml[1]), fmaxf(ml[2], ml[3]));
+            // the two column halves of a tile are combined by k_mcg_list_screened: hi / lo are [2 NJ][rows]
+            __stcs(&hi[((long)J * 2 + half) * ss.rows + grow], mhi);      // streamed: read once, keep L2 for the operands
+            __stcs(&lo[((long)J * 2 + half) * ss.rows + grow], mlo);
         }
     }
     tc_fence_before();
@@ -310,14 +353,16 @@ __global__ void k_scr_items(McgOwn own, long nrb, int NJ, int nchunk, int3* __re
 bool mc_screen(const double* P, const double* Q, const McgShape& sh, McgOwn own, int slot, float* hi, float* lo,
                cudaStream_t st) {
     ScrShape ss;
-    const int KS = sh.KT - 2;
-    ss.K1 = (KS + 15) / 16 * 16;
-    ss.nsteps_s = 3 * ss.K1 / 16;
-    ss.nsteps = 4 * ss.K1 / 16;
-    ss.nk = (4 * ss.K1 + SCR_KTILE - 1) / SCR_KTILE;
+    ss.n = sh.n;
+    ss.KS = sh.KT - 2;
+    ss.nxc = (sh.n + 15) / 16;
+    ss.nxt = (ss.nxc + 1) / 2;
+    ss.ncc = (ss.KS - sh.n + 15) / 16;
+    ss.nk = ss.nxt + ss.ncc;
     ss.rows = sh.rows;
     ss.NJ = (int)(sh.rows / SCR_BN);
     if (ss.nk > SCR_MAX_KT) return false;                        // wider batches: the caller visits all tiles
+    ss.stages = SCR_SMEM_TILES - ss.nk;
     int cc_major = 0, dev = 0;
     CBS_CUDA(cudaGetDevice(&dev));
     CBS_CUDA(cudaDeviceGetAttribute(&cc_major, cudaDevAttrComputeCapabilityMajor, dev));
