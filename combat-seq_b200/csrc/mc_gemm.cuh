@@ -573,8 +573,8 @@ __global__ void k_mcg_list_all(int NJ, int* __restrict__ srclist, int* __restric
     if (threadIdx.x == 0) count[t] = NJ;
 }
 
-// With screening (tu_screen.cu): hi[(2J+h)*rows + i] is an upper bound of max_{j in half h of source tile J} log LH_ij and
-// lo[..] a lower bound of the same maximum over j != i.  Source tile J is kept for target tile t when some row of t can have a
+// With screening (tu_screen.cu): hi[J*rows + i] is an upper bound of max_{j in source tile J} log LH_ij and lo[J*rows + i] a
+// lower bound of the same maximum over j != i.  Source tile J is kept for target tile t when some row of t can have a
 // pair in J within MCG_PRUNE of the row's best pair:  hi[J][i] >= max_J' lo[J'][i] - MCG_PRUNE.  Whatever is dropped is
 // below e^-40 of the row's largest weight, the bound the fold in k_mc_gemm applies anyway.  grid (ntiles64), block 256,
 // NJ bytes of dynamic shared memory.  The 4 thread groups of a block split the source tiles.
@@ -587,15 +587,14 @@ k_mcg_list_screened(const float* __restrict__ hi, const float* __restrict__ lo, 
     const long i = (long)t * MCG_TI + r;
     float m = -INFINITY;
 #pragma unroll 4
-    for (int J = q; J < NJ; J += 4) m = fmaxf(m, fmaxf(lo[(long)(2 * J) * rows + i], lo[(long)(2 * J + 1) * rows + i]));
+    for (int J = q; J < NJ; J += 4) m = fmaxf(m, lo[(long)J * rows + i]);
     mx[q][r] = m;
     for (int J = threadIdx.x; J < NJ; J += 256) flag_s[J] = 0;
     __syncthreads();
     m = fmaxf(fmaxf(mx[0][r], mx[1][r]), fmaxf(mx[2][r], mx[3][r]));
     const float thr = m - prune;                               // -inf when the row has no finite pair: everything is kept
 #pragma unroll 4
-    for (int J = q; J < NJ; J += 4)
-        if (!(fmaxf(hi[(long)(2 * J) * rows + i], hi[(long)(2 * J + 1) * rows + i]) < thr)) flag_s[J] = 1;
+    for (int J = q; J < NJ; J += 4) if (!(hi[(long)J * rows + i] < thr)) flag_s[J] = 1;      // (NaN counts as kept)
     __syncthreads();
     if (threadIdx.x < 32) {
         const int lane = threadIdx.x;

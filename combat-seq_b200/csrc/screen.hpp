@@ -7,8 +7,8 @@ namespace cbs {
 
 // For every target row i of this rank's 128-row blocks and every 128-wide source tile J (rows in the batch's abundance
 // order, operands P / Q as built for k_mc_gemm):
-//   hi[(2J+h)*rows + i] >= max_{j in half h of J}          log LH_ij - b_i        (an upper bound)
-//   lo[(2J+h)*rows + i] <= max_{j in half h of J, j != i}  log LH_ij - b_i        (a lower bound)
+//   hi[J*rows + i] >= max_{j in J}          log LH_ij - b_i        (an upper bound)
+//   lo[J*rows + i] <= max_{j in J, j != i}  log LH_ij - b_i        (a lower bound)
 // with one unknown offset b_i per row (the order-0 Chebyshev coefficient, common to all sources of a row, is left out).
 // Returns false (nothing launched) when the shape is outside what the kernel supports; the caller then visits all tiles.
 bool mc_screen(const double* P, const double* Q, const McgShape& sh, McgOwn own, int slot, float* hi, float* lo,

@@ -131,8 +131,8 @@ static McPlan plan_mc_gemm(const int32_t* cnt, long G, int n, const int* d_cols,
     pl.count = g_dev.get<int>(sl("mcg_count", slot), (size_t)ntiles64);
     bool screened = false;
     if (g_tune.mc_band && own_rows > 0) {
-        float* hi = g_dev.get<float>(sl("mcs_hi", slot), (size_t)2 * NJ * sh.rows);
-        float* lo = g_dev.get<float>(sl("mcs_lo", slot), (size_t)2 * NJ * sh.rows);
+        float* hi = g_dev.get<float>(sl("mcs_hi", slot), (size_t)NJ * sh.rows);
+        float* lo = g_dev.get<float>(sl("mcs_lo", slot), (size_t)NJ * sh.rows);
         screened = mc_screen(pl.P, pl.Q, sh, own, slot, hi, lo, st);
         if (screened) {
             t_ctx->set_func_attr((const void*)k_mcg_list_screened, cudaFuncAttributeMaxDynamicSharedMemorySize, 64 * 1024);

@@ -6,62 +6,66 @@
 // evaluates ALL pairs of a batch at reduced precision together with a bound on its own error,
 //
 //   S_ij = sum_k P_ik Q_jk              in bf16 x 2 (hi/lo split: Ph Qh + Ph Ql + Pl Qh), fp32 accumulation in TMEM
-//   D_ij = sum_k |P_ik| |Q_jk|          in bf16 (1 % is enough for a bound)
-//   |S_ij - exact| <= SCR_EPS * D_ij    (3 * 2^-18 from the dropped lo*lo and residual terms + the fp32 accumulation)
+//   |S_ij - exact| <= SCR_EPS * sum_k |P_ik| |Q_jk|      (3 * 2^-18 from the dropped lo*lo and residual terms + the fp32
+//                                                          accumulation), and, term by term,
+//   sum_k |P_ik| |Q_jk| <= |x_i| |A_j|  (Cauchy-Schwarz over the samples; the two vectors are close to parallel)
+//                        + sum_k |C_ik|  (the Chebyshev polynomials are bounded by 1)
+//                        + (#counts of i below 4) * max_v |lgamma(v + r_j) - lgamma(v + 1)|,
 //
-// and reduces every 128 x 128 tile to per-row maxima of the upper bound S + SCR_EPS*D and of the lower bound S - SCR_EPS*D.
-// k_mcg_list_screened (mc_gemm.cuh) keeps a source tile for a target tile iff an upper bound reaches a row's best lower
-// bound - 40; the FP64 contraction then visits only those tiles.  tcgen05 has no FP64 kind, so the weights themselves stay on
-// the DMMA path; what runs here is 40 tcgen05.mma (128 x 128 x 16) per tile pair, a few per cent of the FP64 work it removes.
+// i.e. three rank-one terms that the epilogue forms from one float4 per row and one per column, and reduces every
+// 128 x 128 tile to per-row maxima of the upper bound S + d and of the lower bound S - d.  k_mcg_list_screened (mc_gemm.cuh)
+// keeps a source tile for a target tile iff an upper bound reaches a row's best lower bound - 40; the FP64 contraction then
+// visits only those tiles.  tcgen05 has no FP64 kind, so the weights themselves stay on the DMMA path; what runs here is 30
+// tcgen05.mma (128 x 256 x 16) per 128 x 256 pairs, a few per cent of the FP64 work it removes.
 //
-// Operand layout.  A row of P or Q is a sequence of 64-column k-tiles, each 4 sub-blocks of 16 columns (one MMA K step):
-//   sample part (x_is / A_js): chunk c of 16 samples lives in k-tile c / 2 as sub-blocks (hi, lo) [+2 for odd c];
-//   series part (Chebyshev orders >= 1 and the one-hot columns): chunk c lives in k-tile NXT + c as (hi, lo, |.|, 0).
-// The cross terms of the split are MMAs between different sub-blocks of the SAME pair of k-tiles (A descriptor at hi, B
-// descriptor at lo, ...), so no operand is stored or fetched twice; the sample part of D needs no operand of its own:
-// counts are >= 0 and A_js <= 0, so |x| |A| = x (-A): the hi x hi MMA again with the negate-B bit of the instruction descriptor.
+// Operand layout.  A row of P or Q is a sequence of 16-column chunks (7 chunks of samples, then 3 chunks holding the
+// Chebyshev orders >= 1 and the one-hot columns at C5's shape); a 64-column k-tile holds two chunks as the four 16-column
+// sub-blocks (hi, lo, hi, lo).  The cross terms of the split are MMAs between different sub-blocks of the SAME pair of
+// k-tiles (A descriptor at hi, B descriptor at lo, ...), so no operand is stored or fetched twice.
 //
-// Kernel: one CTA = one 128-row target block x a range of 128-row source tiles.  The target block's k-tiles stay resident in
-// shared memory; warp 0 streams the source tiles' k-tiles through a ring with bulk async copies (the global layout is the
-// shared-memory image: 128 rows x 64 bf16, 128-byte swizzle, one 16 KB block per copy; the stream is latency-bound, so the
-// ring takes all the shared memory the resident operand leaves); one lane of warp 1 issues tcgen05.mma (M = N = 128, K = 16
-// per instruction, A and B from shared memory descriptors, accumulators S and D in TMEM, double buffered: 2 x 256 of the
-// 512 columns); warps 2-9 read the accumulators back with tcgen05.ld and fold them into the row maxima while the next tile
-// is being multiplied.
+// Kernel: one CTA = one 128-row target block x a range of 256-row source tile pairs.  The target block's k-tiles stay resident
+// in shared memory; warp 0 streams the source rows' k-tiles (32 KB each) through a ring with bulk async copies (the global
+// layout is the shared-memory image: 128 rows x 64 bf16 per 16 KB block, 128-byte swizzle); one lane of warp 1 issues
+// tcgen05.mma (M = 128, N = 256, K = 16 per instruction: 12 KB of shared-memory operands per 128 tensor-core cycles, under
+// the 128 B/clk of the SM, which N = 128 is not), A and B from shared memory descriptors, the accumulator in TMEM, double
+// buffered (2 x 256 of the 512 columns); warps 2-9 read the accumulator back with tcgen05.ld and fold it into the row maxima
+// while the next tile is being multiplied.
 #include "screen.hpp"
 #include <cuda_bf16.h>
 
 namespace cbs {
 
 constexpr int SCR_BM = 128;                 // target rows per CTA (UMMA M)
-constexpr int SCR_BN = 128;                 // source rows per tile (UMMA N) = MCG_TILE
+constexpr int SCR_BN = 256;                 // source rows per MMA (UMMA N): two source tiles of the contraction
 constexpr int SCR_KTILE = 64;               // bf16 per operand row and k-tile: 128 bytes, the swizzle span
-constexpr int SCR_TILE_BYTES = SCR_BM * SCR_KTILE * 2;      // 16 KB
-constexpr int SCR_MAX_KT = 8;               // most k-tiles of an operand row the kernel supports (resident A: 128 KB)
-constexpr int SCR_SMEM_TILES = 13;          // 16 KB tiles that fit shared memory next to the barriers: resident A + ring of B
-constexpr int SCR_EPI_WARPS = 8;            // two warps per TMEM lane quarter, each folding half of the tile's columns
+constexpr int SCR_TILE_BYTES = SCR_BM * SCR_KTILE * 2;      // 16 KB: one k-tile of one 128-row block
+constexpr int SCR_MAX_KT = 7;               // most k-tiles of an operand row the kernel supports (resident A: 112 KB)
+constexpr int SCR_SMEM_BLOCKS = 13;         // 16 KB blocks that fit shared memory: resident A + ring of B (2 blocks per stage)
+constexpr int SCR_EPI_WARPS = 8;            // two warps per TMEM lane quarter, one per source tile of the pair
 constexpr int SCR_THREADS = 64 + 32 * SCR_EPI_WARPS;     // warp 0 producer, warp 1 MMA issuer, warps 2-9 epilogue
-constexpr float SCR_EPS = 3.1e-5f;          // error bound of S relative to D (see above), including 1 % for D's own rounding
+constexpr float SCR_EPS = 3.1e-5f;          // error of S relative to sum |P||Q| (see above), incl. the fp32 rounding of the bound
 constexpr float SCR_EPS_C = 2.5e-7f;        // fp32 rounding of the per-source constant c_j added in the epilogue
-static_assert(SCR_BN == MCG_TILE, "screening tiles are the contraction's source tiles");
+static_assert(SCR_BM == MCG_TILE && SCR_BN == 2 * MCG_TILE, "screening tiles are the contraction's source tiles");
 
 struct ScrShape {
     int n, KS;       // samples; KS - n series columns (Chebyshev orders 1.., one-hot; no order-0 term, no c_j)
-    int nxc, nxt;    // 16-sample chunks and the k-tiles holding them (2 chunks per k-tile)
-    int ncc;         // 16-column chunks of the series part (1 per k-tile)
-    int nk;          // k-tiles per operand row = nxt + ncc
-    int stages;      // ring of B k-tiles = SCR_SMEM_TILES - nk
+    int nxc, ncc;    // 16-column chunks of the sample part and of the series part
+    int nk;          // k-tiles per operand row = ceil((nxc + ncc) / 2)
+    int stages;      // ring of B stages (2 blocks each)
     long rows;       // rows of P / Q (multiple of 128)
-    int NJ;          // source tiles
+    long nrb;        // 128-row blocks; the operands hold one more (zero) block so that the last pair can be read whole
+    int NJ2;         // source tile pairs
 };
 
 // ---- operand conversion: FP64 P / Q (mc_gemm.cuh layout) -> bf16 tiles in the shared-memory image ------------------
 // Element (row r, k-tile kt, column c of the k-tile) lives in block [kt][r / 128] (16 KB each) at byte (r % 128) * 128 +
 // ((c / 8) ^ (r % 8)) * 16 + (c % 8) * 2: the 128-byte swizzle the UMMA descriptors below declare.  One thread writes one
 // 16-byte chunk (8 columns = half a sub-block).  P is only built for the owned blocks, the other blocks are never read.
+// vec[r]: the row's terms of the error bound; targets (x = SCR_EPS |x_i|, y = SCR_EPS sum |C_ik|, z = SCR_EPS #small counts),
+// sources (x = c_j, y = |A_j|, z = max_v |lg_jv|, w = SCR_EPS_C |c_j|).
 __global__ void __launch_bounds__(256)
 k_scr_convert(const double* __restrict__ X, McgShape sh, ScrShape ss, int is_q, McgOwn own, long n_rows,
-              __nv_bfloat16* __restrict__ out, float* __restrict__ cq) {
+              __nv_bfloat16* __restrict__ out, float4* __restrict__ vec) {
     const long t = (long)blockIdx.x * blockDim.x + threadIdx.x;
     const int chunks_per_row = ss.nk * 8;
     const long lr = t / chunks_per_row;
@@ -69,33 +73,41 @@ k_scr_convert(const double* __restrict__ X, McgShape sh, ScrShape ss, int is_q, 
     if (lr >= n_rows) return;
     const long r = is_q ? lr : own.row(lr);
     const int kt = ch >> 3, c8 = ch & 7, sb = c8 >> 1, half = c8 & 1;
-    int kind, col0;                                               // kind 0 hi, 1 lo, 2 |hi|, 3 zero; col0: first MC column, < 0 = none
-    if (kt < ss.nxt) {
-        const int c = 2 * kt + (sb >> 1);
-        kind = sb & 1;
-        col0 = c < ss.nxc ? c * 16 + half * 8 : -1;
-    } else {
-        kind = sb;
-        col0 = ss.n + 1 + (kt - ss.nxt) * 16 + half * 8;          // series columns start after the order-0 term at MC column n
-    }
-    const int lim = kt < ss.nxt ? ss.n : sh.KT - 1;               // exclusive end of the part in MC columns (c_j at KT - 1 is left out)
+    const int c = 2 * kt + (sb >> 1), lo_part = sb & 1;           // chunk, hi / lo
+    int col0, lim;                                                // first MC column of the 8, exclusive end of the part
+    if (c < ss.nxc) { col0 = c * 16 + half * 8; lim = ss.n; }
+    else { col0 = ss.n + 1 + (c - ss.nxc) * 16 + half * 8; lim = c < ss.nxc + ss.ncc ? sh.KT - 1 : 0; }   // (order-0 term at n, c_j at KT-1 left out)
     __align__(16) __nv_bfloat16 v[8];
 #pragma unroll
     for (int e = 0; e < 8; ++e) {
         float f = 0.f;
         const int k = col0 + e;
-        if (col0 >= 0 && kind < 3 && k < lim) {
+        if (k < lim && r < sh.rows) {
             const double x = X[mcg_index(sh.rows, r, k)];
             const float h = __bfloat162float(__double2bfloat16(x));
-            f = kind == 0 ? h : kind == 1 ? (float)(x - (double)h) : fabsf(h);
+            f = lo_part ? (float)(x - (double)h) : h;
         }
         v[e] = __float2bfloat16_rn(f);
     }
-    const long blk = (long)kt * (sh.rows / SCR_BM) + r / SCR_BM;
+    const long blk = (long)kt * (ss.nrb + 1) + r / SCR_BM;
     const int rr = (int)(r % SCR_BM);
     char* dst = reinterpret_cast<char*>(out) + blk * SCR_TILE_BYTES + rr * 128 + ((c8 ^ (rr & 7)) << 4);
     *reinterpret_cast<uint4*>(dst) = *reinterpret_cast<const uint4*>(v);
-    if (is_q && ch == 0) cq[r] = (float)X[mcg_index(sh.rows, r, sh.KT - 1)];      // c_j, added in fp32 in the epilogue
+    if (ch == 0) {
+        if (r >= sh.rows) { vec[r] = make_float4(-1e30f, 0.f, 0.f, 0.f); return; }          // the padding block of Q: impossible sources
+        double s2 = 0, s1 = 0, mx = 0;
+        for (int k = 0; k < ss.n; ++k) { const double x = X[mcg_index(sh.rows, r, k)]; s2 += x * x; }
+        if (!is_q) {
+            for (int k = ss.n + 1; k < ss.n + sh.Kc; ++k) s1 += fabs(X[mcg_index(sh.rows, r, k)]);
+            double hot = 0;
+            for (int k = ss.n + sh.Kc; k < sh.KT - 1; ++k) hot += X[mcg_index(sh.rows, r, k)];
+            vec[r] = make_float4(SCR_EPS * (float)sqrt(s2), SCR_EPS * (float)s1, SCR_EPS * (float)hot, 0.f);
+        } else {
+            for (int k = ss.n + sh.Kc; k < sh.KT - 1; ++k) mx = fmax(mx, fabs(X[mcg_index(sh.rows, r, k)]));
+            const float cj = (float)X[mcg_index(sh.rows, r, sh.KT - 1)];
+            vec[r] = make_float4(cj, (float)sqrt(s2), (float)mx, SCR_EPS_C * fabsf(cj));
+        }
+    }
 }
 
 // ---- PTX wrappers ----------------------------------------------------------------------------------------------------
@@ -157,33 +169,33 @@ __device__ __forceinline__ uint64_t scr_desc(uint32_t smem_addr) {
     return ((uint64_t)hi << 32) | lo;
 }
 // Instruction descriptor (cute::UMMA::InstrDescriptor): D fp32 (bits 4-5 = 1), A and B bf16 (bits 7-9, 10-12 = 1), both
-// K-major (bits 15, 16 = 0), N >> 3 in bits 17-22, M >> 4 in bits 24-28; bit 14 negates B.
-__host__ __device__ constexpr uint32_t scr_idesc(bool neg_b) {
-    return (1u << 4) | (1u << 7) | (1u << 10) | ((neg_b ? 1u : 0u) << 14) | ((uint32_t)(SCR_BN >> 3) << 17) | ((uint32_t)(SCR_BM >> 4) << 24);
+// K-major (bits 15, 16 = 0), N >> 3 in bits 17-22, M >> 4 in bits 24-28.
+__host__ __device__ constexpr uint32_t scr_idesc() {
+    return (1u << 4) | (1u << 7) | (1u << 10) | ((uint32_t)(SCR_BN >> 3) << 17) | ((uint32_t)(SCR_BM >> 4) << 24);
 }
 
 struct ScrSmem {
-    // [SCR_SMEM_TILES x 16 KB: the resident A k-tiles, then the B ring] [c_j double buffer] [barriers] [tmem base];
-    // the tiles need 1024-byte alignment
-    static constexpr size_t tile_bytes = (size_t)SCR_SMEM_TILES * SCR_TILE_BYTES;
-    static constexpr size_t cq_off = tile_bytes;
-    static constexpr size_t bar_off = cq_off + 2 * SCR_BN * sizeof(float2);
-    static constexpr int max_stages = SCR_SMEM_TILES;
-    static constexpr size_t total = bar_off + (3 + 2 * max_stages + 4) * sizeof(uint64_t) + 16 + 1024 /*alignment slack*/;
+    // [SCR_SMEM_BLOCKS x 16 KB: the resident A k-tiles, then the B ring (32 KB stages)] [column vectors, double buffered]
+    // [barriers] [tmem base]; the tiles need 1024-byte alignment
+    static constexpr size_t tile_bytes = (size_t)SCR_SMEM_BLOCKS * SCR_TILE_BYTES;
+    static constexpr size_t qv_off = tile_bytes;
+    static constexpr size_t bar_off = qv_off + 2 * SCR_BN * sizeof(float4);
+    static constexpr int max_stages = SCR_SMEM_BLOCKS / 2;
+    static constexpr size_t total = bar_off + (5 + 2 * max_stages + 1) * sizeof(uint64_t) + 16 + 1024 /*alignment slack*/;
 };
 static_assert(ScrSmem::total <= 227 * 1024, "screening kernel: shared memory");
 
-// items[w] = (target block, first source tile, number of source tiles).  hi / lo are [2 NJ][rows]: one entry per half
-// (64 columns) of a source tile.
+// items[w] = (target block, first source tile pair, number of pairs).  hi / lo are [NJ][rows], NJ = 128-row source tiles.
 __global__ void __launch_bounds__(SCR_THREADS, 1)
-k_scr_mma(const __nv_bfloat16* __restrict__ Pt, const __nv_bfloat16* __restrict__ Qt, const float* __restrict__ cq,
-          ScrShape ss, const int3* __restrict__ items, float* __restrict__ hi, float* __restrict__ lo) {
+k_scr_mma(const __nv_bfloat16* __restrict__ Pt, const __nv_bfloat16* __restrict__ Qt, const float4* __restrict__ pvec,
+          const float4* __restrict__ qvec, ScrShape ss, const int3* __restrict__ items, float* __restrict__ hi,
+          float* __restrict__ lo) {
     extern __shared__ unsigned char scr_raw[];
     unsigned char* smem = reinterpret_cast<unsigned char*>((reinterpret_cast<uintptr_t>(scr_raw) + 1023) & ~(uintptr_t)1023);
     const int NST = ss.stages;
     unsigned char* a_s = smem;
     unsigned char* b_s = smem + (size_t)ss.nk * SCR_TILE_BYTES;
-    float2* cq_s = reinterpret_cast<float2*>(smem + ScrSmem::cq_off);                // [2][128] (c_j, SCR_EPS_C |c_j|)
+    float4* qv_s = reinterpret_cast<float4*>(smem + ScrSmem::qv_off);                // [2][256]
     uint64_t* bars = reinterpret_cast<uint64_t*>(smem + ScrSmem::bar_off);
     uint64_t* a_full = bars;                    // 1
     uint64_t* acc_full = bars + 1;              // 2
@@ -196,7 +208,8 @@ k_scr_mma(const __nv_bfloat16* __restrict__ Pt, const __nv_bfloat16* __restrict_
     const int3 item = items[blockIdx.x];
     const long iblk = item.x;
     const int j0 = item.y, nj = item.z;
-    const long nrb = ss.rows / SCR_BM;
+    const long nrb1 = ss.nrb + 1;
+    constexpr uint32_t STAGE_BYTES = 2 * SCR_TILE_BYTES;
 
     if (threadIdx.x == 0) {
         sbar_init(a_full, 1);
@@ -204,7 +217,7 @@ k_scr_mma(const __nv_bfloat16* __restrict__ Pt, const __nv_bfloat16* __restrict_
         for (int s = 0; s < 2; ++s) { sbar_init(&acc_full[s], 1); sbar_init(&acc_empty[s], SCR_EPI_WARPS); }
         asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
     }
-    if (warp == 2) {                            // TMEM: all 512 columns (two accumulator stages of S and D)
+    if (warp == 2) {                            // TMEM: all 512 columns (two accumulator stages of 128 x 256 fp32)
         asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(s_u32(tmem_slot)), "r"(512u) : "memory");
         asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
     }
@@ -218,15 +231,15 @@ k_scr_mma(const __nv_bfloat16* __restrict__ Pt, const __nv_bfloat16* __restrict_
         if (lane == 0) {
             sbar_expect_tx(a_full, (uint32_t)ss.nk * SCR_TILE_BYTES);
             for (int kt = 0; kt < ss.nk; ++kt)
-                sbulk_g2s(a_s + (size_t)kt * SCR_TILE_BYTES, reinterpret_cast<const char*>(Pt) + ((size_t)kt * nrb + iblk) * SCR_TILE_BYTES,
+                sbulk_g2s(a_s + (size_t)kt * SCR_TILE_BYTES, reinterpret_cast<const char*>(Pt) + ((size_t)kt * nrb1 + iblk) * SCR_TILE_BYTES,
                           SCR_TILE_BYTES, a_full);
             int st = 0; uint32_t ph = 0;
             for (int jj = 0; jj < nj; ++jj) {
                 for (int kt = 0; kt < ss.nk; ++kt) {
                     sbar_wait(&b_empty[st], ph ^ 1u);
-                    sbar_expect_tx(&b_full[st], SCR_TILE_BYTES);
-                    sbulk_g2s(b_s + (size_t)st * SCR_TILE_BYTES,
-                              reinterpret_cast<const char*>(Qt) + ((size_t)kt * nrb + (j0 + jj)) * SCR_TILE_BYTES, SCR_TILE_BYTES, &b_full[st]);
+                    sbar_expect_tx(&b_full[st], STAGE_BYTES);
+                    sbulk_g2s(b_s + (size_t)st * STAGE_BYTES,               // two consecutive 128-row blocks of k-tile kt
+                              reinterpret_cast<const char*>(Qt) + ((size_t)kt * nrb1 + 2 * (size_t)(j0 + jj)) * SCR_TILE_BYTES, STAGE_BYTES, &b_full[st]);
                     if (++st == NST) { st = 0; ph ^= 1u; }
                 }
             }
@@ -237,94 +250,77 @@ k_scr_mma(const __nv_bfloat16* __restrict__ Pt, const __nv_bfloat16* __restrict_
             sbar_wait(a_full, 0);
             tc_fence_after();
             const uint32_t a_addr = s_u32(a_s), b_addr = s_u32(b_s);
+            const int nchunks = ss.nxc + ss.ncc;
             int st = 0; uint32_t ph = 0;
             for (int jj = 0; jj < nj; ++jj) {
                 const int as = jj & 1;
                 sbar_wait(&acc_empty[as], ((uint32_t)(jj >> 1) & 1u) ^ 1u);
                 tc_fence_after();
-                const uint32_t d_s = tmem + (uint32_t)as * 256u, d_d = d_s + 128u;
-                bool s_started = false, d_started = false;
+                const uint32_t d_s = tmem + (uint32_t)as * 256u;
+                uint32_t started = 0u;
                 for (int kt = 0; kt < ss.nk; ++kt) {
                     sbar_wait(&b_full[st], ph);
                     tc_fence_after();
-                    const uint32_t at = a_addr + (uint32_t)kt * SCR_TILE_BYTES, bt = b_addr + (uint32_t)st * SCR_TILE_BYTES;
-                    auto mma = [&](int sa, int sb, bool to_d, bool neg) {          // sub-blocks of 16 columns: 32 bytes apart
-                        bool& started = to_d ? d_started : s_started;
-                        tc_mma_bf16(to_d ? d_d : d_s, scr_desc(at + (uint32_t)sa * 32u), scr_desc(bt + (uint32_t)sb * 32u),
-                                    scr_idesc(neg), started ? 1u : 0u);
-                        started = true;
-                    };
-                    if (kt < ss.nxt) {
+                    const uint32_t at = a_addr + (uint32_t)kt * SCR_TILE_BYTES, bt = b_addr + (uint32_t)st * STAGE_BYTES;
 #pragma unroll
-                        for (int h = 0; h < 2; ++h) {
-                            if (2 * kt + h < ss.nxc) {
-                                mma(2 * h, 2 * h, false, false);          // x_hi A_hi
-                                mma(2 * h, 2 * h + 1, false, false);      // x_hi A_lo
-                                mma(2 * h + 1, 2 * h, false, false);      // x_lo A_hi
-                                mma(2 * h, 2 * h, true, true);            // |x| |A| = x_hi (-A_hi)
-                            }
+                    for (int h = 0; h < 2; ++h) {                         // the k-tile's two chunks: sub-blocks (hi, lo) 32 bytes apart
+                        if (2 * kt + h < nchunks) {
+                            const uint32_t ah = at + (uint32_t)(2 * h) * 32u, bh = bt + (uint32_t)(2 * h) * 32u;
+                            tc_mma_bf16(d_s, scr_desc(ah), scr_desc(bh), scr_idesc(), started); started = 1u;      // hi x hi
+                            tc_mma_bf16(d_s, scr_desc(ah), scr_desc(bh + 32u), scr_idesc(), 1u);                   // hi x lo
+                            tc_mma_bf16(d_s, scr_desc(ah + 32u), scr_desc(bh), scr_idesc(), 1u);                   // lo x hi
                         }
-                    } else {
-                        mma(0, 0, false, false);                          // C_hi T_hi
-                        mma(0, 1, false, false);                          // C_hi T_lo
-                        mma(1, 0, false, false);                          // C_lo T_hi
-                        mma(2, 2, true, false);                           // |C| |T|
                     }
                     tc_commit(&b_empty[st]);                      // the stage is free once these MMAs have read it
                     if (++st == NST) { st = 0; ph ^= 1u; }
                 }
-                tc_commit(&acc_full[as]);                         // accumulators of tile jj complete
+                tc_commit(&acc_full[as]);                         // accumulator of pair jj complete
             }
         }
     } else {
-        // ===== epilogue: warps 2..9; warp w may touch TMEM lanes 32 (w % 4) .. +31; the two warps of a lane quarter split the
-        // tile's columns.  The fold is latency-bound (max chains), so each warp keeps four independent running maxima per
-        // bound and the per-source constants come in as one 16-byte shared-memory load per two columns.
+        // ===== epilogue: warps 2..9; warp w may touch TMEM lanes 32 (w % 4) .. +31; the two warps of a lane quarter take one
+        // source tile (128 columns) of the pair each.  The fold is latency-bound (max chains), so each warp keeps four
+        // independent running maxima per bound; the per-source terms come in as one 16-byte shared-memory load per column.
         const int q = warp & 3, half = (warp - 2) >> 2;
         const int row = q * 32 + lane;                            // row of the target block = TMEM lane
         const long grow = iblk * SCR_BM + row;
-        const int et = threadIdx.x - 64;                          // 0 .. 32 SCR_EPI_WARPS - 1
-        constexpr int HC = SCR_BN / 2;                            // columns per warp
+        const int et = threadIdx.x - 64;                          // 0 .. 255
+        const float4 pv = pvec[grow];                             // SCR_EPS (|x_i|, sum |C_ik|, #small counts)
+        constexpr int HC = SCR_BN / 2;                            // columns per warp = one source tile
         for (int jj = 0; jj < nj; ++jj) {
             const int as = jj & 1;
-            const int J = j0 + jj;
-            if (et < SCR_BN) { const float c = cq[(long)J * SCR_BN + et]; cq_s[as * SCR_BN + et] = make_float2(c, SCR_EPS_C * fabsf(c)); }
+            const long J = 2 * (long)(j0 + jj) + half;            // source tile of this warp
+            qv_s[as * SCR_BN + et] = qvec[2 * (long)(j0 + jj) * MCG_TILE + et];
             asm volatile("bar.sync 1, %0;" ::"n"(32 * SCR_EPI_WARPS) : "memory");        // the epilogue warps
             sbar_wait(&acc_full[as], (uint32_t)(jj >> 1) & 1u);
             tc_fence_after();
-            const uint32_t t_s = tmem + ((uint32_t)(q * 32) << 16) + (uint32_t)as * 256u + (uint32_t)(half * HC), t_d = t_s + 128u;
-            const bool diag = (long)J == iblk;
+            const uint32_t t_s = tmem + ((uint32_t)(q * 32) << 16) + (uint32_t)as * 256u + (uint32_t)(half * HC);
+            const bool diag = J == iblk;
             float mh[4] = {-INFINITY, -INFINITY, -INFINITY, -INFINITY}, ml[4] = {-INFINITY, -INFINITY, -INFINITY, -INFINITY};
 #pragma unroll 1
             for (int c0 = 0; c0 < HC; c0 += 32) {
-                float s[32], d[32];
+                float s[32];
                 tc_ld32(t_s + (uint32_t)c0, s);
-                tc_ld32(t_d + (uint32_t)c0, d);
                 tc_ld_wait();
-                const float4* cp = reinterpret_cast<const float4*>(cq_s + as * SCR_BN + half * HC + c0);
+                const float4* qp = qv_s + as * SCR_BN + half * HC + c0;
 #pragma unroll
-                for (int c = 0; c < 32; c += 2) {
-                    const float4 ce = cp[c >> 1];                 // (c_j, e_j) of columns c, c + 1
-                    const float v0 = s[c] + ce.x, v1 = s[c + 1] + ce.z;
-                    const float e0 = fmaf(SCR_EPS, d[c], ce.y), e1 = fmaf(SCR_EPS, d[c + 1], ce.w);
-                    mh[c & 2] = fmaxf(mh[c & 2], v0 + e0);
-                    mh[(c & 2) + 1] = fmaxf(mh[(c & 2) + 1], v1 + e1);
-                    float l0 = v0 - e0, l1 = v1 - e1;
-                    if (diag) {                                   // j == i is not a source (mu[-i,], helper_seq.R:11-14)
-                        if (half * HC + c0 + c == row) l0 = -INFINITY;
-                        if (half * HC + c0 + c + 1 == row) l1 = -INFINITY;
-                    }
-                    ml[c & 2] = fmaxf(ml[c & 2], l0);
-                    ml[(c & 2) + 1] = fmaxf(ml[(c & 2) + 1], l1);
+                for (int c = 0; c < 32; ++c) {
+                    const float4 qv = qp[c];                      // (c_j, |A_j|, max |lg_jv|, SCR_EPS_C |c_j|)
+                    const float v = s[c] + qv.x;
+                    const float e = fmaf(pv.x, qv.y, fmaf(pv.z, qv.z, pv.y + qv.w));
+                    mh[c & 3] = fmaxf(mh[c & 3], v + e);
+                    float l = v - e;
+                    if (diag && c0 + c == row) l = -INFINITY;     // j == i is not a source (mu[-i,], helper_seq.R:11-14)
+                    ml[c & 3] = fmaxf(ml[c & 3], l);
                 }
             }
             tc_fence_before();
             __syncwarp();
             if (lane == 0) sbar_arrive(&acc_empty[as]);
-            const float mhi = fmaxf(fmaxf(mh[0], mh[1]), fmaxf(mh[2], mh[3])), mlo = fmaxf(fmaxf(ml[0], ml[1]), fmaxf(ml[2], ml[3]));
-            // the two column halves of a tile are combined by k_mcg_list_screened: hi / lo are [2 NJ][rows]
-            __stcs(&hi[((long)J * 2 + half) * ss.rows + grow], mhi);      // streamed: read once, keep L2 for the operands
-            __stcs(&lo[((long)J * 2 + half) * ss.rows + grow], mlo);
+            if (J < ss.nrb) {
+                __stcs(&hi[J * ss.rows + grow], fmaxf(fmaxf(mh[0], mh[1]), fmaxf(mh[2], mh[3])));      // streamed: read once
+                __stcs(&lo[J * ss.rows + grow], fmaxf(fmaxf(ml[0], ml[1]), fmaxf(ml[2], ml[3])));
+            }
         }
     }
     tc_fence_before();
@@ -335,17 +331,15 @@ k_scr_mma(const __nv_bfloat16* __restrict__ Pt, const __nv_bfloat16* __restrict_
     }
 }
 
-// Work items of the screening kernel: every owned target block x source-tile ranges of NJ / nchunk tiles, ordered
-// range-major: the CTAs that are resident at the same time stream the SAME range of source tiles (a few MB), so the B
-// operand is read from HBM once per range and served from L2 to the other SMs; block-major order has every SM streaming a
-// different part of the 70 MB operand and the pass runs at HBM speed.
-__global__ void k_scr_items(McgOwn own, long nrb, int NJ, int nchunk, int3* __restrict__ items) {
+// Work items of the screening kernel: every owned target block x ranges of NJ2 / nchunk source tile pairs, ordered
+// range-major (the CTAs resident at the same time stream the same range of source rows: L2 reuse).
+__global__ void k_scr_items(McgOwn own, long rows, int NJ2, int nchunk, int3* __restrict__ items) {
     const long lb = (long)blockIdx.x * blockDim.x + threadIdx.x;
-    const long nb = own.nblocks(nrb * SCR_BM);
+    const long nb = own.nblocks(rows);
     if (lb >= nb) return;
     const int blk = (int)(lb * own.world + own.rank);
     for (int c = 0; c < nchunk; ++c) {
-        const int a = (int)((long)NJ * c / nchunk), b = (int)((long)NJ * (c + 1) / nchunk);
+        const int a = (int)((long)NJ2 * c / nchunk), b = (int)((long)NJ2 * (c + 1) / nchunk);
         items[(long)c * nb + lb] = make_int3(blk, a, b - a);
     }
 }
@@ -356,35 +350,36 @@ bool mc_screen(const double* P, const double* Q, const McgShape& sh, McgOwn own,
     ss.n = sh.n;
     ss.KS = sh.KT - 2;
     ss.nxc = (sh.n + 15) / 16;
-    ss.nxt = (ss.nxc + 1) / 2;
     ss.ncc = (ss.KS - sh.n + 15) / 16;
-    ss.nk = ss.nxt + ss.ncc;
+    ss.nk = (ss.nxc + ss.ncc + 1) / 2;
     ss.rows = sh.rows;
-    ss.NJ = (int)(sh.rows / SCR_BN);
+    ss.nrb = sh.rows / SCR_BM;
+    ss.NJ2 = (int)((ss.nrb + 1) / 2);
     if (ss.nk > SCR_MAX_KT) return false;                        // wider batches: the caller visits all tiles
-    ss.stages = SCR_SMEM_TILES - ss.nk;
+    ss.stages = (SCR_SMEM_BLOCKS - ss.nk) / 2;
     int cc_major = 0, dev = 0;
     CBS_CUDA(cudaGetDevice(&dev));
     CBS_CUDA(cudaDeviceGetAttribute(&cc_major, cudaDevAttrComputeCapabilityMajor, dev));
     if (cc_major != 10) return false;                            // tcgen05 / TMEM
     const std::string sfx = slot ? "#1" : "#0";
-    const long nrb = sh.rows / SCR_BM, own_blocks = own.nblocks(sh.rows);
-    const size_t op_elems = (size_t)ss.nk * nrb * SCR_BM * SCR_KTILE;
-    __nv_bfloat16* Pt = (__nv_bfloat16*)g_dev.get("mcs_Pt" + sfx, op_elems * 2);
-    __nv_bfloat16* Qt = (__nv_bfloat16*)g_dev.get("mcs_Qt" + sfx, op_elems * 2);
-    float* cq = g_dev.get<float>("mcs_cq" + sfx, (size_t)sh.rows);
+    const long own_blocks = own.nblocks(sh.rows);
+    const size_t op_bytes = (size_t)ss.nk * (ss.nrb + 1) * SCR_TILE_BYTES;
+    __nv_bfloat16* Pt = (__nv_bfloat16*)g_dev.get("mcs_Pt" + sfx, op_bytes);
+    __nv_bfloat16* Qt = (__nv_bfloat16*)g_dev.get("mcs_Qt" + sfx, op_bytes);
+    float4* pvec = (float4*)g_dev.get("mcs_pvec" + sfx, (size_t)(sh.rows + SCR_BM) * sizeof(float4));
+    float4* qvec = (float4*)g_dev.get("mcs_qvec" + sfx, (size_t)(sh.rows + SCR_BM) * sizeof(float4));
     const int cpr = ss.nk * 8;
-    CBS_LAUNCH(k_scr_convert, grid1(own_blocks * SCR_BM * cpr, 256), 256, 0, st, P, sh, ss, 0, own, own_blocks * SCR_BM, Pt, (float*)nullptr);
-    CBS_LAUNCH(k_scr_convert, grid1(sh.rows * cpr, 256), 256, 0, st, Q, sh, ss, 1, own, sh.rows, Qt, cq);
+    CBS_LAUNCH(k_scr_convert, grid1(own_blocks * SCR_BM * cpr, 256), 256, 0, st, P, sh, ss, 0, own, own_blocks * SCR_BM, Pt, pvec);
+    CBS_LAUNCH(k_scr_convert, grid1((sh.rows + SCR_BM) * cpr, 256), 256, 0, st, Q, sh, ss, 1, own, sh.rows + SCR_BM, Qt, qvec);
     int sms = 148;
     cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
     // about 8 waves of CTAs and at least 4 ranges; every CTA re-loads its 128-row A operand once, so ranges should not be
     // too short either
-    int nchunk = (int)std::min<long>(std::max<long>(4, (8L * sms + own_blocks - 1) / std::max<long>(own_blocks, 1)), std::max(1, ss.NJ / 8));
+    int nchunk = (int)std::min<long>(std::max<long>(4, (8L * sms + own_blocks - 1) / std::max<long>(own_blocks, 1)), std::max(1, ss.NJ2 / 4));
     int3* items = (int3*)g_dev.get<int>("mcs_items" + sfx, (size_t)3 * own_blocks * nchunk + 3);
-    CBS_LAUNCH(k_scr_items, grid1(own_blocks, 128), 128, 0, st, own, nrb, ss.NJ, nchunk, items);
+    CBS_LAUNCH(k_scr_items, grid1(own_blocks, 128), 128, 0, st, own, sh.rows, ss.NJ2, nchunk, items);
     t_ctx->set_func_attr((const void*)k_scr_mma, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)ScrSmem::total);
-    CBS_LAUNCH(k_scr_mma, dim3((unsigned)(own_blocks * nchunk)), SCR_THREADS, ScrSmem::total, st, Pt, Qt, cq, ss, items, hi, lo);
+    CBS_LAUNCH(k_scr_mma, dim3((unsigned)(own_blocks * nchunk)), SCR_THREADS, ScrSmem::total, st, Pt, Qt, pvec, qvec, ss, items, hi, lo);
     return true;
 }
 
