@@ -52,6 +52,8 @@ def parse_args():
     ap.add_argument("--genes", type=int, default=0, help="override the workload's gene count (debugging only)")
     ap.add_argument("--cpu-genes", type=int, default=0, help="rows of the bounded CPU sample (0 = auto)")
     ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg")
+    ap.add_argument("--inproc", type=int, default=0, help="single-process multi-GPU (cbs_input.n_gpus): time the host-buffer "
+                                                           "call on this many devices of one process (what the R .Call reaches)")
     return ap.parse_args()
 
 
@@ -137,6 +139,30 @@ def cpu_sample(case, d, n_rows, threads):
     scale = float(nz.sum()) / float(len(rows))
     t_full = t_lin * scale + t_mc * scale * scale
     return {"rows": int(len(rows)), "wall_s": wall, "mc_s": t_mc, "t_full_s": t_full, "value": G0 * N / t_full}
+
+
+def measured_pair(pkg, L, name):
+    """An UNEXTRAPOLATED GPU / CPU pair: a workload the CPU oracle finishes in seconds (C2: 20 000 x 24, shrink = FALSE),
+    whole call on both sides, same inputs, host buffers in and out."""
+    case, d = make_case(pkg, name, 0)
+    G0, N = case.counts.shape
+    orc = graft.load_oracle()
+    threads = cpu_threads()
+    x = np.asfortranarray(case.counts.astype(np.float64))
+    t = time.perf_counter()
+    ref = orc.combat_seq(x, d.batch_idx, d.mod, shrink=case.shrink, shrink_disp=case.shrink_disp, nthreads=threads)
+    cpu_s = time.perf_counter() - t
+    out = np.empty((G0, N), order="F")
+    L.combat_seq_into(x, d.batch_idx, d.mod, out, shrink=case.shrink, shrink_disp=case.shrink_disp)
+    ts = []
+    for _ in range(5):
+        t = time.perf_counter()
+        L.combat_seq_into(x, d.batch_idx, d.mod, out, shrink=case.shrink, shrink_disp=case.shrink_disp)
+        ts.append(time.perf_counter() - t)
+    gpu_s = statistics.median(ts)
+    return {"workload": describe(case, d)["workload"], "cpu_s": cpu_s, "cpu_threads": threads, "cpu_kind": "port (C++ oracle, not R)",
+            "gpu_s": gpu_s, "gpu_value": G0 * N / gpu_s, "cpu_value": G0 * N / cpu_s, "unit": UNIT,
+            "exact_match": float((out == ref["adjusted"]).mean()), "extrapolated": False}
 
 
 def auto_cpu_rows(case):
@@ -258,14 +284,35 @@ def run_native(args):
     for _ in range(args.warmup):
         step_resident()
     L.profile_enable(True)
+    L.get_diag("reset")
     n0 = L.kernel_launches()
     ms_val, res, clocks = timed(step_resident, args.steps, 0, ClockSampler(local))
     launches = L.kernel_launches() - n0
     prof = L.profile_dump()
     L.profile_enable(False)
+    diag = {k: L.get_diag(k) for k in ("mc_terms", "mc_tiles_done", "mc_tiles_all", "mc_tail")}
     # ---- e2e arm: host buffers through the C ABI ----
     ms_e2e, res_e, _ = timed(step_e2e, args.steps, min(args.warmup, 1) if not small else args.warmup)
     checksum = float(np.asarray(h_adj.numpy()[:, :: max(1, G0 // 997)]).sum())
+    # ---- the same call from pageable host memory (what an R matrix is): one warm-up, `steps` timed calls, wall clock ----
+    pg_counts = np.asfortranarray(case.counts.astype(np.float64))      # R's numeric matrix: column-major doubles
+    pg_adj = np.empty((G0, N), order="F")
+    L.combat_seq_into(pg_counts, d.batch_idx, d.mod, pg_adj, **opts)
+    barrier()
+    t_pg = time.perf_counter()
+    for _ in range(args.steps):
+        L.combat_seq_into(pg_counts, d.batch_idx, d.mod, pg_adj, **opts)
+    barrier()
+    t_pg = torch.tensor([(time.perf_counter() - t_pg) * 1e3], dtype=torch.float64, device=dev)
+    if world > 1:
+        dist.all_reduce(t_pg, op=dist.ReduceOp.MAX)
+    pageable = {"value": float(G0) * N * args.steps / (float(t_pg.item()) * 1e-3), "unit": UNIT, "ms_per_step": float(t_pg.item()) / args.steps,
+                "h2d_bytes_per_step": int(G0) * N * 8 * world, "d2h_bytes_per_step": int(G0) * N * 8,
+                "note": "pageable (not pinned) float64 count matrix in, float64 matrix out, host wall clock: the buffers an R caller has"}
+    del pg_counts, pg_adj
+    c2_pair = None
+    if rank == 0 and world == 1 and not args.no_cpu:
+        c2_pair = measured_pair(pkg, L, "C2")
 
     if rank == 0:
         units = float(G0) * N * args.steps
@@ -284,7 +331,14 @@ def run_native(args):
         total_k = sum(v[0] for v in prof.values()) or 1.0
         line["kernels"] = {k: {"ms_per_step": round(v[0] / args.steps, 4), "launches_per_step": v[1] / args.steps,
                                "share": round(v[0] / total_k, 4)} for k, v in sorted(prof.items(), key=lambda kv: -kv[1][0])}
-        line["roofline"] = roofline(L, prof, G, N, nb, world, args.steps, case)
+        ra = rooflines(L, prof, G, int(G0), N, nb, world, args.steps, diag)
+        line["roofline"] = ra[0] if ra else None
+        line["roofline_all"] = ra
+        line["mc_tiles"] = {"visited_per_step": diag["mc_tiles_done"] / args.steps, "all_per_step": diag["mc_tiles_all"] / args.steps,
+                            "chebyshev_terms": diag["mc_terms"], "tail_estimate": diag["mc_tail"]}
+        line["e2e_pageable"] = pageable
+        if c2_pair is not None:
+            line["c2_pair"] = c2_pair
         if world == 1 and not args.no_cpu:
             threads = cpu_threads()                       # explicit num_threads(): torchrun sets OMP_NUM_THREADS=1
             r = cpu_sample(case, d, args.cpu_genes or auto_cpu_rows(case), threads)
@@ -300,74 +354,126 @@ def run_native(args):
         dist.destroy_process_group()
 
 
-def ncu_traffic(name, G, N, world):
-    """dram__bytes_read.sum + dram__bytes_write.sum per launch of this kernel, from the committed `ncu --set full` capture
-    (profiles/ncu_traffic.json, written from the capture's raw page).  The capture is of the 1-GPU C5 workload, so the
-    figure is only reported for that shape; otherwise null."""
-    if world != 1 or (G, N) != (60000, 1000):
-        return None
+def ncu_table():
+    """Per-launch figures taken from the committed `ncu --set full` captures of the 1-GPU C5 workload
+    (profiles/ncu_kernels.json, written by tools/ncu_kernels.py from the captures' raw pages): DRAM bytes and executed
+    FP64 operations (DFMA = 2 flop, DADD / DMUL = 1) of one launch."""
     try:
-        tab = json.load(open(os.path.join(ROOT, "profiles", "ncu_traffic.json")))
+        return json.load(open(os.path.join(ROOT, "profiles", "ncu_kernels.json")))
     except (OSError, ValueError):
-        return None
+        return {}
+
+
+def ncu_entry(tab, name):
     for k, v in tab.items():
         if name.startswith(k):
-            return v["dram_bytes_per_launch"]
+            return v
     return None
 
 
-def roofline(L, prof, G, N, nb, world, steps, case):
-    """Roofline of the dominant kernel (largest share of device time in the timed region)."""
-    r = _roofline(L, prof, G, N, nb, world, steps, case)
-    r["traffic"] = ncu_traffic(r["kernel"], int(case.counts.shape[0]), N, world)
-    return r
+def rooflines(L, prof, G, G0, N, nb, world, steps, diag):
+    """One roofline entry per kernel with at least 2 % of the step's device time (north_star: every kernel against its
+    roofline).  The dominant kernel's entry is also the line's `roofline` object.
 
-
-def _roofline(L, prof, G, N, nb, world, steps, case):
+    bound / algorithmic work per launch:
+      k_mc_gemm        FP64 tensor pipe; flops = 2 * KTP * 64 * 128 per (target tile, source tile) pair actually visited
+                       (the screened lists; `pairs_equiv` also gives the figure for all G^2 pairs, which the round-1 kernel
+                       executed and the reference evaluates)
+      k_scr_mma        bf16 tensor cores (tcgen05); flops = 2 * 128 * 256 * 16 * 3 per chunk of 16 columns and tile pair
+      k_apl_lanes, k_glm_fit_lanes, k_match_quantiles_warp, k_mcg_prep_*
+                       FP64 pipe; executed FP64 flops per launch counted by ncu on the committed capture of the same
+                       workload (null when the shape differs from the capture)
+      streaming kernels HBM; algorithmic bytes"""
     peaks = {}
     try:
         peaks = json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json")))
     except (OSError, ValueError):
         pass
     hbm = float(peaks.get("hbm_gbs", 6650.0))
-    hbm_src = "MEASURED_PEAKS.json hbm_gbs" if "hbm_gbs" in peaks else "fallback 6650 GB/s (B200_PROFILING.md)"
-    name = max(prof, key=lambda k: prof[k][0])
-    ms, n = prof[name]
-    avg_s = ms / n * 1e-3
-    if name.startswith("k_mc_gemm"):
-        # FP64 tensor-core contraction: log LH = P Q^T with inner length KT = n_b + Kc + 4 + 1 (DESIGN.md section 4);
-        # algorithmic flops of one launch (one batch, this rank's targets x all sources) = 2 * KT * G_targets * G.
-        n_b = float(N) / len(nb)
-        kc = L.get_diag("mc_terms")
-        kt = n_b + kc + 4 + 1
-        flops = 2.0 * kt * (float(G) / world) * G
-        peak = L.fp64_mma_peak_tflops()
-        ach = flops / avg_s / 1e12
-        return {"kernel": name, "bound": "tensor", "achieved": ach, "peak": peak, "unit": "TFLOP/s", "frac": ach / peak,
-                "traffic": None, "avg_launch_ms": ms / n, "launches": n,
-                "note": "FP64 tensor pipe (mma.sync m8n8k4 f64 = DMMA; tcgen05 has no FP64 path). peak = DMMA microbenchmark "
-                        "measured in this run (cbs_fp64_mma_peak; MEASURED_PEAKS.json has no FP64 figure; DMMA and DFMA share "
-                        "the FP64 units on B200, so the epilogue's exp() work comes out of the same budget); inner length "
-                        "KT = %d (n_b %d + %d Chebyshev terms + 5); %.3g gene pairs/s = %.3g NB terms/s"
-                        % (kt, n_b, kc, float(G) / world * G / avg_s, float(G) / world * G * n_b / avg_s)}
-    if name.startswith("k_mc"):
-        fp64 = L.fp64_peak_tflops()
-        terms = float(G) * (G - 1.0) * N / world / len(nb)       # per launch: one batch, this rank's target shard
-        ach = terms * MC_FLOP_PER_TERM / avg_s / 1e12
-        return {"kernel": name, "bound": "fp64", "achieved": ach, "peak": fp64, "unit": "TFLOP/s", "frac": ach / fp64,
-                "traffic": None, "avg_launch_ms": ms / n, "launches": n,
-                "note": "FP64-pipe bound (lgamma per NB term, no tensor-core FP64 path on sm_100a beats the DFMA pipe for it); "
-                        "peak = DFMA microbenchmark measured in this run (cbs_fp64_peak); %.0f flop per NB term; "
-                        "%.3g NB terms/s" % (MC_FLOP_PER_TERM, terms / avg_s)}
-    elems = float(G) * N / world if name.startswith("k_match") else float(G) * N / world
-    ach = elems * MQ_BYTES_PER_ELEM / avg_s / 1e9
-    return {"kernel": name, "bound": "hbm", "achieved": ach, "peak": hbm, "unit": "GB/s", "frac": ach / hbm, "traffic": None,
-            "avg_launch_ms": ms / n, "launches": n, "note": "peak = %s; %.0f B per element" % (hbm_src, MQ_BYTES_PER_ELEM)}
+    bf16 = float(peaks.get("bf16_tflops", 1590.0))
+    src = "MEASURED_PEAKS.json" if peaks else "fallback (B200_PROFILING.md)"
+    fp64 = L.fp64_peak_tflops()
+    dmma = L.fp64_mma_peak_tflops()
+    tab = ncu_table()
+    captured_shape = world == 1 and (G0, N) == (60000, 1000)
+    total_ms = sum(v[0] for v in prof.values()) or 1.0
+    n_b = float(N) / len(nb)
+    kc = diag["mc_terms"]
+    kt = n_b + kc + 4 + 1
+    ktp = (int(kt) + 7) // 8 * 8
+    tiles_done, tiles_all = diag["mc_tiles_done"], diag["mc_tiles_all"]
+    out = []
+    for name, (ms, n) in sorted(prof.items(), key=lambda kv: -kv[1][0]):
+        if ms / total_ms < 0.02:
+            continue
+        avg_s = ms / n * 1e-3
+        e = {"kernel": name, "share": round(ms / total_ms, 4), "avg_launch_ms": ms / n, "launches": n, "traffic": None}
+        cap = ncu_entry(tab, name) if captured_shape else None
+        if cap:
+            e["traffic"] = cap.get("dram_bytes_per_launch")
+        if name.startswith("k_mc_gemm"):
+            flops = 2.0 * ktp * 64 * 128 * tiles_done / max(n, 1)          # executed: rank 0's visited tile pairs per launch
+            ach = flops / avg_s / 1e12
+            e.update(bound="tensor", achieved=ach, peak=dmma, unit="TFLOP/s", frac=ach / dmma,
+                     note="FP64 tensor pipe (mma.sync m8n8k4 f64 = DMMA; tcgen05 has no FP64 kind). peak = DMMA microbenchmark with "
+                          "shared-memory operands measured in this run (cbs_fp64_mma_peak; MEASURED_PEAKS.json has no FP64 figure). "
+                          "inner length KTP = %d (n_b %d + %d Chebyshev terms + 5, padded to 8); source tiles visited %d of %d "
+                          "(screened band); pairs_equiv = all G^2 pairs / time" % (ktp, n_b, kc, tiles_done, tiles_all),
+                     pairs_equiv_per_s=float(G) / world * G / avg_s)
+        elif name.startswith("k_scr_mma"):
+            chunks = (int(n_b) + 15) // 16 + (int(kc) - 1 + 4 + 15) // 16
+            rows = (G + 127) // 128 * 128
+            flops = 2.0 * 128 * 256 * 16 * 3 * chunks * (rows / 128.0 / world) * ((rows / 128 + 1) // 2)
+            ach = flops / avg_s / 1e12
+            e.update(bound="tensor", achieved=ach, peak=bf16, unit="TFLOP/s", frac=ach / bf16,
+                     note="bf16 tcgen05.mma 128x256x16, 3 MMAs (hi*hi, hi*lo, lo*hi) per 16-column chunk, %d chunks; peak = %s "
+                          "bf16_tflops (cuBLAS burst)" % (chunks, src))
+        elif cap and cap.get("fp64_flop_per_launch"):
+            ach = cap["fp64_flop_per_launch"] / avg_s / 1e12
+            e.update(bound="fp64", achieved=ach, peak=fp64, unit="TFLOP/s", frac=ach / fp64,
+                     note="FP64 pipe: executed DFMA (2 flop) + DADD + DMUL per launch counted by ncu on the committed capture of this "
+                          "workload (%s); peak = DFMA microbenchmark measured in this run (cbs_fp64_peak)" % cap.get("source", "profiles/"))
+        elif name.startswith(("k_keep_mask", "k_compact_colsum", "k_counts_to_f64", "k_rowsum_sel", "k_mcg_sort_key", "k_scr_convert")):
+            per = {"k_keep_mask": 4.0 * G0 * N, "k_compact_colsum": 8.0 * G * N, "k_counts_to_f64": 12.0 * G0 * N,
+                   "k_rowsum_sel": 4.0 * G * N, "k_mcg_sort_key": 8.0 * G * n_b,
+                   "k_scr_convert": 8.0 * ktp * G + 2.0 * 160 * G}[name.split("<")[0]]
+            ach = per / avg_s / 1e9
+            e.update(bound="hbm", achieved=ach, peak=hbm, unit="GB/s", frac=ach / hbm, note="algorithmic bytes per launch / time; peak = %s hbm_gbs" % src)
+        else:
+            e.update(bound="fp64", achieved=None, peak=fp64, unit="TFLOP/s", frac=None,
+                     note="no committed ncu capture for this shape: executed-flop count unavailable")
+        out.append(e)
+    return out
+
+
+def run_inproc(args):
+    """One process, one cbs_combat_seq call sharded over args.inproc devices by the library's own host threads."""
+    import torch
+    pkg = graft.load_package()
+    L = pkg._lib
+    case, d = make_case(pkg, args.workload, args.genes)
+    G0, N = case.counts.shape
+    h_counts = torch.empty((N, G0), dtype=torch.int32, pin_memory=True)
+    h_counts.numpy()[:] = np.ascontiguousarray(case.counts.T)
+    h_adj = torch.empty((N, G0), dtype=torch.float64, pin_memory=True)
+    opts = dict(shrink=case.shrink, shrink_disp=case.shrink_disp, n_gpus=args.inproc)
+    for _ in range(max(args.warmup, 1)):
+        res = L.combat_seq_into(h_counts.numpy().T, d.batch_idx, d.mod, h_adj.numpy().T, **opts)
+    t = time.perf_counter()
+    for _ in range(args.steps):
+        res = L.combat_seq_into(h_counts.numpy().T, d.batch_idx, d.mod, h_adj.numpy().T, **opts)
+    ms = (time.perf_counter() - t) * 1e3 / args.steps
+    print(json.dumps({"metric": METRIC, "mode": "single process, cbs_input.n_gpus", "n_gpus": args.inproc, "value": G0 * N / (ms * 1e-3),
+                      "unit": UNIT, "ms_per_step": ms, "steps": args.steps, "warmup": args.warmup, "config": describe(case, d),
+                      "stage_ms_rank0": {k: round(v, 3) for k, v in res["stage_ms"].items()},
+                      "checksum": float(np.asarray(h_adj.numpy()[:, :: max(1, G0 // 997)]).sum())}))
 
 
 if __name__ == "__main__":
     a = parse_args()
-    if a.impl == "reference":
+    if a.inproc:
+        run_inproc(a)
+    elif a.impl == "reference":
         run_reference(a)
     else:
         run_native(a)

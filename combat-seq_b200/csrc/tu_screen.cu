@@ -10,10 +10,14 @@
 //                                                          accumulation), and, term by term,
 //   sum_k |P_ik| |Q_jk| <= |x_i| |A_j|  (Cauchy-Schwarz over the samples; the two vectors are close to parallel)
 //                        + sum_k |C_ik|  (the Chebyshev polynomials are bounded by 1)
-//                        + (#counts of i below 4) * max_v |lgamma(v + r_j) - lgamma(v + 1)|,
+//                        + (#counts of i below 4) * max_v |lgamma(v + r_j) - lgamma(v + 1)|
+//                        + 2e-6 |c_j|   (c_j enters as three bf16 pieces, exact to 2^-24; the rest is its share of the
+//                                        fp32 accumulation error),
 //
-// i.e. three rank-one terms that the epilogue forms from one float4 per row and one per column, and reduces every
-// 128 x 128 tile to per-row maxima of the upper bound S + d and of the lower bound S - d.  k_mcg_list_screened (mc_gemm.cuh)
+// i.e. three rank-one terms; their column factors are replaced by their maxima over the 128 sources of a tile, so the bound
+// is one number d per (row, tile), and every 128 x 128 tile reduces to the row maxima m of S itself: upper bound m + d, lower
+// bound m - d.  The per-source constant c_j rides in the contraction as three bf16 columns (hi, mid, lo: 24 bits) against ones,
+// so the epilogue is a pure row maximum of the accumulator.  k_mcg_list_screened (mc_gemm.cuh)
 // keeps a source tile for a target tile iff an upper bound reaches a row's best lower bound - 40; the FP64 contraction then
 // visits only those tiles.  tcgen05 has no FP64 kind, so the weights themselves stay on the DMMA path; what runs here is 30
 // tcgen05.mma (128 x 256 x 16) per 128 x 256 pairs, a few per cent of the FP64 work it removes.
@@ -44,7 +48,6 @@ constexpr int SCR_SMEM_BLOCKS = 13;         // 16 KB blocks that fit shared memo
 constexpr int SCR_EPI_WARPS = 8;            // two warps per TMEM lane quarter, one per source tile of the pair
 constexpr int SCR_THREADS = 64 + 32 * SCR_EPI_WARPS;     // warp 0 producer, warp 1 MMA issuer, warps 2-9 epilogue
 constexpr float SCR_EPS = 3.1e-5f;          // error of S relative to sum |P||Q| (see above), incl. the fp32 rounding of the bound
-constexpr float SCR_EPS_C = 2.5e-7f;        // fp32 rounding of the per-source constant c_j added in the epilogue
 static_assert(SCR_BM == MCG_TILE && SCR_BN == 2 * MCG_TILE, "screening tiles are the contraction's source tiles");
 
 struct ScrShape {
@@ -61,31 +64,50 @@ struct ScrShape {
 // Element (row r, k-tile kt, column c of the k-tile) lives in block [kt][r / 128] (16 KB each) at byte (r % 128) * 128 +
 // ((c / 8) ^ (r % 8)) * 16 + (c % 8) * 2: the 128-byte swizzle the UMMA descriptors below declare.  One thread writes one
 // 16-byte chunk (8 columns = half a sub-block).  P is only built for the owned blocks, the other blocks are never read.
-// vec[r]: the row's terms of the error bound; targets (x = SCR_EPS |x_i|, y = SCR_EPS sum |C_ik|, z = SCR_EPS #small counts),
-// sources (x = c_j, y = |A_j|, z = max_v |lg_jv|, w = SCR_EPS_C |c_j|).
+// Series part of a row: MC columns n+1 .. KT-2 (Chebyshev orders >= 1, one-hot), then three columns for c_j: ones in P, the
+// bf16 pieces (hi, mid, lo) of c_j in Q, all in the hi sub-block (their lo sub-block entries are zero).
+// pvec[r] (targets): SCR_EPS (|x_i|, sum |C_ik|, #small counts).  qtile[J] (source tiles): maxima over the tile's rows of
+// |A_j|, max_v |lg_jv| and |c_j|, kept as the bit patterns of non-negative floats (atomicMax on ints; zero on entry).
 __global__ void __launch_bounds__(256)
 k_scr_convert(const double* __restrict__ X, McgShape sh, ScrShape ss, int is_q, McgOwn own, long n_rows,
-              __nv_bfloat16* __restrict__ out, float4* __restrict__ vec) {
+              __nv_bfloat16* __restrict__ out, float4* __restrict__ pvec, int* __restrict__ qtile) {
     const long t = (long)blockIdx.x * blockDim.x + threadIdx.x;
     const int chunks_per_row = ss.nk * 8;
     const long lr = t / chunks_per_row;
     const int ch = (int)(t - lr * chunks_per_row);
     if (lr >= n_rows) return;
     const long r = is_q ? lr : own.row(lr);
+    const bool pad_row = r >= sh.rows;                            // the zero block behind Q (read by the last tile pair)
     const int kt = ch >> 3, c8 = ch & 7, sb = c8 >> 1, half = c8 & 1;
     const int c = 2 * kt + (sb >> 1), lo_part = sb & 1;           // chunk, hi / lo
-    int col0, lim;                                                // first MC column of the 8, exclusive end of the part
-    if (c < ss.nxc) { col0 = c * 16 + half * 8; lim = ss.n; }
-    else { col0 = ss.n + 1 + (c - ss.nxc) * 16 + half * 8; lim = c < ss.nxc + ss.ncc ? sh.KT - 1 : 0; }   // (order-0 term at n, c_j at KT-1 left out)
+    const int ser0 = ss.n + 1, ser1 = sh.KT - 1;                  // series part in MC columns: [ser0, ser1), then 3 columns of c_j
     __align__(16) __nv_bfloat16 v[8];
 #pragma unroll
     for (int e = 0; e < 8; ++e) {
         float f = 0.f;
-        const int k = col0 + e;
-        if (k < lim && r < sh.rows) {
-            const double x = X[mcg_index(sh.rows, r, k)];
-            const float h = __bfloat162float(__double2bfloat16(x));
-            f = lo_part ? (float)(x - (double)h) : h;
+        if (!pad_row) {
+            int k = -1, cpart = -1;                               // MC column to convert, or piece of c_j
+            if (c < ss.nxc) { const int kk = c * 16 + half * 8 + e; if (kk < ss.n) k = kk; }
+            else {
+                const int kk = ser0 + (c - ss.nxc) * 16 + half * 8 + e;
+                if (kk < ser1) k = kk; else if (kk < ser1 + 3) cpart = kk - ser1;
+            }
+            if (k >= 0) {
+                const double x = X[mcg_index(sh.rows, r, k)];
+                const float h = __bfloat162float(__double2bfloat16(x));
+                f = lo_part ? (float)(x - (double)h) : h;
+            } else if (cpart >= 0 && !lo_part) {
+                if (!is_q) f = 1.f;
+                else {
+                    const double x = X[mcg_index(sh.rows, r, sh.KT - 1)];
+                    const float h = __bfloat162float(__double2bfloat16(x));
+                    const float m = __bfloat162float(__double2bfloat16(x - (double)h));
+                    f = cpart == 0 ? h : cpart == 1 ? m : (float)(x - (double)h - (double)m);
+                }
+            }
+        } else if (is_q && !lo_part && c >= ss.nxc) {             // padding sources: c_j = -1e30, never kept
+            const int kk = ser0 + (c - ss.nxc) * 16 + half * 8 + e;
+            if (kk == ser1) f = -1e30f;
         }
         v[e] = __float2bfloat16_rn(f);
     }
@@ -93,19 +115,22 @@ k_scr_convert(const double* __restrict__ X, McgShape sh, ScrShape ss, int is_q, 
     const int rr = (int)(r % SCR_BM);
     char* dst = reinterpret_cast<char*>(out) + blk * SCR_TILE_BYTES + rr * 128 + ((c8 ^ (rr & 7)) << 4);
     *reinterpret_cast<uint4*>(dst) = *reinterpret_cast<const uint4*>(v);
-    if (ch == 0) {
-        if (r >= sh.rows) { vec[r] = make_float4(-1e30f, 0.f, 0.f, 0.f); return; }          // the padding block of Q: impossible sources
-        double s2 = 0, s1 = 0, mx = 0;
+    if (ch == 0 && !pad_row) {
+        double s2 = 0;
         for (int k = 0; k < ss.n; ++k) { const double x = X[mcg_index(sh.rows, r, k)]; s2 += x * x; }
         if (!is_q) {
+            double s1 = 0, hot = 0;
             for (int k = ss.n + 1; k < ss.n + sh.Kc; ++k) s1 += fabs(X[mcg_index(sh.rows, r, k)]);
-            double hot = 0;
             for (int k = ss.n + sh.Kc; k < sh.KT - 1; ++k) hot += X[mcg_index(sh.rows, r, k)];
-            vec[r] = make_float4(SCR_EPS * (float)sqrt(s2), SCR_EPS * (float)s1, SCR_EPS * (float)hot, 0.f);
+            pvec[r] = make_float4(SCR_EPS * (float)sqrt(s2), SCR_EPS * (float)s1, SCR_EPS * (float)hot, 0.f);
         } else {
+            double mx = 0;
             for (int k = ss.n + sh.Kc; k < sh.KT - 1; ++k) mx = fmax(mx, fabs(X[mcg_index(sh.rows, r, k)]));
-            const float cj = (float)X[mcg_index(sh.rows, r, sh.KT - 1)];
-            vec[r] = make_float4(cj, (float)sqrt(s2), (float)mx, SCR_EPS_C * fabsf(cj));
+            const float cj = fabsf((float)X[mcg_index(sh.rows, r, sh.KT - 1)]);
+            int* q3 = qtile + 4 * (r / MCG_TILE);
+            atomicMax(q3 + 0, __float_as_int(fminf((float)sqrt(s2) * 1.000001f, 3e38f)));
+            atomicMax(q3 + 1, __float_as_int((float)mx * 1.000001f));
+            if (cj < 1e29f) atomicMax(q3 + 2, __float_as_int(cj));             // (c_j = -1e30 marks an impossible source)
         }
     }
 }
@@ -175,11 +200,10 @@ __host__ __device__ constexpr uint32_t scr_idesc() {
 }
 
 struct ScrSmem {
-    // [SCR_SMEM_BLOCKS x 16 KB: the resident A k-tiles, then the B ring (32 KB stages)] [column vectors, double buffered]
-    // [barriers] [tmem base]; the tiles need 1024-byte alignment
+    // [SCR_SMEM_BLOCKS x 16 KB: the resident A k-tiles, then the B ring (32 KB stages)] [barriers] [tmem base]; the tiles
+    // need 1024-byte alignment
     static constexpr size_t tile_bytes = (size_t)SCR_SMEM_BLOCKS * SCR_TILE_BYTES;
-    static constexpr size_t qv_off = tile_bytes;
-    static constexpr size_t bar_off = qv_off + 2 * SCR_BN * sizeof(float4);
+    static constexpr size_t bar_off = tile_bytes;
     static constexpr int max_stages = SCR_SMEM_BLOCKS / 2;
     static constexpr size_t total = bar_off + (5 + 2 * max_stages + 1) * sizeof(uint64_t) + 16 + 1024 /*alignment slack*/;
 };
@@ -188,14 +212,13 @@ static_assert(ScrSmem::total <= 227 * 1024, "screening kernel: shared memory");
 // items[w] = (target block, first source tile pair, number of pairs).  hi / lo are [NJ][rows], NJ = 128-row source tiles.
 __global__ void __launch_bounds__(SCR_THREADS, 1)
 k_scr_mma(const __nv_bfloat16* __restrict__ Pt, const __nv_bfloat16* __restrict__ Qt, const float4* __restrict__ pvec,
-          const float4* __restrict__ qvec, ScrShape ss, const int3* __restrict__ items, float* __restrict__ hi,
+          const float4* __restrict__ qtile, ScrShape ss, const int3* __restrict__ items, float* __restrict__ hi,
           float* __restrict__ lo) {
     extern __shared__ unsigned char scr_raw[];
     unsigned char* smem = reinterpret_cast<unsigned char*>((reinterpret_cast<uintptr_t>(scr_raw) + 1023) & ~(uintptr_t)1023);
     const int NST = ss.stages;
     unsigned char* a_s = smem;
     unsigned char* b_s = smem + (size_t)ss.nk * SCR_TILE_BYTES;
-    float4* qv_s = reinterpret_cast<float4*>(smem + ScrSmem::qv_off);                // [2][256]
     uint64_t* bars = reinterpret_cast<uint64_t*>(smem + ScrSmem::bar_off);
     uint64_t* a_full = bars;                    // 1
     uint64_t* acc_full = bars + 1;              // 2
@@ -279,47 +302,43 @@ k_scr_mma(const __nv_bfloat16* __restrict__ Pt, const __nv_bfloat16* __restrict_
         }
     } else {
         // ===== epilogue: warps 2..9; warp w may touch TMEM lanes 32 (w % 4) .. +31; the two warps of a lane quarter take one
-        // source tile (128 columns) of the pair each.  The fold is latency-bound (max chains), so each warp keeps four
-        // independent running maxima per bound; the per-source terms come in as one 16-byte shared-memory load per column.
+        // source tile (128 columns) of the pair each: a row maximum of the accumulator (four independent chains), plus the
+        // (row, tile) error bound.
         const int q = warp & 3, half = (warp - 2) >> 2;
         const int row = q * 32 + lane;                            // row of the target block = TMEM lane
         const long grow = iblk * SCR_BM + row;
-        const int et = threadIdx.x - 64;                          // 0 .. 255
         const float4 pv = pvec[grow];                             // SCR_EPS (|x_i|, sum |C_ik|, #small counts)
         constexpr int HC = SCR_BN / 2;                            // columns per warp = one source tile
         for (int jj = 0; jj < nj; ++jj) {
             const int as = jj & 1;
             const long J = 2 * (long)(j0 + jj) + half;            // source tile of this warp
-            qv_s[as * SCR_BN + et] = qvec[2 * (long)(j0 + jj) * MCG_TILE + et];
-            asm volatile("bar.sync 1, %0;" ::"n"(32 * SCR_EPI_WARPS) : "memory");        // the epilogue warps
+            const float4 qt = qtile[min(J, ss.nrb)];              // max |A_j|, max |lg_jv|, max |c_j| over the tile
             sbar_wait(&acc_full[as], (uint32_t)(jj >> 1) & 1u);
             tc_fence_after();
             const uint32_t t_s = tmem + ((uint32_t)(q * 32) << 16) + (uint32_t)as * 256u + (uint32_t)(half * HC);
             const bool diag = J == iblk;
-            float mh[4] = {-INFINITY, -INFINITY, -INFINITY, -INFINITY}, ml[4] = {-INFINITY, -INFINITY, -INFINITY, -INFINITY};
+            float m4[4] = {-INFINITY, -INFINITY, -INFINITY, -INFINITY};
 #pragma unroll 1
             for (int c0 = 0; c0 < HC; c0 += 32) {
                 float s[32];
                 tc_ld32(t_s + (uint32_t)c0, s);
                 tc_ld_wait();
-                const float4* qp = qv_s + as * SCR_BN + half * HC + c0;
+                if (diag && (row >> 5) == (c0 >> 5)) {             // j == i is not a source (mu[-i,], helper_seq.R:11-14)
 #pragma unroll
-                for (int c = 0; c < 32; ++c) {
-                    const float4 qv = qp[c];                      // (c_j, |A_j|, max |lg_jv|, SCR_EPS_C |c_j|)
-                    const float v = s[c] + qv.x;
-                    const float e = fmaf(pv.x, qv.y, fmaf(pv.z, qv.z, pv.y + qv.w));
-                    mh[c & 3] = fmaxf(mh[c & 3], v + e);
-                    float l = v - e;
-                    if (diag && c0 + c == row) l = -INFINITY;     // j == i is not a source (mu[-i,], helper_seq.R:11-14)
-                    ml[c & 3] = fmaxf(ml[c & 3], l);
+                    for (int c = 0; c < 32; ++c) m4[c & 3] = fmaxf(m4[c & 3], c == (row & 31) ? -INFINITY : s[c]);
+                } else {
+#pragma unroll
+                    for (int c = 0; c < 32; ++c) m4[c & 3] = fmaxf(m4[c & 3], s[c]);
                 }
             }
             tc_fence_before();
             __syncwarp();
             if (lane == 0) sbar_arrive(&acc_empty[as]);
             if (J < ss.nrb) {
-                __stcs(&hi[J * ss.rows + grow], fmaxf(fmaxf(mh[0], mh[1]), fmaxf(mh[2], mh[3])));      // streamed: read once
-                __stcs(&lo[J * ss.rows + grow], fmaxf(fmaxf(ml[0], ml[1]), fmaxf(ml[2], ml[3])));
+                const float m = fmaxf(fmaxf(m4[0], m4[1]), fmaxf(m4[2], m4[3]));
+                const float e = fmaf(pv.x, qt.x, fmaf(pv.z, qt.y, fmaf(2e-6f, qt.z, pv.y))) + 1e-6f * fabsf(m);
+                __stcs(&hi[J * ss.rows + grow], m + e);          // streamed: read once by k_mcg_list_screened
+                __stcs(&lo[J * ss.rows + grow], m - e);
             }
         }
     }
@@ -350,7 +369,7 @@ bool mc_screen(const double* P, const double* Q, const McgShape& sh, McgOwn own,
     ss.n = sh.n;
     ss.KS = sh.KT - 2;
     ss.nxc = (sh.n + 15) / 16;
-    ss.ncc = (ss.KS - sh.n + 15) / 16;
+    ss.ncc = (ss.KS - sh.n + 3 + 15) / 16;                       // + the three columns of c_j
     ss.nk = (ss.nxc + ss.ncc + 1) / 2;
     ss.rows = sh.rows;
     ss.nrb = sh.rows / SCR_BM;
@@ -366,11 +385,12 @@ bool mc_screen(const double* P, const double* Q, const McgShape& sh, McgOwn own,
     const size_t op_bytes = (size_t)ss.nk * (ss.nrb + 1) * SCR_TILE_BYTES;
     __nv_bfloat16* Pt = (__nv_bfloat16*)g_dev.get("mcs_Pt" + sfx, op_bytes);
     __nv_bfloat16* Qt = (__nv_bfloat16*)g_dev.get("mcs_Qt" + sfx, op_bytes);
-    float4* pvec = (float4*)g_dev.get("mcs_pvec" + sfx, (size_t)(sh.rows + SCR_BM) * sizeof(float4));
-    float4* qvec = (float4*)g_dev.get("mcs_qvec" + sfx, (size_t)(sh.rows + SCR_BM) * sizeof(float4));
+    float4* pvec = (float4*)g_dev.get("mcs_pvec" + sfx, (size_t)sh.rows * sizeof(float4));
+    int* qtile = g_dev.get<int>("mcs_qtile" + sfx, (size_t)4 * (ss.nrb + 1));
+    CBS_CUDA(cudaMemsetAsync(qtile, 0, (size_t)4 * (ss.nrb + 1) * sizeof(int), st));
     const int cpr = ss.nk * 8;
-    CBS_LAUNCH(k_scr_convert, grid1(own_blocks * SCR_BM * cpr, 256), 256, 0, st, P, sh, ss, 0, own, own_blocks * SCR_BM, Pt, pvec);
-    CBS_LAUNCH(k_scr_convert, grid1((sh.rows + SCR_BM) * cpr, 256), 256, 0, st, Q, sh, ss, 1, own, sh.rows + SCR_BM, Qt, qvec);
+    CBS_LAUNCH(k_scr_convert, grid1(own_blocks * SCR_BM * cpr, 256), 256, 0, st, P, sh, ss, 0, own, own_blocks * SCR_BM, Pt, pvec, (int*)nullptr);
+    CBS_LAUNCH(k_scr_convert, grid1((sh.rows + SCR_BM) * cpr, 256), 256, 0, st, Q, sh, ss, 1, own, sh.rows + SCR_BM, Qt, (float4*)nullptr, qtile);
     int sms = 148;
     cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
     // about 8 waves of CTAs and at least 4 ranges; every CTA re-loads its 128-row A operand once, so ranges should not be
@@ -379,7 +399,7 @@ bool mc_screen(const double* P, const double* Q, const McgShape& sh, McgOwn own,
     int3* items = (int3*)g_dev.get<int>("mcs_items" + sfx, (size_t)3 * own_blocks * nchunk + 3);
     CBS_LAUNCH(k_scr_items, grid1(own_blocks, 128), 128, 0, st, own, sh.rows, ss.NJ2, nchunk, items);
     t_ctx->set_func_attr((const void*)k_scr_mma, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)ScrSmem::total);
-    CBS_LAUNCH(k_scr_mma, dim3((unsigned)(own_blocks * nchunk)), SCR_THREADS, ScrSmem::total, st, Pt, Qt, pvec, qvec, ss, items, hi, lo);
+    CBS_LAUNCH(k_scr_mma, dim3((unsigned)(own_blocks * nchunk)), SCR_THREADS, ScrSmem::total, st, Pt, Qt, pvec, (const float4*)qtile, ss, items, hi, lo);
     return true;
 }
 
