@@ -161,7 +161,8 @@ k_apl_lanes(const int32_t* __restrict__ cnt, long G, long g0, long g1, const dou
                 for (int it = 0; it < 50; ++it) {
                     const double ec = exp(cur);
                     double dl = 0, info = 0;
-                    for (int t = t0 + ln; t < t1; t += APLL_LANES) {
+#pragma unroll 4
+                    for (int t = t0 + ln; t < t1; t += APLL_LANES) {         // (independent reciprocal chains: the loop is latency-bound)
                         const double mu = ec * lib_s[t], inv = rcp_pos(1 + mu * phi);
                         dl += (y[t] - mu) * inv;
                         info += mu * inv;
@@ -175,6 +176,7 @@ k_apl_lanes(const int32_t* __restrict__ cnt, long G, long g0, long g1, const dou
             const double cb = fmax(cur, -1e8);                   // mglmOneWay: pmax(beta, -1e8)
             const double ecell = exp(cb);
             double w = 0;
+#pragma unroll 2
             for (int t = t0 + ln; t < t1; t += APLL_LANES) {
                 const double mu = ecell * lib_s[t];
                 if (mu == 0) continue;
