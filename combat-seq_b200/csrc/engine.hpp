@@ -71,7 +71,8 @@ struct AplJob { int design; double phi; };
 // tu_apl.cu
 void launch_apl(const int32_t* cnt, long G, long g0, long g1, const double* logoff, const DesignDev* designs,
                 const unsigned char* sel, const double* phi_gene, const std::vector<AplJob>& jobs, double* d_apl, cudaStream_t st,
-                const std::vector<DesignDev>* h_designs = nullptr);     // host copies of `designs` (enables the lane-group kernel)
+                const std::vector<DesignDev>* h_designs = nullptr,      // host copies of `designs` (enables the lane-group kernel)
+                double* d_warm = nullptr);                               // [design][gene][4] Newton warm starts carried between launches
 void run_common_disp(const int32_t* cnt, long G, long g0, long g1, const double* logoff, const DesignSet& ds,
                      const unsigned char* sel, cbs_comm* comm, cudaStream_t st, std::vector<double>& common, int* n_steps);
 void run_tagwise_disp(const int32_t* cnt, long G, long g0, long g1, const double* logoff, const DesignSet& ds,

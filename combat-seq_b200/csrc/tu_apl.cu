@@ -100,7 +100,8 @@ template <int APLL_LANES>
 __global__ void __launch_bounds__(128)
 k_apl_lanes(const int32_t* __restrict__ cnt, long G, long g0, long g1, const double* __restrict__ logoff,
             const DesignDev* __restrict__ designs, const unsigned char* __restrict__ sel, AplLaunch L, AplGroups GR,
-            double* __restrict__ apl, const double* __restrict__ lgfact, const double* __restrict__ lgr) {
+            double* __restrict__ apl, const double* __restrict__ lgfact, const double* __restrict__ lgr,
+            double* __restrict__ warm) {
     constexpr int APLL_GENES = 128 / APLL_LANES;
     extern __shared__ double apl_sm[];
     const int e0 = GR.start[blockIdx.y], e1 = GR.start[blockIdx.y + 1];
@@ -145,6 +146,16 @@ k_apl_lanes(const int32_t* __restrict__ cnt, long G, long g0, long g1, const dou
     }
     sum_lgy1 = lane_sum<APLL_LANES>(sum_lgy1, gm);
 
+    // Newton start of every cell: glm_one_group's own start value for the first evaluation of a gene, afterwards the
+    // coefficient the previous evaluation converged to (the previous grid point, or the previous Brent abscissa of the batch
+    // through `warm`, [design][gene][cell]).  The iteration still runs to |step| < 1e-10, so it ends at the same root
+    // (the likelihood is evaluated at a stationary point: a 1e-10 difference in the coefficient moves it by 1e-20), in 2-3
+    // steps instead of 6-9.
+    double cbw[APLL_PM];
+    double* wg = warm ? warm + ((long)di * G + g) * APLL_PM : nullptr;
+#pragma unroll
+    for (int l = 0; l < APLL_PM; ++l) cbw[l] = (wg && l < p) ? wg[l] : NAN;
+
     for (int e = e0; e < e1; ++e) {
         const double phi = L.phi[e];
         const double* lgr_e = lgr ? lgr + (long)e * LGFACT_N : nullptr;
@@ -158,6 +169,7 @@ k_apl_lanes(const int32_t* __restrict__ cnt, long G, long g0, long g1, const dou
             // edgeR glm_one_group: Newton on the cell's coefficient, maxit 50, |step| < 1e-10
             double cur = start0[l];
             if (cur > -INFINITY) {
+                if (cbw[l] == cbw[l] && cbw[l] > -1e7) cur = cbw[l];
                 for (int it = 0; it < 50; ++it) {
                     const double ec = exp(cur);
                     double dl = 0, info = 0;
@@ -174,6 +186,7 @@ k_apl_lanes(const int32_t* __restrict__ cnt, long G, long g0, long g1, const dou
                 }
             }
             const double cb = fmax(cur, -1e8);                   // mglmOneWay: pmax(beta, -1e8)
+            cbw[l] = cb;
             const double ecell = exp(cb);
             double w = 0;
 #pragma unroll 2
@@ -220,12 +233,16 @@ k_apl_lanes(const int32_t* __restrict__ cnt, long G, long g0, long g1, const dou
         }
         if (ln == 0) apl[(long)e * G + g] = sum_loglik - adj;
     }
+    if (wg && ln == 0) {
+#pragma unroll
+        for (int l = 0; l < APLL_PM; ++l) if (l < p) wg[l] = cbw[l];
+    }
 }
 
 // APL of genes [g0,g1) for every job -> d_apl[job*G + g]
 void launch_apl(const int32_t* cnt, long G, long g0, long g1, const double* logoff, const DesignDev* designs,
                 const unsigned char* sel, const double* phi_gene, const std::vector<AplJob>& jobs, double* d_apl,
-                cudaStream_t st, const std::vector<DesignDev>* h_designs) {
+                cudaStream_t st, const std::vector<DesignDev>* h_designs, double* d_warm) {
     if (g1 <= g0) return;
     // lane-group kernel: scalar dispersions, every design of the launch one-way with few cells and a batch that fits shared memory
     bool lanes_ok = g_tune.apl_lanes && !phi_gene && h_designs != nullptr && !jobs.empty();
@@ -263,10 +280,10 @@ void launch_apl(const int32_t* cnt, long G, long g0, long g1, const double* logo
             dim3 grid((unsigned)((g1 - g0 + genes - 1) / genes), (unsigned)GR.n);
             if (lanes == 2)
                 CBS_LAUNCH(k_apl_lanes<2>, grid, 128, smem, st, cnt, G, g0, g1, logoff, designs, sel, L, GR, d_apl + first * G,
-                           (const double*)lgfact, (const double*)t);
+                           (const double*)lgfact, (const double*)t, d_warm);
             else
                 CBS_LAUNCH(k_apl_lanes<8>, grid, 128, smem, st, cnt, G, g0, g1, logoff, designs, sel, L, GR, d_apl + first * G,
-                           (const double*)lgfact, (const double*)t);
+                           (const double*)lgfact, (const double*)t, d_warm);
         }
         return;
     }
@@ -328,6 +345,9 @@ void run_common_disp(const int32_t* cnt, long G, long g0, long g1, const double*
     for (int b = 0; b < nb; ++b)
         if (ds.h_array[b].p < ds.h_array[b].n) { br[b].init(0.0, std::pow(4.0, 0.25), 1e-5); active[b] = 1; }
     double* d_apl = g_dev.get<double>("apl_common", (size_t)nb * G);
+    // Newton warm starts across the Brent rounds (k_apl_lanes): NaN = "no previous evaluation"
+    double* d_warm = g_dev.get<double>("apl_warm", (size_t)nb * G * APLL_PM);
+    CBS_CUDA(cudaMemsetAsync(d_warm, 0xff, (size_t)nb * G * APLL_PM * sizeof(double), st));
     int steps = 0;
     for (;;) {
         std::vector<AplJob> jobs;
@@ -335,7 +355,7 @@ void run_common_disp(const int32_t* cnt, long G, long g0, long g1, const double*
         for (int b = 0; b < nb; ++b)
             if (active[b] && !br[b].done) { const double x = br[b].query(); jobs.push_back({b, x * x * x * x}); who.push_back(b); }
         if (jobs.empty()) break;
-        launch_apl(cnt, G, g0, g1, logoff, ds.d_array, sel, nullptr, jobs, d_apl, st, &ds.h_array);
+        launch_apl(cnt, G, g0, g1, logoff, ds.d_array, sel, nullptr, jobs, d_apl, st, &ds.h_array, d_warm);
         std::vector<double> sums;
         apl_sums(d_apl, G, g0, g1, sel, jobs, comm, st, sums);
         for (size_t k = 0; k < who.size(); ++k) br[who[k]].feed(-sums[k]);     // optimize(maximum = TRUE)
