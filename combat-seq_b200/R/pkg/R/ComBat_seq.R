@@ -4,10 +4,11 @@
 # as.matrix / as.factor / model.matrix and the confounding checks stay in R, as in the reference (:25-31, :53-94).
 # NOT RUN in the build environment: R is not installed there (see INTEGRATION.md); the Python mirror
 # combat-seq_b200/api.py + design.py is the tested twin of this file.
-#   dyn.load("cbs_r_shim.so")   # built by: R CMD SHLIB r_shim.c -L.. -lcombatseq -o cbs_r_shim.so
+# Extras after the reference's arguments (defaults = reference behaviour): mc.mode, seed (gene.subset.n sampling) and
+# n.gpus (0 = every visible GPU; the one R process drives them all through cbs_input.n_gpus).
 ComBat_seq <- function(counts, batch, group=NULL, covar_mod=NULL, full_mod=TRUE,
                        shrink=FALSE, shrink.disp=FALSE, gene.subset.n=NULL,
-                       mc.mode=c("reference", "stable"), seed=0L){
+                       mc.mode=c("reference", "stable"), seed=0L, n.gpus=0L){
   counts <- as.matrix(counts)
   dims <- dimnames(counts)
   batch <- as.factor(batch)
@@ -44,6 +45,7 @@ ComBat_seq <- function(counts, batch, group=NULL, covar_mod=NULL, full_mod=TRUE,
   }
   NAs <- any(is.na(counts))
   if(NAs){cat(c('Found', sum(is.na(counts)), 'Missing Data Values\n'), sep=' ')}
+  # (the library stops on NA / negative / non-integer counts with edgeR::DGEList's wording, as the reference does at :43)
   # mod handed to the library: intercept first, then the non-constant columns (the library rebuilds
   # design = [batch indicators | mod[,-1]], which is cbind(batchmod, mod)[, !check])
   mod_c <- cbind(1, mod[, !apply(mod, 2, function(x) all(x == 1)), drop=FALSE])
@@ -62,7 +64,7 @@ ComBat_seq <- function(counts, batch, group=NULL, covar_mod=NULL, full_mod=TRUE,
   adjust_counts <- .Call("cbs_R_combat_seq", counts, as.integer(batch) - 1L, n_batch, mod_c,
                          as.logical(shrink), as.logical(shrink.disp),
                          if(is.null(gene.subset.n)) -1L else as.integer(gene.subset.n),
-                         as.integer(match.arg(mc.mode) == "stable"), as.double(seed))
+                         as.integer(match.arg(mc.mode) == "stable"), as.double(seed), as.integer(n.gpus))
   dimnames(adjust_counts) <- dims
   return(adjust_counts)
 }

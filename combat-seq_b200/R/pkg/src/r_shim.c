@@ -1,7 +1,9 @@
 /* r_shim.c — .Call bridge from R to the C ABI of libcombatseq.so (include/combatseq.h).
  * Replaces the in-process R body of ComBat_seq() (/root/reference/ComBat_seq.R:33-203); no logic lives here.
- * Build where R exists:  R CMD SHLIB r_shim.c -I../../include -L.. -lcombatseq -o cbs_r_shim.so
- * NOT COMPILED in the build environment (no Rinternals.h there).  R is single-threaded: the R API is only touched
+ * Build where R exists:  R CMD INSTALL combat-seq_b200/R/pkg   (src/Makevars links libcombatseq.so), or
+ *                        R CMD SHLIB r_shim.c -I../../../../include -L../../.. -lcombatseq -o cbs_r_shim.so
+ * NOT COMPILED AGAINST R in the build environment (no R there); tests/test_abi_host.py compiles it against a minimal
+ * stand-in of R's C API (tests/r_stub/) so that at least the C and the use of include/combatseq.h are checked.  R is single-threaded: the R API is only touched
  * on the calling thread, nothing longjmps through C++ frames (cbs_* never throw; the error text is copied before
  * Rf_error), and the one allocation is PROTECTed. */
 #include <R.h>
@@ -10,7 +12,7 @@
 #include "combatseq.h"
 
 SEXP cbs_R_combat_seq(SEXP counts, SEXP batch_idx, SEXP n_batch, SEXP mod, SEXP shrink, SEXP shrink_disp,
-                      SEXP gene_subset_n, SEXP mc_stable, SEXP seed) {
+                      SEXP gene_subset_n, SEXP mc_stable, SEXP seed, SEXP n_gpus) {
     SEXP dim = Rf_getAttrib(counts, R_DimSymbol);
     SEXP mdim = Rf_getAttrib(mod, R_DimSymbol);
     cbs_input in;
@@ -30,6 +32,7 @@ SEXP cbs_R_combat_seq(SEXP counts, SEXP batch_idx, SEXP n_batch, SEXP mod, SEXP 
     in.seed = (uint64_t)Rf_asReal(seed);
     in.mc_mode = Rf_asInteger(mc_stable) ? CBS_MC_STABLE : CBS_MC_REFERENCE;
     in.device = -1;
+    in.n_gpus = Rf_asInteger(n_gpus);        /* 0 = every visible GPU: one R process drives them all (single-process sharding) */
     SEXP ans = PROTECT(Rf_allocMatrix(REALSXP, in.G0, in.N));
     out.adjusted = REAL(ans);
     int rc = cbs_combat_seq(&in, &out);

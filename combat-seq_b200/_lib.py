@@ -26,7 +26,7 @@ EXPORTS = ("cbs_version", "cbs_device_count", "cbs_last_error", "cbs_shutdown", 
            "cbs_comm_unique_id", "cbs_comm_create", "cbs_comm_destroy", "cbs_shard_range", "cbs_combat_seq", "cbs_nb_logpmf",
            "cbs_nb_cdf", "cbs_nb_quantile", "cbs_glm_fit", "cbs_apl", "cbs_common_disp", "cbs_tagwise_disp",
            "cbs_mc_int", "cbs_match_quantiles", "cbs_profile_enable", "cbs_profile_dump", "cbs_fp64_peak",
-           "cbs_fp64_mma_peak", "cbs_set_tuning", "cbs_get_diag")
+           "cbs_fp64_mma_peak", "cbs_set_tuning", "cbs_get_diag", "cbs_tagwise_disp_prior")
 
 
 class CbsInput(C.Structure):
@@ -184,11 +184,15 @@ def common_disp(y, design=None):
     return v.value
 
 
-def tagwise_disp(y, design, common):
+def tagwise_disp(y, design, common, prior_df=0.0):
     y = _F(y, np.int32); G, n = y.shape
     des = _F(design) if design is not None else None
     p = des.shape[1] if des is not None else 1
     out = np.empty(G)
+    if prior_df:
+        check(lib().cbs_tagwise_disp_prior(C.c_int64(G), C.c_int32(n), _p(y, i32p), _p(des), C.c_int32(p), C.c_double(common),
+                                           C.c_double(prior_df), _p(out)))
+        return out
     check(lib().cbs_tagwise_disp(C.c_int64(G), C.c_int32(n), _p(y, i32p), _p(des), C.c_int32(p), C.c_double(common),
                                  _p(out)))
     return out

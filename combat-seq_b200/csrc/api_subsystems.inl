@@ -98,6 +98,7 @@ namespace cbs {
 struct OneBatch {
     DesignSet ds;
     int32_t* d_cnt; double* d_logoff; unsigned char* d_sel; int* d_bidx;
+    std::vector<double> h_lib;
     void init(int64_t G, int32_t n, const int32_t* counts, const double* design, int32_t p) {
         ds.add(subproblem_design(design, n, p));
         ds.finish();
@@ -115,6 +116,8 @@ struct OneBatch {
         CBS_CUDA(cudaMemcpy(cs.data(), d_cs, (size_t)n * sizeof(unsigned long long), cudaMemcpyDeviceToHost));
         std::vector<double> logoff((size_t)2 * n);
         for (int s = 0; s < n; ++s) { logoff[2 * s] = std::log((double)cs[s]); logoff[2 * s + 1] = (double)cs[s]; }
+        h_lib.resize(n);
+        for (int s = 0; s < n; ++s) h_lib[s] = (double)cs[s];
         d_logoff = upload(g_dev, "logoff", logoff.data(), (size_t)2 * n);
         std::vector<int> bidx(n, 0);
         d_bidx = upload(g_dev, "batch_idx", bidx.data(), (size_t)n);
@@ -136,6 +139,27 @@ int cbs_common_disp(int64_t G, int32_t n, const int32_t* counts, const double* d
     std::vector<double> c;
     run_common_disp(ob.d_cnt, G, 0, G, ob.d_logoff, ob.ds, ob.d_sel, nullptr, 0, c, nullptr);
     *common = c[0];
+    CBS_ENTRY_END
+}
+
+int cbs_tagwise_disp_prior(int64_t G, int32_t n, const int32_t* counts, const double* design, int32_t p, double common,
+                           double prior_df, double* tagwise) {
+    CBS_NEED_GPU();
+    if (G < 1 || !counts || !tagwise || !(prior_df >= 0)) return fail(CBS_EINVAL, "null pointer / bad size / negative prior.df");
+    if (int rc = check_design_size(n, design ? p : 1)) return rc;
+    CBS_ENTRY_BEGIN
+    OneBatch ob;
+    ob.init(G, n, counts, design, p);
+    if (ob.ds.h_array[0].p >= n) {      // estimateGLMTagwiseDisp.default: ncol(design) >= ncol(y) -> NA
+        for (int64_t g = 0; g < G; ++g) tagwise[g] = std::nan("");
+    } else {
+        DesignSet one;
+        one.add(subproblem_design(nullptr, n, 1));
+        one.finish();
+        double* d_phi = g_dev.get<double>("phi_hat", (size_t)G);
+        run_tagwise_disp_prior(ob.d_cnt, G, ob.d_logoff, ob.h_lib, ob.ds, one, ob.d_sel, common, prior_df, 0, d_phi);
+        CBS_CUDA(cudaMemcpy(tagwise, d_phi, (size_t)G * sizeof(double), cudaMemcpyDeviceToHost));
+    }
     CBS_ENTRY_END
 }
 

@@ -79,6 +79,10 @@ void run_tagwise_disp(const int32_t* cnt, long G, long g0, long g1, const double
                       const unsigned char* sel, const std::vector<double>& common, const std::vector<char>& do_batch,
                       cudaStream_t st, double* d_phi_hat);
 
+void run_tagwise_disp_prior(const int32_t* cnt, long G, const double* logoff, const std::vector<double>& h_lib,
+                            const DesignSet& ds, const DesignSet& onecell, const unsigned char* sel, double common,
+                            double prior_df, cudaStream_t st, double* d_phi_hat);
+
 // tu_glm.cu
 void run_glm_fit(const int32_t* cnt, long G, long g0, long g1, int N, const double* d_logoff,
                  const std::vector<double>& h_lib, const double* d_phi, const int* d_phi_col, const DesignDev* d_design,

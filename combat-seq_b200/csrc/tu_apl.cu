@@ -4,6 +4,8 @@
 // (/root/reference/ComBat_seq.R:110-119) of edgeR 3.22: APL evaluation + Brent's optimize() on delta = phi^(1/4),
 // then the 11-point grid + FMM spline maximiser.
 #include "engine.hpp"
+#include <cub/device/device_radix_sort.cuh>
+#include <cub/device/device_scan.cuh>
 
 namespace cbs {
 
@@ -109,15 +111,28 @@ k_apl_lanes(const int32_t* __restrict__ cnt, long G, long g0, long g1, const dou
     const DesignDev d = designs[di];
     const int n = d.n, p = d.p, ns = apll_row_stride(n, APLL_LANES);
     double* y_s = apl_sm;                       // [genes][ns]
-    double* lib_s = apl_sm + APLL_GENES * ns;   // [n] library sizes, [n] log library sizes (design order)
+    double* lib_s = apl_sm + APLL_GENES * ns;   // [n] library sizes, [n] log library sizes, [n] columns (design order)
     double* off_s = lib_s + n;
+    int* col_s = reinterpret_cast<int*>(off_s + n);
     const long gbase = g0 + (long)blockIdx.x * APLL_GENES;
-    for (int k = threadIdx.x; k < APLL_GENES * n; k += blockDim.x) {        // consecutive genes per sample: whole sectors
-        const int gi = k & (APLL_GENES - 1), t = k / APLL_GENES;
-        const long g = gbase + gi;
-        y_s[gi * ns + t] = g < g1 ? (double)cnt[g + (long)d.col[t] * G] : 0.0;
+    for (int t = threadIdx.x; t < n; t += blockDim.x) { const int c = d.col[t]; off_s[t] = logoff[2 * c]; lib_s[t] = logoff[2 * c + 1]; col_s[t] = c; }
+    __syncthreads();
+    // consecutive genes per sample: whole sectors.  Eight loads are in flight per thread before the first conversion (the
+    // loop was the top stall of the kernel with one dependent load at a time; ncu, profiles/r02_ncu_k_apl_lanes_a.txt).
+    for (int k0 = threadIdx.x; k0 < APLL_GENES * n; k0 += 8 * 128) {
+        int v[8];
+#pragma unroll
+        for (int u = 0; u < 8; ++u) {
+            const int k = k0 + u * 128, gi = k & (APLL_GENES - 1), t = k / APLL_GENES;
+            const long g = gbase + gi;
+            v[u] = (k < APLL_GENES * n && g < g1) ? __ldg(cnt + g + (long)col_s[t] * G) : 0;
+        }
+#pragma unroll
+        for (int u = 0; u < 8; ++u) {
+            const int k = k0 + u * 128, gi = k & (APLL_GENES - 1), t = k / APLL_GENES;
+            if (k < APLL_GENES * n) y_s[gi * ns + t] = __hiloint2double(0x43300000, v[u]) - 4503599627370496.0;     // exact int -> double
+        }
     }
-    for (int t = threadIdx.x; t < n; t += blockDim.x) { const int c = d.col[t]; off_s[t] = logoff[2 * c]; lib_s[t] = logoff[2 * c + 1]; }
     __syncthreads();
     const int gslot = threadIdx.x / APLL_LANES, ln = threadIdx.x % APLL_LANES;
     const long g = gbase + gslot;
@@ -254,11 +269,11 @@ void launch_apl(const int32_t* cnt, long G, long g0, long g1, const double* logo
             nmax = std::max(nmax, hd.n);
         }
     const int lanes = nmax <= 256 ? 2 : 8, genes = 128 / lanes;          // (cells are at most as long as the batch)
-    lanes_ok = lanes_ok && ((size_t)genes * apll_row_stride(nmax, lanes) + 2 * (size_t)nmax) * sizeof(double) <= 200 * 1024;
+    lanes_ok = lanes_ok && ((size_t)genes * apll_row_stride(nmax, lanes) + 3 * (size_t)nmax) * sizeof(double) <= 200 * 1024;
     if (lanes_ok) {
         double* lgfact = g_dev.get<double>("lgfact", (size_t)LGFACT_N);
         CBS_LAUNCH(k_lgfact_init, grid1(LGFACT_N, 256), 256, 0, st, lgfact);
-        const size_t smem = ((size_t)genes * apll_row_stride(nmax, lanes) + 2 * (size_t)nmax) * sizeof(double);
+        const size_t smem = ((size_t)genes * apll_row_stride(nmax, lanes) + 3 * (size_t)nmax) * sizeof(double);
         t_ctx->set_func_attr((const void*)k_apl_lanes<2>, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024);
         t_ctx->set_func_attr((const void*)k_apl_lanes<8>, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024);
         for (size_t e0 = 0; e0 < jobs.size();) {
@@ -389,6 +404,106 @@ void run_tagwise_disp(const int32_t* cnt, long G, long g0, long g1, const double
             CBS_LAUNCH(k_fill_apl, grid1(g1 - g0, 256), 256, 0, st, d_phi_hat + (size_t)b * G + g0, g1 - g0, common[b]);
         }
     }
+}
+
+// ---- prior.df > 0: weighted-likelihood empirical-Bayes moderation of the tagwise dispersions -----------------------------
+// edgeR estimateGLMTagwiseDisp(prior.df) -> dispCoxReidInterpolateTagwise: the APL grid of every gene is blended with the
+// trend of the grid over abundance, apl.smooth = (apl + prior.n * trend) / (1 + prior.n), prior.n = prior.df / (nlibs - ncoefs),
+// trend = moving average (width floor(span * ntags), span = (10 / ntags)^0.23) of the APL rows ordered by AveLogCPM.
+// ComBat-seq itself always passes prior.df = 0 (/root/reference/ComBat_seq.R:116), where this is the identity; the
+// capability is exposed through cbs_tagwise_disp_prior.
+
+// aveLogCPM(y, prior.count = 2, dispersion = 0.05): key of the abundance order; genes outside the selection sort last
+__global__ void __launch_bounds__(128)
+k_ave_log_cpm(const int32_t* __restrict__ cnt, long G, const double* __restrict__ logoff, const double* __restrict__ yadd,
+              const DesignDev* __restrict__ onecell, const unsigned char* __restrict__ sel, double goff,
+              double* __restrict__ key, int* __restrict__ idx) {
+    const long g = (long)blockIdx.x * blockDim.x + threadIdx.x;
+    if (g >= G) return;
+    idx[g] = (int)g;
+    if (sel && !sel[g]) { key[g] = INFINITY; return; }
+    const DesignDev d = *onecell;
+    RowSrc src{cnt, G, logoff, yadd, nullptr, nullptr, 0.05};
+    Row r(src, g, goff);
+    const double beta = fit_one_group(d, r, 0, d.n, 50, 1e-10);
+    key[g] = (beta + log(1e6)) / log(2.0);
+}
+
+// colbuf[k * Gs + r] = apl[k * G + order[r]]: the grid columns in abundance order
+__global__ void k_gather_sorted(const double* __restrict__ apl, long G, const int* __restrict__ order, long Gs,
+                                double* __restrict__ colbuf) {
+    const long r = (long)blockIdx.x * blockDim.x + threadIdx.x;
+    const int k = blockIdx.y;
+    if (r < Gs) colbuf[(long)k * Gs + r] = apl[(long)k * G + order[r]];
+}
+
+// movingAverageByCol(full.length = TRUE) from the inclusive prefix sums cs of the sorted columns, blended into apl in place
+__global__ void k_blend_trend(const double* __restrict__ cs, const int* __restrict__ order, long G, long Gs, int width,
+                              double prior_n, double* __restrict__ apl) {
+    const long r = (long)blockIdx.x * blockDim.x + threadIdx.x;
+    const int k = blockIdx.y;
+    if (r >= Gs) return;
+    const long half1 = (width + 1) / 2, half2 = width / 2;
+    const long lo = max(0L, r - half1 + 1), hi = min(Gs - 1, r + half2);
+    const double* c = cs + (long)k * Gs;
+    const double trend = (c[hi] - (lo > 0 ? c[lo - 1] : 0.0)) / (double)(hi - lo + 1);
+    double* a = apl + (long)k * G + order[r];
+    *a = (*a + prior_n * trend) / (1 + prior_n);
+}
+
+// estimateGLMTagwiseDisp(y, design, dispersion = common, prior.df) for ONE batch on one device (every gene of the batch
+// takes part in the trend, so the stage does not shard by genes).  ds holds the batch's design, onecell an intercept-only
+// design over the same columns.
+void run_tagwise_disp_prior(const int32_t* cnt, long G, const double* logoff, const std::vector<double>& h_lib,
+                            const DesignSet& ds, const DesignSet& onecell, const unsigned char* sel, double common,
+                            double prior_df, cudaStream_t st, double* d_phi_hat) {
+    std::vector<AplJob> jobs;
+    for (int k = 0; k < 11; ++k) jobs.push_back({0, common * std::pow(2.0, -6.0 + k * (12.0 / 10))});
+    double* d_apl = g_dev.get<double>("apl_grid", jobs.size() * (size_t)G);
+    launch_apl(cnt, G, 0, G, logoff, ds.d_array, sel, nullptr, jobs, d_apl, st, &ds.h_array);
+    const int n = ds.h_array[0].n, p = ds.h_array[0].p;
+    if (prior_df > 0) {
+        // abundance order of the selected genes
+        double mean_lib = 0;
+        for (int s = 0; s < n; ++s) mean_lib += h_lib[s];
+        mean_lib /= n;
+        std::vector<double> yadd(n);
+        for (int s = 0; s < n; ++s) yadd[s] = 2.0 * h_lib[s] / mean_lib;                     // add_prior.cpp, prior.count = 2
+        double* d_yadd = upload(g_dev, "alc_yadd", yadd.data(), (size_t)n, st);
+        double* key = g_dev.get<double>("alc_key", (size_t)G);
+        double* key2 = g_dev.get<double>("alc_key2", (size_t)G);
+        int* idx = g_dev.get<int>("alc_idx", (size_t)G);
+        int* order = g_dev.get<int>("alc_order", (size_t)G);
+        CBS_LAUNCH(k_ave_log_cpm, grid1(G, 128), 128, 0, st, cnt, G, logoff, d_yadd, onecell.d_array, sel, std::log1p(4.0 / mean_lib), key, idx);
+        size_t tmp_bytes = 0;
+        CBS_CUDA(cub::DeviceRadixSort::SortPairs(nullptr, tmp_bytes, key, key2, idx, order, (int)G, 0, 64, st));
+        void* tmp = g_dev.get("alc_sort_tmp", tmp_bytes);
+        CBS_CUDA(cub::DeviceRadixSort::SortPairs(tmp, tmp_bytes, key, key2, idx, order, (int)G, 0, 64, st));
+        // number of selected genes (they sort before the +inf keys)
+        std::vector<unsigned char> h_sel(G, 1);
+        if (sel) CBS_CUDA(cudaMemcpyAsync(h_sel.data(), sel, (size_t)G, cudaMemcpyDeviceToHost, st));
+        CBS_CUDA(cudaStreamSynchronize(st));
+        long Gs = 0;
+        for (long g = 0; g < G; ++g) Gs += h_sel[g] ? 1 : 0;
+        const double prior_n = prior_df / (double)(n - p);
+        const double span = G > 10 ? std::pow(10.0 / (double)G, 0.23) : 1.0;
+        int width = (int)std::floor(span * (double)Gs);
+        if (width > Gs) width = (int)Gs;
+        if (Gs > 0 && width > 1) {
+            double* colbuf = g_dev.get<double>("alc_cols", (size_t)11 * Gs);
+            double* cs = g_dev.get<double>("alc_cs", (size_t)11 * Gs);
+            CBS_LAUNCH(k_gather_sorted, dim3((unsigned)((Gs + 255) / 256), 11), 256, 0, st, d_apl, G, order, Gs, colbuf);
+            size_t scan_bytes = 0;
+            CBS_CUDA(cub::DeviceScan::InclusiveSum(nullptr, scan_bytes, colbuf, cs, (int)Gs, st));
+            void* stmp = g_dev.get("alc_scan_tmp", scan_bytes);
+            for (int k = 0; k < 11; ++k)
+                CBS_CUDA(cub::DeviceScan::InclusiveSum(stmp, scan_bytes, colbuf + (size_t)k * Gs, cs + (size_t)k * Gs, (int)Gs, st));
+            CBS_LAUNCH(k_blend_trend, dim3((unsigned)((Gs + 255) / 256), 11), 256, 0, st, cs, order, G, Gs, width, prior_n, d_apl);
+        } else if (Gs > 0) {
+            // width <= 1: movingAverageByCol returns its input, the blend is the identity
+        }
+    }
+    CBS_LAUNCH(k_tagwise_max, grid1(G, 128), 128, 0, st, d_apl, G, 0L, G, sel, common, d_phi_hat);
 }
 
 }  // namespace cbs

@@ -169,6 +169,12 @@ int cbs_apl(int64_t G, int32_t n, const int32_t* counts, const double* design, i
 int cbs_common_disp(int64_t G, int32_t n, const int32_t* counts, const double* design, int32_t p, double* common);
 int cbs_tagwise_disp(int64_t G, int32_t n, const int32_t* counts, const double* design, int32_t p,
                      double common, double* tagwise);
+/* The same with edgeR's weighted-likelihood empirical-Bayes moderation, estimateGLMTagwiseDisp(..., prior.df): the APL grid
+ * of every gene is blended with the moving-average trend of the grid over abundance (aveLogCPM order) before the spline
+ * maximisation.  ComBat_seq() itself passes prior.df = 0 (ComBat_seq.R:116), which cbs_tagwise_disp reproduces; this entry
+ * exposes the capability for prior_df > 0 (one device). */
+int cbs_tagwise_disp_prior(int64_t G, int32_t n, const int32_t* counts, const double* design, int32_t p,
+                           double common, double prior_df, double* tagwise);
 
 /* monte_carlo_int_NB(dat, mu, gamma, phi, gene.subset.n)  helper_seq.R:8-42 for one batch */
 int cbs_mc_int(int64_t G, int32_t n, const int32_t* counts, const double* mu, const double* gamma,

@@ -142,11 +142,15 @@ def common_disp(y, design=None, nthreads=1):
     return v, ne.value
 
 
-def tagwise_disp(y, design, common, nthreads=1):
+def tagwise_disp(y, design, common, nthreads=1, prior_df=0.0):
     y = _F(y); G, n = y.shape
     des = _F(design) if design is not None else None
     p = des.shape[1] if des is not None else 1
     out = np.empty(G)
+    if prior_df:
+        lib().ref_tagwise_disp_prior(C.c_int64(G), C.c_int32(n), _p(y), _p(des), C.c_int32(p), C.c_double(common),
+                                     C.c_double(prior_df), _p(out), C.c_int(nthreads))
+        return out
     lib().ref_tagwise_disp(C.c_int64(G), C.c_int32(n), _p(y), _p(des), C.c_int32(p), C.c_double(common), _p(out),
                            C.c_int(nthreads))
     return out

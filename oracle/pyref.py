@@ -289,13 +289,45 @@ def maximize_interpolant(x, y):                                # src/interpolato
     return xmax
 
 
-def tagwise_disp(Y, X, common):                                # dispCoxReidInterpolateTagwise, prior.df = 0
-    G = Y.shape[0]
-    off = np.repeat(np.log(Y.sum(axis=0))[None, :], G, 0)
+def ave_log_cpm(Y, lib):                                       # R/aveLogCPM.R: prior.count 2, dispersion 0.05
+    prior = 2.0 * lib / lib.mean()
+    off = np.log(lib + 2 * prior)
+    return np.array([(glm_one_group(y + prior, off, np.full(len(lib), 0.05)) + np.log(1e6)) / np.log(2) for y in Y])
+
+
+def moving_average_by_col(x, width):                           # R/movingAverageByCol.R, full.length = TRUE
+    n = x.shape[0]
+    if width <= 1:
+        return x
+    width = min(width, n)
+    half1, half2 = -(-width // 2), width // 2
+    z = np.vstack([np.zeros((half1, x.shape[1])), x, np.zeros((half2, x.shape[1]))])
+    cs = np.cumsum(z, axis=0)
+    out = cs[width:] - cs[:-width]
+    w = np.full(n, float(width))
+    if half1 > 1:
+        w[:half1 - 1] = width - np.arange(half1 - 1, 0, -1)
+    if half2 > 0:
+        w[n - half2:] = width - np.arange(1, half2 + 1)
+    return out / w[:, None]
+
+
+def tagwise_disp(Y, X, common, prior_df=0.0):                  # dispCoxReidInterpolateTagwise; ComBat-seq passes prior.df = 0
+    G, n = Y.shape
+    lib = Y.sum(axis=0).astype(float)
+    off = np.repeat(np.log(lib)[None, :], G, 0)
     out = np.full(G, common)
     sel = Y.sum(axis=1) >= 5
     pts = np.linspace(-6, 6, 11)
     apl = np.stack([adjusted_profile_lik(common * 2 ** t, Y[sel], X, off[sel]) for t in pts], axis=1)
+    if prior_df > 0:                                           # weighted-likelihood EB moderation towards the abundance trend
+        prior_n = prior_df / (n - X.shape[1])
+        span = (10.0 / G) ** 0.23 if G > 10 else 1.0
+        width = int(np.floor(span * sel.sum()))
+        o = np.argsort(ave_log_cpm(Y[sel].astype(float), lib), kind="stable")
+        smooth = np.empty_like(apl)
+        smooth[o] = moving_average_by_col(apl[o], width)
+        apl = (apl + prior_n * smooth) / (1 + prior_n)
     out[sel] = [common * 2 ** maximize_interpolant(pts, a) for a in apl]
     return out
 

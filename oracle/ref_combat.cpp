@@ -349,6 +349,11 @@ void ref_apl(int64_t G, int32_t n, const double* y, const double* design, int32_
 double ref_common_disp(int64_t G, int32_t n, const double* y, const double* design, int32_t p, int nthreads, int* n_eval) {
     return estimate_common_disp(y, G, n, design, p, nthreads, n_eval);
 }
+void ref_tagwise_disp_prior(int64_t G, int32_t n, const double* y, const double* design, int32_t p, double common, double prior_df,
+                            double* tagwise, int nthreads) {
+    std::vector<double> ones(n, 1.0);
+    estimate_tagwise_disp(y, G, n, design ? design : ones.data(), design ? p : 1, common, tagwise, nthreads, prior_df);
+}
 void ref_tagwise_disp(int64_t G, int32_t n, const double* y, const double* design, int32_t p, double common, double* tagwise, int nthreads) {
     std::vector<double> ones(n, 1.0);
     estimate_tagwise_disp(y, G, n, design ? design : ones.data(), design ? p : 1, common, tagwise, nthreads);

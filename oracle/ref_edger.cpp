@@ -575,12 +575,43 @@ double maximize_interpolant(int npts, const double* x, const double* y) {
 
 // R/estimateGLMTagwiseDisp.R + R/dispCoxReidInterpolateTagwise.R with prior.df = 0 (ComBat_seq.R:116):
 // prior.n = 0 => apl.smooth == apl, so the abundance trend / moving average never contributes.
+// R/aveLogCPM.R (aveLogCPM.default): prior.count = 2 scaled by lib.size / mean(lib.size) (src/add_prior.cpp), one-group NB fit
+// with dispersion 0.05, (beta + log(1e6)) / log(2)                                                        [edgeR-recall, A.9]
+static double ave_log_cpm(const double* yrow, int n, const double* lib, double mean_lib) {
+    std::vector<double> yy(n), off(n), disp(n, 0.05);
+    for (int s = 0; s < n; ++s) {
+        const double prior = 2.0 * lib[s] / mean_lib;
+        yy[s] = yrow[s] + prior;
+        off[s] = std::log(lib[s] + 2 * prior);
+    }
+    return (glm_one_group(n, yy.data(), off.data(), disp.data(), 50, 1e-10) + std::log(1e6)) / std::log(2.0);
+}
+
+// R/movingAverageByCol.R with full.length = TRUE: zero-padded cumulative sums; every row becomes the mean of the rows that
+// exist inside its window [r - ceil(width/2) + 1, r + floor(width/2)]                                        [edgeR-recall]
+static void moving_average_rows(const std::vector<double>& x, long n, int width, std::vector<double>& out) {
+    out = x;
+    if (width <= 1) return;
+    if (width > n) width = (int)n;
+    const long half1 = (width + 1) / 2, half2 = width / 2;
+    std::vector<long double> cs(n + 1, 0.0L);                        // R's cumsum accumulates in long double
+    for (long i = 0; i < n; ++i) cs[i + 1] = cs[i] + (long double)x[i];
+    for (long r = 0; r < n; ++r) {
+        const long lo = std::max(0L, r - half1 + 1), hi = std::min(n - 1, r + half2);
+        out[r] = (double)((double)(cs[hi + 1]) - (double)(cs[lo])) / (double)(hi - lo + 1);
+    }
+}
+
+// R/estimateGLMTagwiseDisp.R + R/dispCoxReidInterpolateTagwise.R.  prior_df = 0 is what ComBat-seq passes
+// (/root/reference/ComBat_seq.R:116): no moderation.  prior_df > 0: the weighted-likelihood empirical-Bayes moderation,
+// apl.smooth = (apl + prior.n * trend) / (1 + prior.n) with prior.n = prior.df / (nlibs - ncoefs) and trend = moving average
+// (width floor(span * ntags), span = (10 / ntags)^0.23) of the APL rows ordered by AveLogCPM.               [edgeR-recall, A.7]
 void estimate_tagwise_disp(const double* y, long G, int n, const double* design, int p, double common,
-                           double* tagwise, int nthreads) {
+                           double* tagwise, int nthreads, double prior_df) {
     for (long g = 0; g < G; ++g) tagwise[g] = common;
     if (p >= n) { for (long g = 0; g < G; ++g) tagwise[g] = kNaN; return; }
-    std::vector<double> off(n);
-    for (int s = 0; s < n; ++s) { double cs = 0; for (long g = 0; g < G; ++g) cs += y[g + (size_t)s * G]; off[s] = std::log(cs); }
+    std::vector<double> off(n), lib(n);
+    for (int s = 0; s < n; ++s) { double cs = 0; for (long g = 0; g < G; ++g) cs += y[g + (size_t)s * G]; lib[s] = cs; off[s] = std::log(cs); }
     std::vector<long> rows;
     for (long g = 0; g < G; ++g) { double rs = 0; for (int s = 0; s < n; ++s) rs += y[g + (size_t)s * G]; if (rs >= 5) rows.push_back(g); }
     if (rows.empty()) return;
@@ -595,6 +626,31 @@ void estimate_tagwise_disp(const double* y, long G, int n, const double* design,
         for (long i = 0; i < Gs; ++i) sd[i] = common * std::pow(2.0, pts[k]);
         Bcast d{sd.data(), Gs, n, 1}, o{off.data(), Gs, n, 2};
         adjusted_profile_lik(ysub.data(), Gs, n, design, p, d, o, apl.data() + (size_t)k * Gs, nthreads);
+    }
+    if (prior_df > 0) {
+        const double prior_n = prior_df / (double)(n - p);
+        const double span = G > 10 ? std::pow(10.0 / (double)G, 0.23) : 1.0;       // ntags of estimateGLMTagwiseDisp: all rows of y
+        const int width = (int)std::floor(span * (double)Gs);                      // ntags of the filtered recursive call
+        double mean_lib = 0;
+        for (int s = 0; s < n; ++s) mean_lib += lib[s];
+        mean_lib /= n;
+        std::vector<double> alc(Gs), row(n);
+        for (long i = 0; i < Gs; ++i) {
+            for (int s = 0; s < n; ++s) row[s] = ysub[i + (size_t)s * Gs];
+            alc[i] = ave_log_cpm(row.data(), n, lib.data(), mean_lib);
+        }
+        std::vector<long> o(Gs);
+        for (long i = 0; i < Gs; ++i) o[i] = i;
+        std::stable_sort(o.begin(), o.end(), [&](long a, long b) { return alc[a] < alc[b]; });     // order(): ties by index
+        std::vector<double> col(Gs), sm;
+        for (int k = 0; k < npts; ++k) {
+            for (long r = 0; r < Gs; ++r) col[r] = apl[o[r] + (size_t)k * Gs];
+            moving_average_rows(col, Gs, width, sm);
+            for (long r = 0; r < Gs; ++r) {
+                double& a = apl[o[r] + (size_t)k * Gs];
+                a = (a + prior_n * sm[r]) / (1 + prior_n);
+            }
+        }
     }
     for (long i = 0; i < Gs; ++i) {
         double yv[npts];

@@ -52,7 +52,7 @@ double estimate_common_disp(const double* y, long G, int n, const double* design
                             int* n_eval = nullptr);
 // estimateGLMTagwiseDisp.default(y, design, dispersion = common, prior.df = 0)
 void estimate_tagwise_disp(const double* y, long G, int n, const double* design, int p, double common,
-                           double* tagwise, int nthreads);
+                           double* tagwise, int nthreads, double prior_df = 0.0);
 
 void   fmm_spline(int n, const double* x, const double* y, double* b, double* c, double* d);
 double maximize_interpolant(int npts, const double* x, const double* y);   // src/interpolator.cpp find_max

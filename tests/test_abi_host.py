@@ -157,3 +157,17 @@ def test_messages_follow_the_reference(pkg, capsys):
     assert "Apply shrinkage - computing posterior estimates for parameters" in out
     assert "Using 3 random genes for Monte Carlo integration" in out
     assert "Apply shrinkage to mean only" in out and out[-1] == "Adjusting the data"
+
+
+def test_r_shim_compiles_against_a_stub_of_the_r_api():
+    """The .Call shim cannot be built against R here (no R in the image); it is at least compiled (-fsyntax-only) against a
+    minimal stand-in of the R API declarations it uses, with the real include/combatseq.h, so that field names, types and
+    the entry point's arity stay in step with the C ABI."""
+    import subprocess
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    shim = os.path.join(root, "combat-seq_b200", "R", "pkg", "src", "r_shim.c")
+    r = subprocess.run(["gcc", "-fsyntax-only", "-Wall", "-Werror", "-I" + os.path.join(root, "tests", "r_stub"),
+                        "-I" + os.path.join(root, "include"), shim], capture_output=True, text=True)
+    assert r.returncode == 0, r.stderr
+    wrapper = open(os.path.join(root, "combat-seq_b200", "R", "pkg", "R", "ComBat_seq.R")).read()
+    assert wrapper.count("as.integer(n.gpus)") == 1 and "n_gpus" in open(shim).read()

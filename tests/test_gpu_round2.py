@@ -172,3 +172,20 @@ def test_single_process_multi_gpu_is_bit_identical(pkg, synth):
             for k in want + ("keep", "lib_size", "disp_common", "n_mc_fallback"):
                 assert np.array_equal(one[k], many[k], equal_nan=True), "%s differs at n_gpus=%d (%s)" % (k, n, case.name)
             assert (many["row_begin"], many["row_end"]) == (0, case.counts.shape[0])
+
+
+def test_tagwise_prior_df_moderation(pkg, oracle, synth):
+    # estimateGLMTagwiseDisp(prior.df > 0) on the device (aveLogCPM kernel, radix sort, prefix-sum moving
+    # average, blend) against the oracle; prior.df = 0 is the unmoderated path ComBat_seq() uses.
+    # (abundances well separated: genes whose aveLogCPM agree to rounding can be ordered differently by two implementations,
+    # which moves window edges: an ill-conditioning of the moderation itself, see tests/test_oracle_edger.py)
+    counts, batch, group = synth.simulate(1500, [8, 8], (1, 1.5), (0.15, 0.3), seed=31, low_frac=0.0, base_logmean=6.5, base_logsd=1.2)
+    d = pkg.design.build_design(counts.shape[1], batch, group, None, True)
+    cols = np.flatnonzero(d.batch_idx == 1)
+    Y, X = counts[:, cols], d.mod[cols]
+    base = pkg._lib.tagwise_disp(Y, X, 0.3)
+    for prior_df in (5.0, 20.0):
+        got = pkg._lib.tagwise_disp(Y, X, 0.3, prior_df=prior_df)
+        ref = oracle.tagwise_disp(Y.astype(float), X, 0.3, nthreads=oracle.max_threads(), prior_df=prior_df)
+        assert rel_err(got, ref) <= 1.0
+        assert not np.allclose(got, base)

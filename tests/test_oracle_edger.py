@@ -168,3 +168,39 @@ def test_qr_rank(oracle):
     assert oracle.qr_rank(np.column_stack([X, X[:, 0] + X[:, 1]])) == 4
     assert oracle.qr_rank(np.column_stack([np.ones(10), np.ones(10)])) == 1
     assert oracle.qr_rank(np.column_stack([X[:, 0], X[:, 0] * (1 + 1e-9)])) == 1      # tol = 1e-7 as R's qr()
+
+
+def test_tagwise_prior_df_moderation_two_restatements_agree(oracle):
+    """estimateGLMTagwiseDisp(prior.df > 0) — aveLogCPM order, moving-average trend of the APL grid,
+    blend (apl + prior.n * trend) / (1 + prior.n).  The C++ oracle against the independent numpy restatement (oracle/pyref.py);
+    prior.df = 0 (what ComBat_seq.R:116 passes) must leave the unmoderated result untouched."""
+    import pyref
+    rng = np.random.default_rng(8)
+    G, n = 260, 8
+    # well separated abundances: two genes whose aveLogCPM agree to rounding may be ordered differently by two
+    # implementations, which moves the edges of every window between them (ill-conditioned in edgeR itself)
+    mu = np.exp(np.sort(rng.uniform(4, 9, G)))[:, None] * rng.uniform(0.7, 1.3, (1, n))
+    Y = rng.negative_binomial(5, 5 / (5 + mu)).astype(float)
+    X = np.column_stack([np.ones(n), np.arange(n) % 2])
+    base = oracle.tagwise_disp(Y, X, 0.2, nthreads=2)
+    assert np.array_equal(oracle.tagwise_disp(Y, X, 0.2, nthreads=2, prior_df=0.0), base)
+    for prior_df in (3.0, 10.0, 50.0):
+        a = oracle.tagwise_disp(Y, X, 0.2, nthreads=2, prior_df=prior_df)
+        b = pyref.tagwise_disp(Y, X, 0.2, prior_df=prior_df)
+        assert np.max(np.abs(a - b) / b) < 1e-8
+        assert np.abs(np.log(a) - np.log(base)).mean() > 0.01                   # it does something ...
+    strong = oracle.tagwise_disp(Y, X, 0.2, nthreads=2, prior_df=1e4)
+    sel = Y.sum(axis=1) >= 5
+    assert np.std(np.log(strong[sel])) < 0.5 * np.std(np.log(base[sel]))          # ... and shrinks towards the trend
+
+
+def test_moving_average_matches_a_direct_window_mean():
+    import pyref
+    rng = np.random.default_rng(1)
+    x = rng.normal(size=(37, 3))
+    for width in (1, 2, 5, 8, 37, 50):
+        got = pyref.moving_average_by_col(x, width)
+        w = min(width, 37)
+        h1, h2 = -(-w // 2), w // 2
+        want = np.array([x[max(0, r - h1 + 1): min(36, r + h2) + 1].mean(axis=0) for r in range(37)]) if w > 1 else x
+        assert np.allclose(got, want, rtol=1e-12, atol=1e-12)
