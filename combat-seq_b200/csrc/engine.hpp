@@ -17,6 +17,7 @@ struct Tuning {
     int glm_scr = 1;             // 1 = Levenberg work arrays of the lane-group GLM kernel in shared memory (one copy per gene)
     int apl_fast = 1;            // 1 = lgamma tables + hoisted invariants in the APL kernel (same bits), 0 = per-sample calls
     int apl_lanes = 1;           // 1 = lane-group APL kernel with the batch row staged in shared memory (one-way designs), 0 = k_apl
+    int glm_two_pass = 1;        // 1 = fits that need more than 9 sweeps are redone by a warp per gene (k_glm_fit_wide)
     int glm_hist = 0;            // 1 = histogram of Levenberg iterations per gene (diagnostics; cbs_get_diag "glm_iter_*")
     double mc_tail_tol = 1e-8;   // largest accepted Chebyshev tail estimate (log-likelihood units)
 };

@@ -17,8 +17,13 @@
 #include <cmath>
 #include "fastmath.cuh"
 
+#ifndef CBS_GLM_UNROLL      // samples of a class sweep in flight per lane (development builds: tools/build_variant.sh)
+#define CBS_GLM_UNROLL 1
+#endif
+
 namespace cbs {
 
+constexpr int kGlmUnroll = CBS_GLM_UNROLL;
 constexpr int PMAX = 32;                     // max design columns handled by the per-thread solvers
 constexpr int PTRI = PMAX * (PMAX + 1) / 2;  // packed lower triangle
 
@@ -49,6 +54,7 @@ struct RowSrc {
     const double* phi;     // per-gene dispersion columns phi[g + phi_col[c]*G], or nullptr => phi_scalar
     const int* phi_col;    // [N] dispersion column of each sample (batch index), nullptr => column 0
     double phi_scalar;
+    const int32_t* cnt_row = nullptr;   // optional: THIS gene's counts indexed by column (a shared-memory copy), instead of cnt
 };
 
 struct Row {
@@ -57,7 +63,7 @@ struct Row {
     __device__ __forceinline__ double y(int c) const {
         // counts are non-negative and below 2^31: 2^52 + x is exact in the low mantissa word, one DADD instead of I2F.F64
         // (the conversion sits in every sweep of the fitters; I2F.F64 was the top stall of the GLM kernel, ncu round 1)
-        const double v = __hiloint2double(0x43300000, s.cnt[g + (long)c * s.G]) - 4503599627370496.0;
+        const double v = __hiloint2double(0x43300000, s.cnt_row ? s.cnt_row[c] : s.cnt[g + (long)c * s.G]) - 4503599627370496.0;
         return s.yadd ? v + s.yadd[c] : v;
     }
     __device__ __forceinline__ double off(int c) const { return s.logoff[2 * c] + goff; }
@@ -161,6 +167,7 @@ __device__ inline double lev_sweep(const DesignDev& d, const Row& r, const doubl
             for (int k = k0; k < k1; ++k) eta += d.cval[k] * beta[d.cidx[k]];
             const double E = exp(eta);
             double sw = 0, sz = 0;
+#pragma unroll kGlmUnroll
             for (int t = t0 + ln; t < t1; t += LANES) {
                 const int col = d.col[t];
                 const double mu = E * r.lib(col), y = r.y(col), phi = r.phi(col);
@@ -221,8 +228,8 @@ __device__ inline void chol_solve_packed(const double* a, int p, double* b) {
     for (int i = p - 1; i >= 0; --i) { double s = b[i]; for (int k = i + 1; k < p; ++k) s -= a[tri(k, i)] * b[k]; b[i] = s / a[tri(i, i)]; }
 }
 
-// edgeR glm_levenberg::fit with the "null" start.  beta (out, p).  Returns the number of iterations, or -1 when y is all
-// zero (beta = NaN, mu = 0).
+// edgeR glm_levenberg::fit with the "null" start.  beta (out, p).  Returns the number of sweeps over the samples (1 + one per
+// Levenberg trial step), or -1 when y is all zero (beta = NaN, mu = 0).
 // Work arrays of one Levenberg fit: 3 packed p x p triangles and 4 p-vectors.  One thread per gene keeps them in local
 // memory.  A lane group can share ONE copy in shared memory (SCR = true, `scr` = lev_scratch_doubles<PM>() doubles owned
 // by the group): outside the sample sweeps every lane of the group executes the same instructions on bit-identical
@@ -236,7 +243,7 @@ __host__ __device__ constexpr int lev_scratch_doubles() {
 }
 template <int LANES = 1, int PM = PMAX, bool SCR = false>
 __device__ inline int fit_levenberg(const DesignDev& d, const Row& r, double* beta, int ln = 0, unsigned gm = 0xffffffffu,
-                                    int maxit = 250, double tolerance = 1e-6, double* scr = nullptr) {
+                                    int maxit = 250, double tolerance = 1e-6, double* scr = nullptr, int max_sweeps = 0x7fffffff) {
     constexpr int PT = PM * (PM + 1) / 2;
     constexpr int LT = SCR ? 1 : PT, LV = SCR ? 1 : PM;
     const int p = d.p, pt = p * (p + 1) / 2;
@@ -264,7 +271,7 @@ __device__ inline int fit_levenberg(const DesignDev& d, const Row& r, double* be
     for (int i = 0; i < p; ++i) beta[i] = d.start[i] * c0;
     double dev = lev_sweep<LANES>(d, r, beta, xtwx, dl, ln, gm);
     double max_info = -1, lambda = 0;
-    int iter = 0;
+    int iter = 0, sweeps = 1;
     while ((++iter) <= maxit) {
         for (int i = 0; i < p; ++i) if (xtwx[tri(i, i)] > max_info) max_info = xtwx[tri(i, i)];
         if (iter == 1) { lambda = max_info * 1e-6; if (lambda < 1e-13) lambda = 1e-13; }
@@ -280,7 +287,9 @@ __device__ inline int fit_levenberg(const DesignDev& d, const Row& r, double* be
             } while (1);
             chol_solve_packed(work, p, dbeta);
             for (int i = 0; i < p; ++i) beta_new[i] = beta[i] + dbeta[i];
+            if (sweeps >= max_sweeps) return -2;                   // handed to the wide second pass (tu_glm.cu): nothing is written
             const double dev_new = lev_sweep<LANES>(d, r, beta_new, xtwx_new, dl_new, ln, gm);
+            ++sweeps;
             if (dev_new / ymax < CBS_SUPREMELY_LOW) low_dev = true;
             if (dev_new <= dev || low_dev) {
                 for (int i = 0; i < p; ++i) beta[i] = beta_new[i];
@@ -299,14 +308,14 @@ __device__ inline int fit_levenberg(const DesignDev& d, const Row& r, double* be
         for (int i = 0; i < pt; ++i) xtwx[i] = xtwx_new[i];     // information at the accepted coefficients
         for (int i = 0; i < p; ++i) dl[i] = dl_new[i];
     }
-    return iter;
+    return sweeps;
 }
 
 // glmFit.default's plain fit of one gene: coefficients beta[p]; cellbeta[p] additionally for one-way designs.
-// Returns the Levenberg iteration count (0 for one-way designs, -1 for an all-zero row).
+// Returns the Levenberg sweep count (0 for one-way designs, -1 for an all-zero row).
 template <int LANES = 1, int PM = PMAX>
 __device__ inline int fit_gene(const DesignDev& d, const Row& r, double* beta, double* cellbeta, int ln = 0,
-                               unsigned gm = 0xffffffffu, double* scr = nullptr) {
+                               unsigned gm = 0xffffffffu, double* scr = nullptr, int max_sweeps = 0x7fffffff) {
     if (d.oneway) {
         for (int l = 0; l < d.p; ++l) {
             const double b = fit_one_group<LANES>(d, r, d.cell_start[l], d.cell_start[l + 1], 50, 1e-10, ln, gm);
@@ -318,8 +327,8 @@ __device__ inline int fit_gene(const DesignDev& d, const Row& r, double* beta, d
             beta[k] = s;
         }
     } else {
-        if (LANES > 1 && scr != nullptr && d.ncls > 0) return fit_levenberg<LANES, PM, true>(d, r, beta, ln, gm, 250, 1e-6, scr);
-        return fit_levenberg<LANES, PM, false>(d, r, beta, ln, gm);
+        if (LANES > 1 && scr != nullptr && d.ncls > 0) return fit_levenberg<LANES, PM, true>(d, r, beta, ln, gm, 250, 1e-6, scr, max_sweeps);
+        return fit_levenberg<LANES, PM, false>(d, r, beta, ln, gm, 250, 1e-6, nullptr, max_sweeps);
     }
     return 0;
 }

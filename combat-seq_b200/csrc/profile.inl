@@ -79,6 +79,7 @@ int cbs_set_tuning(const char* key, double value) {
         return CBS_OK;
     }
     if (!strcmp(key, "glm_scr")) { g_tune.glm_scr = value != 0; return CBS_OK; }
+    if (!strcmp(key, "glm_two_pass")) { g_tune.glm_two_pass = value != 0; return CBS_OK; }
     return fail(CBS_EINVAL, "unknown tuning key '%s'", key);
 }
 int cbs_get_diag(const char* key, double* value) {

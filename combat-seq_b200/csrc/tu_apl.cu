@@ -268,13 +268,17 @@ void launch_apl(const int32_t* cnt, long G, long g0, long g1, const double* logo
             lanes_ok = lanes_ok && hd.oneway && hd.p <= APLL_PM && hd.n <= APLL_MAXN && j.phi > 0;
             nmax = std::max(nmax, hd.n);
         }
-    const int lanes = nmax <= 256 ? 2 : 8, genes = 128 / lanes;          // (cells are at most as long as the batch)
+    #ifndef CBS_APL_SHORT_LANES
+#define CBS_APL_SHORT_LANES 2
+#endif
+    const int lanes = nmax <= 256 ? CBS_APL_SHORT_LANES : 8, genes = 128 / lanes;          // (cells are at most as long as the batch)
     lanes_ok = lanes_ok && ((size_t)genes * apll_row_stride(nmax, lanes) + 3 * (size_t)nmax) * sizeof(double) <= 200 * 1024;
     if (lanes_ok) {
         double* lgfact = g_dev.get<double>("lgfact", (size_t)LGFACT_N);
         CBS_LAUNCH(k_lgfact_init, grid1(LGFACT_N, 256), 256, 0, st, lgfact);
         const size_t smem = ((size_t)genes * apll_row_stride(nmax, lanes) + 3 * (size_t)nmax) * sizeof(double);
         t_ctx->set_func_attr((const void*)k_apl_lanes<2>, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024);
+        t_ctx->set_func_attr((const void*)k_apl_lanes<4>, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024);
         t_ctx->set_func_attr((const void*)k_apl_lanes<8>, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024);
         for (size_t e0 = 0; e0 < jobs.size();) {
             AplLaunch L; AplGroups GR;
@@ -293,7 +297,10 @@ void launch_apl(const int32_t* cnt, long G, long g0, long g1, const double* logo
             double* t = g_dev.get<double>("lgr", (size_t)APL_MAX_EVALS * LGFACT_N);
             CBS_LAUNCH(k_lgr_init, dim3(LGFACT_N / 256, (unsigned)L.n_evals), 256, 0, st, L, t);
             dim3 grid((unsigned)((g1 - g0 + genes - 1) / genes), (unsigned)GR.n);
-            if (lanes == 2)
+            if (lanes == 4)
+                CBS_LAUNCH(k_apl_lanes<4>, grid, 128, smem, st, cnt, G, g0, g1, logoff, designs, sel, L, GR, d_apl + first * G,
+                           (const double*)lgfact, (const double*)t, d_warm);
+            else if (lanes == 2)
                 CBS_LAUNCH(k_apl_lanes<2>, grid, 128, smem, st, cnt, G, g0, g1, logoff, designs, sel, L, GR, d_apl + first * G,
                            (const double*)lgfact, (const double*)t, d_warm);
             else

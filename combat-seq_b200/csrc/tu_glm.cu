@@ -54,13 +54,48 @@ k_glm_fit(const int32_t* __restrict__ cnt, long G, long g0, long g1, const doubl
 // DRAM traffic per launch, 15x the algorithmic bytes); dynamic shared memory = (128 / GLM_LANES) * lev_scratch_doubles<PM>().
 constexpr int GLM_LANES = 8;
 constexpr int GLM_LANES_PMAX = 16;
+#ifndef CBS_GLM_MINBLOCKS
+#define CBS_GLM_MINBLOCKS 5
+#endif
+// what a fit leaves behind: coefficients, alpha_g (ComBat_seq.R:131), fitted values; LANES lanes of the gene share the stores
+template <int LANES, int PM>
+__device__ __forceinline__ void glm_store(const DesignDev& d, const Row& r, long g, long G, int ln, const double* beta,
+                                          const double* cellbeta, double* __restrict__ coef, double* __restrict__ fitted,
+                                          const double* __restrict__ alpha_w, int n_alpha, double* __restrict__ alpha_out) {
+    if (coef) for (int k = ln; k < d.p; k += LANES) coef[g + (long)k * G] = beta[k];
+    if (alpha_out && ln == 0) {
+        double a = 0;
+        for (int b = 0; b < n_alpha; ++b) a += beta[b] * alpha_w[b];
+        alpha_out[g] = a;
+    }
+    if (fitted) {
+        if (d.oneway) {
+            for (int l = 0; l < d.p; ++l)
+                for (int t = d.cell_start[l] + ln; t < d.cell_start[l + 1]; t += LANES) {
+                    const int c = d.col[t];
+                    fitted[g + (long)c * G] = exp(cellbeta[l] + r.off(c));
+                }
+        } else {
+            const bool dead = isnan(beta[0]);
+            for (int t = ln; t < d.n; t += LANES) fitted[g + (long)d.col[t] * G] = dead ? 0.0 : exp(lin_pred(d, r, t, beta));
+        }
+    }
+}
+
+// A fit that needs more than GLM_SWEEP_CAP sweeps over the samples (Levenberg trial steps that keep being rejected: 0.05 % of
+// C5's fits, up to 64 sweeps against the usual 5-7) is abandoned here and its gene appended to `strag`; k_glm_fit_wide redoes
+// it with a whole warp and the gene's counts in shared memory.  On 8 lanes such a fit is a serial chain ten times longer
+// than its neighbours': it alone set the duration of a launch once the genes were spread over 8 GPUs (7 ms per launch
+// whatever the shard).  The decision depends on the gene only, so it is the same for every sharding.
+constexpr int GLM_SWEEP_CAP = 9;
 template <int PM>                                            // PM >= design columns: sizes the per-thread packed X'WX (local memory)
-__global__ void __launch_bounds__(128, 5)
+__global__ void __launch_bounds__(128, CBS_GLM_MINBLOCKS)
 k_glm_fit_lanes(const int32_t* __restrict__ cnt, long G, long g0, long g1, const double* __restrict__ logoff,
                 const double* __restrict__ yadd, double two_prior_over_meanlib, const double* __restrict__ phi,
                 const int* __restrict__ phi_col, const DesignDev* __restrict__ design, const double* __restrict__ goff_in,
                 int mode, double* __restrict__ coef, double* __restrict__ fitted, const double* __restrict__ alpha_w,
-                int n_alpha, double* __restrict__ alpha_out, int use_scr, int* __restrict__ iter_hist) {
+                int n_alpha, double* __restrict__ alpha_out, int use_scr, int* __restrict__ iter_hist,
+                int* __restrict__ strag, int* __restrict__ n_strag) {
     const long slot = ((long)blockIdx.x * blockDim.x + threadIdx.x) / GLM_LANES;
     const long g = g0 + slot;
     const int ln = threadIdx.x % GLM_LANES;
@@ -74,25 +109,49 @@ k_glm_fit_lanes(const int32_t* __restrict__ cnt, long G, long g0, long g1, const
     double beta[PM], cellbeta[PM];
     extern __shared__ __align__(16) double glm_scr[];       // lev_scratch_doubles<PM>() per lane group, or nothing
     double* scr = use_scr ? glm_scr + (threadIdx.x / GLM_LANES) * lev_scratch_doubles<PM>() : nullptr;
-    const int n_iter = fit_gene<GLM_LANES, PM>(d, r, beta, cellbeta, ln, gm, scr);
-    if (iter_hist && ln == 0) atomicAdd(&iter_hist[max(0, min(n_iter, 255))], 1);      // diagnostics: Levenberg iterations per gene
-    if (coef) for (int k = ln; k < d.p; k += GLM_LANES) coef[g + (long)k * G] = beta[k];
-    if (alpha_out && ln == 0) {
-        double a = 0;
-        for (int b = 0; b < n_alpha; ++b) a += beta[b] * alpha_w[b];
-        alpha_out[g] = a;
+    const int n_sweeps = fit_gene<GLM_LANES, PM>(d, r, beta, cellbeta, ln, gm, scr, strag ? GLM_SWEEP_CAP : 0x7fffffff);
+    if (n_sweeps == -2) {                                    // too long for 8 lanes: the wide pass fits it
+        if (ln == 0) strag[atomicAdd(n_strag, 1)] = (int)(g - g0);
+        return;
     }
-    if (fitted) {
-        if (d.oneway) {
-            for (int l = 0; l < d.p; ++l)
-                for (int t = d.cell_start[l] + ln; t < d.cell_start[l + 1]; t += GLM_LANES) {
-                    const int c = d.col[t];
-                    fitted[g + (long)c * G] = exp(cellbeta[l] + r.off(c));
-                }
-        } else {
-            const bool dead = isnan(beta[0]);
-            for (int t = ln; t < d.n; t += GLM_LANES) fitted[g + (long)d.col[t] * G] = dead ? 0.0 : exp(lin_pred(d, r, t, beta));
+    if (iter_hist && ln == 0) atomicAdd(&iter_hist[max(0, min(n_sweeps, 255))], 1);      // diagnostics: sweeps per fit
+    glm_store<GLM_LANES, PM>(d, r, g, G, ln, beta, cellbeta, coef, fitted, alpha_w, n_alpha, alpha_out);
+}
+
+// Second pass: one warp per abandoned gene, the gene's counts staged in shared memory (the sweeps then run at shared-memory
+// instead of DRAM latency), the Levenberg work arrays in shared memory as in the first pass.  The fit restarts from the null
+// start; with 32 lanes the sums associate differently than with 8, so the coefficients of these genes differ from an 8-lane
+// fit in the last places: what matters is that the route a gene takes does not depend on the sharding.
+// grid: any; warps stride over the list.  Dynamic shared memory: 4 x (scratch + N ints).
+template <int PM>
+__global__ void __launch_bounds__(128)
+k_glm_fit_wide(const int32_t* __restrict__ cnt, long G, long g0, int N, const double* __restrict__ logoff,
+               const double* __restrict__ yadd, double two_prior_over_meanlib, const double* __restrict__ phi,
+               const int* __restrict__ phi_col, const DesignDev* __restrict__ design, const double* __restrict__ goff_in,
+               int mode, double* __restrict__ coef, double* __restrict__ fitted, const double* __restrict__ alpha_w,
+               int n_alpha, double* __restrict__ alpha_out, int* __restrict__ iter_hist, const int* __restrict__ strag,
+               const int* __restrict__ n_strag, int stage_counts) {
+    extern __shared__ __align__(16) double glm_scr[];
+    const int warp = threadIdx.x >> 5, ln = threadIdx.x & 31;
+    double* scr = glm_scr + warp * lev_scratch_doubles<PM>();
+    int32_t* xs = reinterpret_cast<int32_t*>(glm_scr + 4 * lev_scratch_doubles<PM>()) + (long)warp * N;
+    const DesignDev d = *design;
+    const int count = *n_strag;
+    for (int i = blockIdx.x * 4 + warp; i < count; i += gridDim.x * 4) {
+        const long g = g0 + strag[i];
+        if (stage_counts) {
+            __syncwarp();
+            for (int c = ln; c < N; c += 32) xs[c] = cnt[g + (long)c * G];
+            __syncwarp();
         }
+        double goff = goff_in ? goff_in[g] : 0.0;
+        if (mode == 1) goff = log(exp(goff) + two_prior_over_meanlib);
+        RowSrc src{cnt, G, logoff, mode == 1 ? yadd : nullptr, phi, phi_col, 0.0, stage_counts ? xs : nullptr};
+        Row r(src, g, goff);
+        double beta[PM], cellbeta[PM];
+        const int n_sweeps = fit_gene<32, PM>(d, r, beta, cellbeta, ln, 0xffffffffu, scr);
+        if (iter_hist && ln == 0) atomicAdd(&iter_hist[max(0, min(n_sweeps, 255))], 1);
+        glm_store<32, PM>(d, r, g, G, ln, beta, cellbeta, coef, fitted, alpha_w, n_alpha, alpha_out);
     }
 }
 
@@ -120,14 +179,27 @@ void run_glm_fit(const int32_t* cnt, long G, long g0, long g1, int N, const doub
     const bool lanes = h_p <= GLM_LANES_PMAX;
     int* d_hist = g_tune.glm_hist ? g_dev.get<int>("glm_iter_hist", 256) : nullptr;     // zeroed by cbs_get_diag("reset")
     const dim3 lgrid = grid1((g1 - g0) * GLM_LANES, 128);
+    // the wide second pass needs the class form of the sweep with shared scratch (every Levenberg design of the pipeline)
+    const bool two_pass = g_tune.glm_scr && g_tune.glm_two_pass;
+    int* d_strag = g_dev.get<int>("glm_strag", (size_t)(g1 - g0));
+    int* d_nstrag = g_dev.get<int>("glm_nstrag", 1);
     auto launch = [&](const double* yadd, double tp, int mode, double* coef, double* fitted, double* alpha) {
         // one shared-memory copy of the Levenberg work arrays per gene (16 genes per block)
 #define CBS_GLM_LANES(PM_) do { \
             const size_t smem = g_tune.glm_scr ? (size_t)(128 / GLM_LANES) * lev_scratch_doubles<PM_>() * sizeof(double) : 0; \
             t_ctx->set_func_attr((const void*)k_glm_fit_lanes<PM_>, cudaFuncAttributeMaxDynamicSharedMemorySize, \
                                  (int)((128 / GLM_LANES) * lev_scratch_doubles<PM_>() * sizeof(double))); \
+            CBS_CUDA(cudaMemsetAsync(d_nstrag, 0, sizeof(int), st)); \
             CBS_LAUNCH(k_glm_fit_lanes<PM_>, lgrid, 128, smem, st, cnt, G, g0, g1, d_logoff, yadd, tp, d_phi, \
-                       d_phi_col, d_design, d_goff, mode, coef, fitted, d_alpha_w, n_alpha, alpha, g_tune.glm_scr ? 1 : 0, d_hist); } while (0)
+                       d_phi_col, d_design, d_goff, mode, coef, fitted, d_alpha_w, n_alpha, alpha, g_tune.glm_scr ? 1 : 0, d_hist, \
+                       two_pass ? d_strag : (int*)nullptr, d_nstrag); \
+            if (two_pass) { \
+                const int stage = N <= 8192; \
+                const size_t wsmem = 4 * lev_scratch_doubles<PM_>() * sizeof(double) + (stage ? (size_t)4 * N * sizeof(int32_t) : 0); \
+                t_ctx->set_func_attr((const void*)k_glm_fit_wide<PM_>, cudaFuncAttributeMaxDynamicSharedMemorySize, 160 * 1024); \
+                CBS_LAUNCH(k_glm_fit_wide<PM_>, dim3(64), 128, wsmem, st, cnt, G, g0, N, d_logoff, yadd, tp, d_phi, d_phi_col, d_design, \
+                           d_goff, mode, coef, fitted, d_alpha_w, n_alpha, alpha, d_hist, (const int*)d_strag, (const int*)d_nstrag, stage); \
+            } } while (0)
         if (lanes) {
             if (h_p <= 4) CBS_GLM_LANES(4); else if (h_p <= 8) CBS_GLM_LANES(8); else if (h_p <= 12) CBS_GLM_LANES(12); else CBS_GLM_LANES(16);
         } else
