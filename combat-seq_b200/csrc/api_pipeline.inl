@@ -140,10 +140,10 @@ static void pipeline(const cbs_input* in, cbs_output* out, const T* h_or_d_count
     std::vector<double> design((size_t)N * p, 0.0);
     for (int s = 0; s < N; ++s) design[(size_t)in->batch_idx[s] * N + s] = 1.0;
     for (int k = 1; k < p_mod; ++k) for (int s = 0; s < N; ++s) design[(size_t)(B + k - 1) * N + s] = in->mod[(size_t)k * N + s];
-    DesignSet full;
+    DesignSet full("full");
     full.add(make_design(design.data(), N, p, nullptr));
     full.finish();
-    DesignSet bds;                       // per-batch dispersion designs
+    DesignSet bds("batch");                    // per-batch dispersion designs
     std::vector<char> fallback(B, 0), do_tagwise(B, 0);
     for (int b = 0; b < B; ++b) {
         const int nb = (int)bcols[b].size();
@@ -183,9 +183,9 @@ static void pipeline(const cbs_input* in, cbs_output* out, const T* h_or_d_count
     double* d_coef = g_dev.get<double>("coef", (size_t)G * p);
     double* d_mu_hat = g_dev.get<double>("mu_hat", (size_t)G * N);
     // glm_f: only its prior-count coefficients are used, through alpha_g (ComBat_seq.R:131)
-    run_glm_fit(d_cnt, G, g0, g1, N, d_logoff, lib, d_phi_hat, d_bidx, full.d_array, p, nullptr, 1e-4, nullptr, nullptr, d_aw, B, d_alpha, st);
+    run_glm_fit(d_cnt, G, g0, g1, N, d_logoff, lib, d_phi_hat, d_bidx, full.d_array, p, nullptr, 1e-4, nullptr, nullptr, d_aw, B, d_alpha, st, full.h_array[0].ncls > 0);
     // glm_f2: offset = log(lib) + alpha_g (ComBat_seq.R:132-134); gamma_hat = coef[,1:B], mu_hat = fitted.values
-    run_glm_fit(d_cnt, G, g0, g1, N, d_logoff, lib, d_phi_hat, d_bidx, full.d_array, p, d_alpha, 1e-4, d_coef, d_mu_hat, nullptr, 0, nullptr, st);
+    run_glm_fit(d_cnt, G, g0, g1, N, d_logoff, lib, d_phi_hat, d_bidx, full.d_array, p, d_alpha, 1e-4, d_coef, d_mu_hat, nullptr, 0, nullptr, st, full.h_array[0].ncls > 0);
     double* d_gamma_hat = d_coef;        // first B columns
     lap(CBS_ST_GLM);
 

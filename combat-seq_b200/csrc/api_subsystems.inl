@@ -46,7 +46,7 @@ int cbs_glm_fit(int64_t G, int32_t n, const int32_t* counts, const double* desig
     if (disp_cols) for (int s = 0; s < n; ++s) if (disp_cols[s] < 0 || disp_cols[s] >= n_disp_cols) return fail(CBS_EINVAL, "disp_cols out of range");
     if (G == 0) return CBS_OK;
     CBS_ENTRY_BEGIN
-    DesignSet ds;
+    DesignSet ds("sub");
     ds.add(make_design(design, n, p, nullptr));
     ds.finish();
     int32_t* d_cnt = upload(g_dev, "cnt", counts, (size_t)G * n);
@@ -61,7 +61,7 @@ int cbs_glm_fit(int64_t G, int32_t n, const int32_t* counts, const double* desig
     double* d_coef = coef ? g_dev.get<double>("coef", (size_t)G * p) : nullptr;
     double* d_fit = fitted ? g_dev.get<double>("mu_hat", (size_t)G * n) : nullptr;
     run_glm_fit(d_cnt, G, 0, G, n, d_logoff, hlib, d_phi, d_pc, ds.d_array, p, d_goff, prior_count, d_coef, d_fit,
-                nullptr, 0, nullptr, 0);
+                nullptr, 0, nullptr, 0, ds.h_array[0].ncls > 0);
     if (coef) CBS_CUDA(cudaMemcpy(coef, d_coef, (size_t)G * p * sizeof(double), cudaMemcpyDeviceToHost));
     if (fitted) CBS_CUDA(cudaMemcpy(fitted, d_fit, (size_t)G * n * sizeof(double), cudaMemcpyDeviceToHost));
     CBS_CUDA(cudaDeviceSynchronize());
@@ -75,7 +75,7 @@ int cbs_apl(int64_t G, int32_t n, const int32_t* counts, const double* design, i
     if (int rc = check_design_size(n, design ? p : 1)) return rc;
     if (G == 0) return CBS_OK;
     CBS_ENTRY_BEGIN
-    DesignSet ds;
+    DesignSet ds("sub");
     ds.add(subproblem_design(design, n, p));
     ds.finish();
     int32_t* d_cnt = upload(g_dev, "cnt", counts, (size_t)G * n);
@@ -96,7 +96,7 @@ int cbs_apl(int64_t G, int32_t n, const int32_t* counts, const double* design, i
 namespace cbs {
 // shared set-up of cbs_common_disp / cbs_tagwise_disp: one batch whose columns are the whole matrix
 struct OneBatch {
-    DesignSet ds;
+    DesignSet ds{"sub"};
     int32_t* d_cnt; double* d_logoff; unsigned char* d_sel; int* d_bidx;
     std::vector<double> h_lib;
     void init(int64_t G, int32_t n, const int32_t* counts, const double* design, int32_t p) {
@@ -153,7 +153,7 @@ int cbs_tagwise_disp_prior(int64_t G, int32_t n, const int32_t* counts, const do
     if (ob.ds.h_array[0].p >= n) {      // estimateGLMTagwiseDisp.default: ncol(design) >= ncol(y) -> NA
         for (int64_t g = 0; g < G; ++g) tagwise[g] = std::nan("");
     } else {
-        DesignSet one;
+        DesignSet one("onecell");
         one.add(subproblem_design(nullptr, n, 1));
         one.finish();
         double* d_phi = g_dev.get<double>("phi_hat", (size_t)G);

@@ -73,31 +73,42 @@ static bool have_gpu() {
 #define CBS_NEED_GPU() do { if (!have_gpu()) return fail(CBS_ENOGPU, "no CUDA device visible: libcombatseq has no CPU path"); } while (0)
 
 // ---------------------------------------------------------------------------------------------------
-void DesignSet::add(const HostDesign& h) {
-    auto up = [&](const void* src, size_t bytes) -> void* {
-        void* p = nullptr;
-        CBS_CUDA(cudaMalloc(&p, bytes ? bytes : 8));
-        allocs.push_back(p);
-        if (bytes) CBS_CUDA(cudaMemcpy(p, src, bytes, cudaMemcpyHostToDevice));
-        return p;
-    };
-    DesignDev d;
-    d.n = h.n; d.p = h.p; d.oneway = h.oneway; d.ncls = h.ncls;
-    d.col = (const int*)up(h.col.data(), h.col.size() * sizeof(int));
-    d.cell_start = (const int*)up(h.cell_start.data(), h.cell_start.size() * sizeof(int));
-    d.minv = (const double*)up(h.minv.data(), h.minv.size() * sizeof(double));
-    d.rowptr = (const int*)up(h.rowptr.data(), h.rowptr.size() * sizeof(int));
-    d.cidx = (const int*)up(h.cidx.data(), h.cidx.size() * sizeof(int));
-    d.cval = (const double*)up(h.cval.data(), h.cval.size() * sizeof(double));
-    d.start = (const double*)up(h.start.data(), h.start.size() * sizeof(double));
-    h_array.push_back(d);
-}
 void DesignSet::finish() {
-    void* p = nullptr;
-    CBS_CUDA(cudaMalloc(&p, h_array.size() * sizeof(DesignDev) + 8));
-    allocs.push_back(p);
-    CBS_CUDA(cudaMemcpy(p, h_array.data(), h_array.size() * sizeof(DesignDev), cudaMemcpyHostToDevice));
-    d_array = (DesignDev*)p;
+    std::vector<char> blob;
+    auto put = [&](const void* src, size_t bytes) -> size_t {        // returns the offset of the copy inside the blob
+        const size_t off = (blob.size() + 15) / 16 * 16;
+        blob.resize(off + bytes);
+        if (bytes) memcpy(blob.data() + off, src, bytes);
+        return off;
+    };
+    struct Offs { size_t col, cell_start, minv, rowptr, cidx, cval, start; };
+    std::vector<Offs> offs;
+    for (const HostDesign& h : host)
+        offs.push_back({put(h.col.data(), h.col.size() * sizeof(int)), put(h.cell_start.data(), h.cell_start.size() * sizeof(int)),
+                        put(h.minv.data(), h.minv.size() * sizeof(double)), put(h.rowptr.data(), h.rowptr.size() * sizeof(int)),
+                        put(h.cidx.data(), h.cidx.size() * sizeof(int)), put(h.cval.data(), h.cval.size() * sizeof(double)),
+                        put(h.start.data(), h.start.size() * sizeof(double))});
+    const size_t arr_off = (blob.size() + 15) / 16 * 16;
+    blob.resize(arr_off + host.size() * sizeof(DesignDev) + 16);
+    char* dev = (char*)g_dev.get("designs:" + name, blob.size());
+    h_array.clear();
+    for (size_t i = 0; i < host.size(); ++i) {
+        const HostDesign& h = host[i];
+        DesignDev d;
+        d.n = h.n; d.p = h.p; d.oneway = h.oneway; d.ncls = h.ncls;
+        d.col = (const int*)(dev + offs[i].col);
+        d.cell_start = (const int*)(dev + offs[i].cell_start);
+        d.minv = (const double*)(dev + offs[i].minv);
+        d.rowptr = (const int*)(dev + offs[i].rowptr);
+        d.cidx = (const int*)(dev + offs[i].cidx);
+        d.cval = (const double*)(dev + offs[i].cval);
+        d.start = (const double*)(dev + offs[i].start);
+        h_array.push_back(d);
+    }
+    memcpy(blob.data() + arr_off, h_array.data(), h_array.size() * sizeof(DesignDev));
+    CBS_CUDA(cudaMemcpyAsync(dev, blob.data(), blob.size(), cudaMemcpyHostToDevice, t_ctx->st));
+    CBS_CUDA(cudaStreamSynchronize(t_ctx->st));          // the blob is a local
+    d_array = (DesignDev*)(dev + arr_off);
 }
 
 void shard_range(long G, int rank, int world, long* g0, long* g1) {

@@ -41,13 +41,16 @@ extern Diag g_diag;
     } while (0)
 constexpr int NCCL_INT8 = 0, NCCL_INT32 = 2, NCCL_UINT64 = 5, NCCL_FLOAT64 = 8, NCCL_SUM = 0, NCCL_MAX = 2;   // nccl.h enum values
 
-// Device copy of a HostDesign: one allocation per array (a few KB each), released with the set.
+// Device copies of HostDesigns: all arrays of all designs of a set packed into ONE cached device buffer (named, so that two
+// sets alive at the same time do not share it) and uploaded with one copy: no cudaMalloc / cudaFree per call, which are
+// device-synchronising and serialise the host threads of a single-process multi-GPU call.
 struct DesignSet {
-    std::vector<void*> allocs;
+    explicit DesignSet(const char* name_) : name(name_) {}
+    std::string name;
+    std::vector<HostDesign> host;
     DesignDev* d_array = nullptr;      // device array of DesignDev
-    std::vector<DesignDev> h_array;
-    ~DesignSet() { for (void* p : allocs) cudaFree(p); }
-    void add(const HostDesign& h);
+    std::vector<DesignDev> h_array;    // scalar fields valid on the host; pointers are device addresses
+    void add(const HostDesign& h) { host.push_back(h); }
     void finish();
 };
 
@@ -88,7 +91,8 @@ void run_tagwise_disp_prior(const int32_t* cnt, long G, const double* logoff, co
 void run_glm_fit(const int32_t* cnt, long G, long g0, long g1, int N, const double* d_logoff,
                  const std::vector<double>& h_lib, const double* d_phi, const int* d_phi_col, const DesignDev* d_design,
                  int h_p, const double* d_goff, double prior_count, double* d_coef, double* d_fitted,
-                 const double* d_alpha_w, int n_alpha, double* d_alpha, cudaStream_t st);
+                 const double* d_alpha_w, int n_alpha, double* d_alpha, cudaStream_t st,
+                 bool class_form = false);    // the design is a Levenberg design in class form (HostDesign::ncls > 0): enables the wide second pass
 
 // tu_mc.cu: monte_carlo_int_NB for every batch (ComBat_seq.R:142-165); see the definition for the sharding rules
 void run_mc_stage(const int32_t* cnt, long G, int B, const std::vector<std::vector<int>>& bcols, long g0, long g1,

@@ -118,11 +118,41 @@ k_glm_fit_lanes(const int32_t* __restrict__ cnt, long G, long g0, long g1, const
     glm_store<GLM_LANES, PM>(d, r, g, G, ln, beta, cellbeta, coef, fitted, alpha_w, n_alpha, alpha_out);
 }
 
-// Second pass: one warp per abandoned gene, the gene's counts staged in shared memory (the sweeps then run at shared-memory
-// instead of DRAM latency), the Levenberg work arrays in shared memory as in the first pass.  The fit restarts from the null
-// start; with 32 lanes the sums associate differently than with 8, so the coefficients of these genes differ from an 8-lane
-// fit in the last places: what matters is that the route a gene takes does not depend on the sharding.
-// grid: any; warps stride over the list.  Dynamic shared memory: 4 x (scratch + N ints).
+// Second pass: one BLOCK (4 warps) per abandoned gene.  The gene's counts are staged in shared memory (the sweeps then run
+// at shared-memory instead of DRAM latency); a sweep is split over the design's classes (warp w takes classes w, w + 4, ...:
+// one exp per class, the class's samples over the 32 lanes, butterfly sums), the class sums are left in shared memory and
+// warp 0 assembles deviance, X'WX and X'z from them in class order.  Warp 0 runs edgeR's Levenberg iteration exactly as
+// fit_levenberg does (same lambda schedule, acceptance and stopping rules); the other warps wait for its sweep requests at
+// a named barrier.  Everything that mutates the shared work arrays is done by lane 0 of warp 0 between __syncwarp()s; the
+// other lanes of warp 0 follow the control flow on the same values.  The fit restarts from the null start; its sums
+// associate differently than on 8 lanes, so the coefficients of these few genes differ from an 8-lane fit in the last
+// places: what matters is that the route a gene takes does not depend on the sharding.  Needs the class form (d.ncls > 0).
+// grid: any (blocks stride over the list).  Dynamic shared memory: glm_wide_smem_doubles<PM>() doubles + N ints.
+template <int PM>
+__host__ __device__ constexpr int glm_wide_smem_doubles() { return 3 * (PM * (PM + 1) / 2) + 5 * PM + 96 + 2; }
+__device__ __forceinline__ void glm_wide_bar() { asm volatile("bar.sync 1, 128;" ::: "memory"); }
+
+// class sums of one sweep at the coefficients bsrc for the classes of this warp: cls[c], cls[32+c], cls[64+c] = sum W, sum z, deviance
+__device__ __forceinline__ void glm_wide_classes(const DesignDev& d, const Row& r, const double* bsrc, int warp, int lane,
+                                                 double* cls) {
+    for (int c = warp; c < d.ncls; c += 4) {
+        const int t0 = d.cell_start[c], t1 = d.cell_start[c + 1], k0 = d.rowptr[t0], k1 = d.rowptr[t0 + 1];
+        double eta = r.goff;
+        for (int k = k0; k < k1; ++k) eta += d.cval[k] * bsrc[d.cidx[k]];
+        const double E = exp(eta);
+        double sw = 0, sz = 0, dv = 0;
+        for (int t = t0 + lane; t < t1; t += 32) {
+            const int col = d.col[t];
+            const double mu = E * r.lib(col), y = r.y(col), phi = r.phi(col);
+            dv += unit_nb_deviance(y, mu, phi);
+            const double inv = rcp_pos(1 + mu * phi);
+            sw += mu * inv; sz += (y - mu) * inv;
+        }
+        sw = lane_sum<32>(sw, 0xffffffffu); sz = lane_sum<32>(sz, 0xffffffffu); dv = lane_sum<32>(dv, 0xffffffffu);
+        if (lane == 0) { cls[c] = sw; cls[32 + c] = sz; cls[64 + c] = dv; }
+    }
+}
+
 template <int PM>
 __global__ void __launch_bounds__(128)
 k_glm_fit_wide(const int32_t* __restrict__ cnt, long G, long g0, int N, const double* __restrict__ logoff,
@@ -132,26 +162,146 @@ k_glm_fit_wide(const int32_t* __restrict__ cnt, long G, long g0, int N, const do
                int n_alpha, double* __restrict__ alpha_out, int* __restrict__ iter_hist, const int* __restrict__ strag,
                const int* __restrict__ n_strag, int stage_counts) {
     extern __shared__ __align__(16) double glm_scr[];
-    const int warp = threadIdx.x >> 5, ln = threadIdx.x & 31;
-    double* scr = glm_scr + warp * lev_scratch_doubles<PM>();
-    int32_t* xs = reinterpret_cast<int32_t*>(glm_scr + 4 * lev_scratch_doubles<PM>()) + (long)warp * N;
+    constexpr int PT = PM * (PM + 1) / 2;
+    double* const xtwx = glm_scr;
+    double* const xtwx_new = glm_scr + PT;
+    double* const work = glm_scr + 2 * PT;
+    double* const dl = glm_scr + 3 * PT;
+    double* const dl_new = dl + PM;
+    double* const dbeta = dl + 2 * PM;
+    double* const beta_new = dl + 3 * PM;
+    double* const beta_s = dl + 4 * PM;
+    double* const cls = dl + 5 * PM;                          // [3][32] class sums of the current sweep
+    int* const ctrl = reinterpret_cast<int*>(cls + 96);       // ctrl[0]: 1 = sweep requested, 2 = fit finished; ctrl[1]: 0 = at beta, 1 = at beta_new
+    int32_t* const xs = reinterpret_cast<int32_t*>(cls + 98);
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     const DesignDev d = *design;
+    const int p = d.p, pt = p * (p + 1) / 2;
     const int count = *n_strag;
-    for (int i = blockIdx.x * 4 + warp; i < count; i += gridDim.x * 4) {
+    for (int i = blockIdx.x; i < count; i += gridDim.x) {
         const long g = g0 + strag[i];
-        if (stage_counts) {
-            __syncwarp();
-            for (int c = ln; c < N; c += 32) xs[c] = cnt[g + (long)c * G];
-            __syncwarp();
-        }
+        __syncthreads();                                      // the previous gene of this block is done with the shared arrays
+        if (stage_counts) for (int c = threadIdx.x; c < N; c += blockDim.x) xs[c] = cnt[g + (long)c * G];
+        __syncthreads();
         double goff = goff_in ? goff_in[g] : 0.0;
         if (mode == 1) goff = log(exp(goff) + two_prior_over_meanlib);
         RowSrc src{cnt, G, logoff, mode == 1 ? yadd : nullptr, phi, phi_col, 0.0, stage_counts ? xs : nullptr};
         Row r(src, g, goff);
+        if (warp != 0) {                                      // workers: serve sweep requests until the fit is finished
+            for (;;) {
+                glm_wide_bar();
+                if (ctrl[0] == 2) break;
+                glm_wide_classes(d, r, ctrl[1] ? beta_new : beta_s, warp, lane, cls);
+                glm_wide_bar();
+            }
+            continue;
+        }
+        // ---- warp 0: the Levenberg iteration (glm.cuh fit_levenberg, same rules) ----
+        // one sweep at bsrc: deviance returned, X'WX -> xt, X'z -> dz
+        auto sweep = [&](int at_new, double* xt, double* dz) -> double {
+            if (lane == 0) { ctrl[0] = 1; ctrl[1] = at_new; }
+            __syncwarp();
+            glm_wide_bar();
+            glm_wide_classes(d, r, at_new ? beta_new : beta_s, 0, lane, cls);
+            glm_wide_bar();
+            double dev = 0;
+            for (int c = 0; c < d.ncls; ++c) dev += cls[64 + c];
+            if (lane == 0) {
+                for (int k = 0; k < pt; ++k) xt[k] = 0;
+                for (int k = 0; k < p; ++k) dz[k] = 0;
+                for (int c = 0; c < d.ncls; ++c) {
+                    const int t0 = d.cell_start[c], k0 = d.rowptr[t0], k1 = d.rowptr[t0 + 1];
+                    const double sw = cls[c], sz = cls[32 + c];
+                    for (int k = k0; k < k1; ++k) {
+                        const int ik = d.cidx[k];
+                        const double vk = d.cval[k];
+                        dz[ik] += vk * sz;
+                        for (int k2 = k0; k2 <= k; ++k2) xt[tri(ik, d.cidx[k2])] += vk * d.cval[k2] * sw;
+                    }
+                }
+            }
+            __syncwarp();
+            return dev;
+        };
+        double ymax = 0, sum_exprs = 0, sum_weight = 0;
+        const double eg0 = exp(r.goff);
+        for (int t = lane; t < d.n; t += 32) {
+            const int c = d.col[t];
+            const double y = r.y(c);
+            if (y > ymax) ymax = y;
+            const double curN = r.lib(c) * eg0, w = curN / (1 + r.phi(c) * curN);
+            sum_exprs += y * w / curN;
+            sum_weight += w;
+        }
+        ymax = lane_max<32>(ymax, 0xffffffffu); sum_exprs = lane_sum<32>(sum_exprs, 0xffffffffu); sum_weight = lane_sum<32>(sum_weight, 0xffffffffu);
+        int sweeps = -1;
+        if (ymax < CBS_LOW_VALUE) {
+            if (lane == 0) for (int k = 0; k < p; ++k) beta_s[k] = nan("");
+            __syncwarp();
+        } else {
+            const double c0 = log(sum_exprs / sum_weight);
+            if (lane == 0) for (int k = 0; k < p; ++k) beta_s[k] = d.start[k] * c0;
+            __syncwarp();
+            double dev = sweep(0, xtwx, dl);
+            double max_info = -1, lambda = 0;
+            int iter = 0;
+            sweeps = 1;
+            while ((++iter) <= 250) {
+                for (int k = 0; k < p; ++k) if (xtwx[tri(k, k)] > max_info) max_info = xtwx[tri(k, k)];
+                if (iter == 1) { lambda = max_info * 1e-6; if (lambda < 1e-13) lambda = 1e-13; }
+                int lev = 0;
+                bool low_dev = false, failed = false;
+                while (++lev) {
+                    for (;;) {
+                        int ok = 0;
+                        if (lane == 0) {
+                            for (int k = 0; k < pt; ++k) work[k] = xtwx[k];
+                            for (int k = 0; k < p; ++k) { work[tri(k, k)] += lambda; dbeta[k] = dl[k]; }
+                            ok = chol_packed(work, p) ? 1 : 0;
+                        }
+                        ok = __shfl_sync(0xffffffffu, ok, 0);
+                        if (ok) break;
+                        lambda *= 10;
+                        if (lambda <= 0) lambda = CBS_RIDICULOUSLY_LOW;
+                    }
+                    if (lane == 0) {
+                        chol_solve_packed(work, p, dbeta);
+                        for (int k = 0; k < p; ++k) beta_new[k] = beta_s[k] + dbeta[k];
+                    }
+                    __syncwarp();
+                    const double dev_new = sweep(1, xtwx_new, dl_new);
+                    ++sweeps;
+                    if (dev_new / ymax < CBS_SUPREMELY_LOW) low_dev = true;
+                    if (dev_new <= dev || low_dev) {
+                        if (lane == 0) for (int k = 0; k < p; ++k) beta_s[k] = beta_new[k];
+                        __syncwarp();
+                        dev = dev_new;
+                        break;
+                    }
+                    lambda *= 2;
+                    if (lambda <= 0) lambda = CBS_RIDICULOUSLY_LOW;
+                    if (lambda / max_info > 1 / CBS_SUPREMELY_LOW) { failed = true; break; }
+                }
+                if (failed || low_dev) break;
+                double divergence = 0;
+                for (int k = 0; k < p; ++k) divergence += dl[k] * dbeta[k];
+                if (divergence < 1e-6) break;
+                if (lev == 1) lambda /= 10;
+                __syncwarp();
+                if (lane == 0) {
+                    for (int k = 0; k < pt; ++k) xtwx[k] = xtwx_new[k];     // information at the accepted coefficients
+                    for (int k = 0; k < p; ++k) dl[k] = dl_new[k];
+                }
+                __syncwarp();
+            }
+        }
+        if (lane == 0) ctrl[0] = 2;
+        __syncwarp();
+        glm_wide_bar();                                       // releases the workers
+        if (iter_hist && lane == 0) atomicAdd(&iter_hist[max(0, min(sweeps, 255))], 1);
         double beta[PM], cellbeta[PM];
-        const int n_sweeps = fit_gene<32, PM>(d, r, beta, cellbeta, ln, 0xffffffffu, scr);
-        if (iter_hist && ln == 0) atomicAdd(&iter_hist[max(0, min(n_sweeps, 255))], 1);
-        glm_store<32, PM>(d, r, g, G, ln, beta, cellbeta, coef, fitted, alpha_w, n_alpha, alpha_out);
+        for (int k = 0; k < p; ++k) { beta[k] = beta_s[k]; cellbeta[k] = 0; }
+        glm_store<32, PM>(d, r, g, G, lane, beta, cellbeta, coef, fitted, alpha_w, n_alpha, alpha_out);
     }
 }
 
@@ -161,7 +311,7 @@ k_glm_fit_wide(const int32_t* __restrict__ cnt, long G, long g0, int N, const do
 void run_glm_fit(const int32_t* cnt, long G, long g0, long g1, int N, const double* d_logoff,
                         const std::vector<double>& h_lib, const double* d_phi, const int* d_phi_col,
                         const DesignDev* d_design, int h_p, const double* d_goff, double prior_count, double* d_coef,
-                        double* d_fitted, const double* d_alpha_w, int n_alpha, double* d_alpha, cudaStream_t st) {
+                        double* d_fitted, const double* d_alpha_w, int n_alpha, double* d_alpha, cudaStream_t st, bool class_form) {
     if (g1 <= g0) return;
     const dim3 grid = grid1(g1 - g0, 128);
     double two_prior = 0;
@@ -180,7 +330,7 @@ void run_glm_fit(const int32_t* cnt, long G, long g0, long g1, int N, const doub
     int* d_hist = g_tune.glm_hist ? g_dev.get<int>("glm_iter_hist", 256) : nullptr;     // zeroed by cbs_get_diag("reset")
     const dim3 lgrid = grid1((g1 - g0) * GLM_LANES, 128);
     // the wide second pass needs the class form of the sweep with shared scratch (every Levenberg design of the pipeline)
-    const bool two_pass = g_tune.glm_scr && g_tune.glm_two_pass;
+    const bool two_pass = g_tune.glm_scr && g_tune.glm_two_pass && class_form;
     int* d_strag = g_dev.get<int>("glm_strag", (size_t)(g1 - g0));
     int* d_nstrag = g_dev.get<int>("glm_nstrag", 1);
     auto launch = [&](const double* yadd, double tp, int mode, double* coef, double* fitted, double* alpha) {
@@ -194,8 +344,8 @@ void run_glm_fit(const int32_t* cnt, long G, long g0, long g1, int N, const doub
                        d_phi_col, d_design, d_goff, mode, coef, fitted, d_alpha_w, n_alpha, alpha, g_tune.glm_scr ? 1 : 0, d_hist, \
                        two_pass ? d_strag : (int*)nullptr, d_nstrag); \
             if (two_pass) { \
-                const int stage = N <= 8192; \
-                const size_t wsmem = 4 * lev_scratch_doubles<PM_>() * sizeof(double) + (stage ? (size_t)4 * N * sizeof(int32_t) : 0); \
+                const int stage = N <= 32768; \
+                const size_t wsmem = glm_wide_smem_doubles<PM_>() * sizeof(double) + (stage ? (size_t)N * sizeof(int32_t) : 0); \
                 t_ctx->set_func_attr((const void*)k_glm_fit_wide<PM_>, cudaFuncAttributeMaxDynamicSharedMemorySize, 160 * 1024); \
                 CBS_LAUNCH(k_glm_fit_wide<PM_>, dim3(64), 128, wsmem, st, cnt, G, g0, N, d_logoff, yadd, tp, d_phi, d_phi_col, d_design, \
                            d_goff, mode, coef, fitted, d_alpha_w, n_alpha, alpha, d_hist, (const int*)d_strag, (const int*)d_nstrag, stage); \
