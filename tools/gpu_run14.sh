@@ -1,0 +1,4 @@
+#!/bin/bash
+O=gpurun_out; mkdir -p $O
+timeout 900 python -m pytest tests -m gpu -x -q -rs > $O/r02_pytest_gpu_14.txt 2>&1; echo "rc=$?" >> $O/r02_pytest_gpu_14.txt
+timeout 900 python bench.py --steps 3 --warmup 3 --no-cpu > $O/r02_bench_c5_14.json 2> $O/r02_bench_c5_14.err; echo "rc=$?" >> $O/r02_bench_c5_14.err
