@@ -129,7 +129,48 @@ k_glm_fit_lanes(const int32_t* __restrict__ cnt, long G, long g0, long g1, const
 // places: what matters is that the route a gene takes does not depend on the sharding.  Needs the class form (d.ncls > 0).
 // grid: any (blocks stride over the list).  Dynamic shared memory: glm_wide_smem_doubles<PM>() doubles + N ints.
 template <int PM>
-__host__ __device__ constexpr int glm_wide_smem_doubles() { return 3 * (PM * (PM + 1) / 2) + 5 * PM + 96 + 2; }
+__host__ __device__ constexpr int glm_wide_smem_doubles() { return 3 * (PM * (PM + 1) / 2) + 5 * PM + 96 + 2 + 32 * PM; }
+
+// chol_packed / chol_solve_packed (glm.cuh) with the rows of a column spread over the lanes of one warp.  Every element goes
+// through the same operations as in the serial routines (the factorisation and the forward substitution in the same order, the
+// back substitution subtracts its terms in the opposite order); a is a shared-memory array, p <= 32.  Returns false (on
+// every lane) when a pivot is <= 0 or NaN.
+__device__ __forceinline__ bool chol_packed_warp(double* a, int p, int lane) {
+    for (int j = 0; j < p; ++j) {
+        int ok = 1;
+        if (lane == 0) {
+            double ajj = a[tri(j, j)];
+            for (int k = 0; k < j; ++k) ajj -= a[tri(j, k)] * a[tri(j, k)];
+            ok = ajj > 0;
+            if (ok) a[tri(j, j)] = sqrt(ajj);
+        }
+        ok = __shfl_sync(0xffffffffu, ok, 0);
+        if (!ok) return false;
+        __syncwarp();
+        const int c = j + 1 + lane;
+        if (c < p) {
+            double v = a[tri(c, j)];
+            for (int k = 0; k < j; ++k) v -= a[tri(j, k)] * a[tri(c, k)];
+            a[tri(c, j)] = v / a[tri(j, j)];
+        }
+        __syncwarp();
+    }
+    return true;
+}
+__device__ __forceinline__ void chol_solve_packed_warp(const double* a, int p, double* b, int lane) {
+    for (int i = 0; i < p; ++i) {                              // forward: b[c] -= a[c][i] b[i] in the order i = 0, 1, ... for every c
+        if (lane == i) b[i] = b[i] / a[tri(i, i)];
+        __syncwarp();
+        if (lane > i && lane < p) b[lane] -= a[tri(lane, i)] * b[i];
+        __syncwarp();
+    }
+    for (int i = p - 1; i >= 0; --i) {                         // backward: b[c] -= a[i][c] b[i] in the order i = p-1, p-2, ...
+        if (lane == i) b[i] = b[i] / a[tri(i, i)];
+        __syncwarp();
+        if (lane < i) b[lane] -= a[tri(i, lane)] * b[i];
+        __syncwarp();
+    }
+}
 __device__ __forceinline__ void glm_wide_bar() { asm volatile("bar.sync 1, 128;" ::: "memory"); }
 
 // class sums of one sweep at the coefficients bsrc for the classes of this warp: cls[c], cls[32+c], cls[64+c] = sum W, sum z, deviance
@@ -173,11 +214,18 @@ k_glm_fit_wide(const int32_t* __restrict__ cnt, long G, long g0, int N, const do
     double* const beta_s = dl + 4 * PM;
     double* const cls = dl + 5 * PM;                          // [3][32] class sums of the current sweep
     int* const ctrl = reinterpret_cast<int*>(cls + 96);       // ctrl[0]: 1 = sweep requested, 2 = fit finished; ctrl[1]: 0 = at beta, 1 = at beta_new
-    int32_t* const xs = reinterpret_cast<int32_t*>(cls + 98);
+    double* const Xc = cls + 98;                              // [32][PM] dense design row of every class
+    int32_t* const xs = reinterpret_cast<int32_t*>(Xc + 32 * PM);
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     const DesignDev d = *design;
     const int p = d.p, pt = p * (p + 1) / 2;
     const int count = *n_strag;
+    for (int k = threadIdx.x; k < 32 * PM; k += blockDim.x) Xc[k] = 0;
+    __syncthreads();
+    for (int c = threadIdx.x; c < d.ncls; c += blockDim.x) {
+        const int t0 = d.cell_start[c];
+        for (int k = d.rowptr[t0]; k < d.rowptr[t0 + 1]; ++k) Xc[c * PM + d.cidx[k]] = d.cval[k];
+    }
     for (int i = blockIdx.x; i < count; i += gridDim.x) {
         const long g = g0 + strag[i];
         __syncthreads();                                      // the previous gene of this block is done with the shared arrays
@@ -206,18 +254,20 @@ k_glm_fit_wide(const int32_t* __restrict__ cnt, long G, long g0, int N, const do
             glm_wide_bar();
             double dev = 0;
             for (int c = 0; c < d.ncls; ++c) dev += cls[64 + c];
-            if (lane == 0) {
-                for (int k = 0; k < pt; ++k) xt[k] = 0;
-                for (int k = 0; k < p; ++k) dz[k] = 0;
-                for (int c = 0; c < d.ncls; ++c) {
-                    const int t0 = d.cell_start[c], k0 = d.rowptr[t0], k1 = d.rowptr[t0 + 1];
-                    const double sw = cls[c], sz = cls[32 + c];
-                    for (int k = k0; k < k1; ++k) {
-                        const int ik = d.cidx[k];
-                        const double vk = d.cval[k];
-                        dz[ik] += vk * sz;
-                        for (int k2 = k0; k2 <= k; ++k2) xt[tri(ik, d.cidx[k2])] += vk * d.cval[k2] * sw;
-                    }
+            // X'WX and X'z from the class sums, one packed entry per lane and round, classes added in order (the zeros of
+            // the dense design rows add exact zeros: the same sums as the sparse accumulation of lev_sweep)
+            for (int e = lane; e < pt + p; e += 32) {
+                double s = 0;
+                if (e < pt) {
+                    int i2 = 0;
+                    while ((i2 + 1) * (i2 + 2) / 2 <= e) ++i2;
+                    const int j2 = e - i2 * (i2 + 1) / 2;
+                    for (int c = 0; c < d.ncls; ++c) s += Xc[c * PM + i2] * Xc[c * PM + j2] * cls[c];
+                    xt[e] = s;
+                } else {
+                    const int i2 = e - pt;
+                    for (int c = 0; c < d.ncls; ++c) s += Xc[c * PM + i2] * cls[32 + c];
+                    dz[i2] = s;
                 }
             }
             __syncwarp();
@@ -253,27 +303,22 @@ k_glm_fit_wide(const int32_t* __restrict__ cnt, long G, long g0, int N, const do
                 bool low_dev = false, failed = false;
                 while (++lev) {
                     for (;;) {
-                        int ok = 0;
-                        if (lane == 0) {
-                            for (int k = 0; k < pt; ++k) work[k] = xtwx[k];
-                            for (int k = 0; k < p; ++k) { work[tri(k, k)] += lambda; dbeta[k] = dl[k]; }
-                            ok = chol_packed(work, p) ? 1 : 0;
-                        }
-                        ok = __shfl_sync(0xffffffffu, ok, 0);
-                        if (ok) break;
+                        for (int k = lane; k < pt; k += 32) work[k] = xtwx[k];
+                        __syncwarp();
+                        if (lane < p) { work[tri(lane, lane)] += lambda; dbeta[lane] = dl[lane]; }
+                        __syncwarp();
+                        if (chol_packed_warp(work, p, lane)) break;
                         lambda *= 10;
                         if (lambda <= 0) lambda = CBS_RIDICULOUSLY_LOW;
                     }
-                    if (lane == 0) {
-                        chol_solve_packed(work, p, dbeta);
-                        for (int k = 0; k < p; ++k) beta_new[k] = beta_s[k] + dbeta[k];
-                    }
+                    chol_solve_packed_warp(work, p, dbeta, lane);
+                    if (lane < p) beta_new[lane] = beta_s[lane] + dbeta[lane];
                     __syncwarp();
                     const double dev_new = sweep(1, xtwx_new, dl_new);
                     ++sweeps;
                     if (dev_new / ymax < CBS_SUPREMELY_LOW) low_dev = true;
                     if (dev_new <= dev || low_dev) {
-                        if (lane == 0) for (int k = 0; k < p; ++k) beta_s[k] = beta_new[k];
+                        if (lane < p) beta_s[lane] = beta_new[lane];
                         __syncwarp();
                         dev = dev_new;
                         break;
@@ -288,10 +333,8 @@ k_glm_fit_wide(const int32_t* __restrict__ cnt, long G, long g0, int N, const do
                 if (divergence < 1e-6) break;
                 if (lev == 1) lambda /= 10;
                 __syncwarp();
-                if (lane == 0) {
-                    for (int k = 0; k < pt; ++k) xtwx[k] = xtwx_new[k];     // information at the accepted coefficients
-                    for (int k = 0; k < p; ++k) dl[k] = dl_new[k];
-                }
+                for (int k = lane; k < pt; k += 32) xtwx[k] = xtwx_new[k];     // information at the accepted coefficients
+                if (lane < p) dl[lane] = dl_new[lane];
                 __syncwarp();
             }
         }
