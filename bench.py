@@ -307,7 +307,7 @@ def run_native(args):
     if world > 1:
         dist.all_reduce(t_pg, op=dist.ReduceOp.MAX)
     pageable = {"value": float(G0) * N * args.steps / (float(t_pg.item()) * 1e-3), "unit": UNIT, "ms_per_step": float(t_pg.item()) / args.steps,
-                "h2d_bytes_per_step": int(G0) * N * 8 * world, "d2h_bytes_per_step": int(G0) * N * 8,
+                "h2d_bytes_per_step": int(G0) * N * 8, "d2h_bytes_per_step": int(G0) * N * 8,
                 "note": "pageable (not pinned) float64 count matrix in, float64 matrix out, host wall clock: the buffers an R caller has"}
     del pg_counts, pg_adj
     c2_pair = None
@@ -322,7 +322,7 @@ def run_native(args):
                 "warmup": args.warmup, "ms_per_step": ms_val / args.steps, "higher_is_better": True, "scaling": "strong",
                 "vs_baseline": None, "dtype": "f64", "data": "synthetic", "config": describe(case, d), "clocks": clocks,
                 "e2e": {"value": units / (ms_e2e * 1e-3), "unit": UNIT, "ms_per_step": ms_e2e / args.steps,
-                        "h2d_bytes_per_step": int(G0) * N * 4 * world, "d2h_bytes_per_step": int(G0) * N * 8,
+                        "h2d_bytes_per_step": int(G0) * N * 4, "d2h_bytes_per_step": int(G0) * N * 8,
                         "checksum": checksum},
                 "gpu_launches": int(launches)}
         line["config"]["l2"] = "L2 flushed between timed steps" if small else "inputs larger than L2 (%.0f MB counts)" % (G0 * N * 4 / 1e6)

@@ -579,11 +579,15 @@ __global__ void k_mcg_list_all(int NJ, int* __restrict__ srclist, int* __restric
 // below e^-40 of the row's largest weight, the bound the fold in k_mc_gemm applies anyway.  grid (ntiles64), block 256,
 // NJ bytes of dynamic shared memory.  The 4 thread groups of a block split the source tiles.
 __global__ void __launch_bounds__(256)
-k_mcg_list_screened(const float* __restrict__ hi, const float* __restrict__ lo, long rows, int NJ, float prune,
+k_mcg_list_screened(const float* __restrict__ hi, const float* __restrict__ lo, long rows, int NJ, float prune, McgOwn own,
                     int* __restrict__ srclist, int* __restrict__ count) {
     extern __shared__ unsigned char flag_s[];                  // [NJ]
     __shared__ float mx[4][MCG_TI];
     const int t = blockIdx.x, r = threadIdx.x & (MCG_TI - 1), q = threadIdx.x / MCG_TI;
+    if (!own.owns_tile64(t)) {                                 // another rank's targets: no bounds were computed here
+        if (threadIdx.x == 0) count[t] = 0;
+        return;
+    }
     const long i = (long)t * MCG_TI + r;
     float m = -INFINITY;
 #pragma unroll 4

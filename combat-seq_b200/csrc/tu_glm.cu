@@ -52,7 +52,10 @@ k_glm_fit(const int32_t* __restrict__ cnt, long G, long g0, long g1, const doubl
 // Used for designs with p <= GLM_LANES_PMAX columns.  use_scr: the Levenberg work arrays (3 packed X'WX + 4 vectors) are
 // one shared-memory copy per gene instead of a local-memory copy per lane (ncu, round 1: the local copies made 10.9 GB of
 // DRAM traffic per launch, 15x the algorithmic bytes); dynamic shared memory = (128 / GLM_LANES) * lev_scratch_doubles<PM>().
-constexpr int GLM_LANES = 8;
+#ifndef CBS_GLM_LANES_N
+#define CBS_GLM_LANES_N 8
+#endif
+constexpr int GLM_LANES = CBS_GLM_LANES_N;
 constexpr int GLM_LANES_PMAX = 16;
 #ifndef CBS_GLM_MINBLOCKS
 #define CBS_GLM_MINBLOCKS 5
@@ -88,14 +91,31 @@ __device__ __forceinline__ void glm_store(const DesignDev& d, const Row& r, long
 // than its neighbours': it alone set the duration of a launch once the genes were spread over 8 GPUs (7 ms per launch
 // whatever the shard).  The decision depends on the gene only, so it is the same for every sharding.
 constexpr int GLM_SWEEP_CAP = 9;
+// One launch can carry two independent fits of the same genes (blockIdx.y picks the job): the plain fit and the predFC fit
+// of a glmFit(prior.count > 0) call read the same counts and do not depend on each other, and once the genes are spread
+// over several GPUs a launch is a fraction of a wave whose duration is the latency of one fit, not its throughput.
+struct GlmJob {
+    const double* yadd; double two_prior_over_meanlib; int mode;
+    double* coef; double* fitted; double* alpha_out; int* strag; int* n_strag;
+};
+struct GlmJobs { GlmJob j[2]; };
+__device__ __forceinline__ GlmJob glm_pick_job(const GlmJobs& jobs) {
+    GlmJob a = jobs.j[0];
+    if (blockIdx.y) a = jobs.j[1];
+    return a;
+}
 template <int PM>                                            // PM >= design columns: sizes the per-thread packed X'WX (local memory)
 __global__ void __launch_bounds__(128, CBS_GLM_MINBLOCKS)
 k_glm_fit_lanes(const int32_t* __restrict__ cnt, long G, long g0, long g1, const double* __restrict__ logoff,
-                const double* __restrict__ yadd, double two_prior_over_meanlib, const double* __restrict__ phi,
+                const __grid_constant__ GlmJobs jobs, const double* __restrict__ phi,
                 const int* __restrict__ phi_col, const DesignDev* __restrict__ design, const double* __restrict__ goff_in,
-                int mode, double* __restrict__ coef, double* __restrict__ fitted, const double* __restrict__ alpha_w,
-                int n_alpha, double* __restrict__ alpha_out, int use_scr, int* __restrict__ iter_hist,
-                int* __restrict__ strag, int* __restrict__ n_strag) {
+                const double* __restrict__ alpha_w, int n_alpha, int use_scr, int* __restrict__ iter_hist) {
+    const GlmJob jb = glm_pick_job(jobs);
+    const double* __restrict__ yadd = jb.yadd;
+    const double two_prior_over_meanlib = jb.two_prior_over_meanlib;
+    const int mode = jb.mode;
+    double* __restrict__ coef = jb.coef; double* __restrict__ fitted = jb.fitted; double* __restrict__ alpha_out = jb.alpha_out;
+    int* __restrict__ strag = jb.strag; int* __restrict__ n_strag = jb.n_strag;
     const long slot = ((long)blockIdx.x * blockDim.x + threadIdx.x) / GLM_LANES;
     const long g = g0 + slot;
     const int ln = threadIdx.x % GLM_LANES;
@@ -197,11 +217,15 @@ __device__ __forceinline__ void glm_wide_classes(const DesignDev& d, const Row& 
 template <int PM>
 __global__ void __launch_bounds__(128)
 k_glm_fit_wide(const int32_t* __restrict__ cnt, long G, long g0, int N, const double* __restrict__ logoff,
-               const double* __restrict__ yadd, double two_prior_over_meanlib, const double* __restrict__ phi,
+               const __grid_constant__ GlmJobs jobs, const double* __restrict__ phi,
                const int* __restrict__ phi_col, const DesignDev* __restrict__ design, const double* __restrict__ goff_in,
-               int mode, double* __restrict__ coef, double* __restrict__ fitted, const double* __restrict__ alpha_w,
-               int n_alpha, double* __restrict__ alpha_out, int* __restrict__ iter_hist, const int* __restrict__ strag,
-               const int* __restrict__ n_strag, int stage_counts) {
+               const double* __restrict__ alpha_w, int n_alpha, int* __restrict__ iter_hist, int stage_counts) {
+    const GlmJob jb = glm_pick_job(jobs);
+    const double* __restrict__ yadd = jb.yadd;
+    const double two_prior_over_meanlib = jb.two_prior_over_meanlib;
+    const int mode = jb.mode;
+    double* __restrict__ coef = jb.coef; double* __restrict__ fitted = jb.fitted; double* __restrict__ alpha_out = jb.alpha_out;
+    const int* __restrict__ strag = jb.strag; const int* __restrict__ n_strag = jb.n_strag;
     extern __shared__ __align__(16) double glm_scr[];
     constexpr int PT = PM * (PM + 1) / 2;
     double* const xtwx = glm_scr;
@@ -374,36 +398,47 @@ void run_glm_fit(const int32_t* cnt, long G, long g0, long g1, int N, const doub
     const dim3 lgrid = grid1((g1 - g0) * GLM_LANES, 128);
     // the wide second pass needs the class form of the sweep with shared scratch (every Levenberg design of the pipeline)
     const bool two_pass = g_tune.glm_scr && g_tune.glm_two_pass && class_form;
-    int* d_strag = g_dev.get<int>("glm_strag", (size_t)(g1 - g0));
-    int* d_nstrag = g_dev.get<int>("glm_nstrag", 1);
-    auto launch = [&](const double* yadd, double tp, int mode, double* coef, double* fitted, double* alpha) {
-        // one shared-memory copy of the Levenberg work arrays per gene (16 genes per block)
-#define CBS_GLM_LANES(PM_) do { \
-            const size_t smem = g_tune.glm_scr ? (size_t)(128 / GLM_LANES) * lev_scratch_doubles<PM_>() * sizeof(double) : 0; \
-            t_ctx->set_func_attr((const void*)k_glm_fit_lanes<PM_>, cudaFuncAttributeMaxDynamicSharedMemorySize, \
-                                 (int)((128 / GLM_LANES) * lev_scratch_doubles<PM_>() * sizeof(double))); \
-            CBS_CUDA(cudaMemsetAsync(d_nstrag, 0, sizeof(int), st)); \
-            CBS_LAUNCH(k_glm_fit_lanes<PM_>, lgrid, 128, smem, st, cnt, G, g0, g1, d_logoff, yadd, tp, d_phi, \
-                       d_phi_col, d_design, d_goff, mode, coef, fitted, d_alpha_w, n_alpha, alpha, g_tune.glm_scr ? 1 : 0, d_hist, \
-                       two_pass ? d_strag : (int*)nullptr, d_nstrag); \
-            if (two_pass) { \
-                const int stage = N <= 32768; \
-                const size_t wsmem = glm_wide_smem_doubles<PM_>() * sizeof(double) + (stage ? (size_t)N * sizeof(int32_t) : 0); \
-                t_ctx->set_func_attr((const void*)k_glm_fit_wide<PM_>, cudaFuncAttributeMaxDynamicSharedMemorySize, 160 * 1024); \
-                CBS_LAUNCH(k_glm_fit_wide<PM_>, dim3(64), 128, wsmem, st, cnt, G, g0, N, d_logoff, yadd, tp, d_phi, d_phi_col, d_design, \
-                           d_goff, mode, coef, fitted, d_alpha_w, n_alpha, alpha, d_hist, (const int*)d_strag, (const int*)d_nstrag, stage); \
-            } } while (0)
-        if (lanes) {
-            if (h_p <= 4) CBS_GLM_LANES(4); else if (h_p <= 8) CBS_GLM_LANES(8); else if (h_p <= 12) CBS_GLM_LANES(12); else CBS_GLM_LANES(16);
-        } else
-#undef CBS_GLM_LANES
-            CBS_LAUNCH(k_glm_fit, grid, 128, 0, st, cnt, G, g0, g1, d_logoff, yadd, tp, d_phi, d_phi_col, d_design,
-                       d_goff, mode, coef, fitted, d_alpha_w, n_alpha, alpha);
+    int* d_strag = g_dev.get<int>("glm_strag", 2 * (size_t)(g1 - g0));
+    int* d_nstrag = g_dev.get<int>("glm_nstrag", 2);
+    // the fits this call asks for: the plain one (fitted values, or everything when prior_count == 0) and the predFC one
+    GlmJobs jobs{};
+    int nj = 0;
+    auto add_job = [&](const double* yadd, double tp, int mode, double* coef, double* fitted, double* alpha) {
+        jobs.j[nj] = GlmJob{yadd, tp, mode, coef, fitted, alpha, two_pass ? d_strag + (size_t)nj * (g1 - g0) : (int*)nullptr,
+                            d_nstrag + nj};
+        ++nj;
     };
     if (d_fitted || (prior_count <= 0 && (d_coef || d_alpha)))
-        launch(nullptr, 0.0, 0, prior_count > 0 ? (double*)nullptr : d_coef, d_fitted, prior_count > 0 ? (double*)nullptr : d_alpha);
+        add_job(nullptr, 0.0, 0, prior_count > 0 ? (double*)nullptr : d_coef, d_fitted, prior_count > 0 ? (double*)nullptr : d_alpha);
     if (prior_count > 0 && (d_coef || d_alpha))
-        launch(d_yadd, two_prior, 1, d_coef, (double*)nullptr, d_alpha);
+        add_job(d_yadd, two_prior, 1, d_coef, (double*)nullptr, d_alpha);
+    if (!nj) return;
+    if (nj == 1) jobs.j[1] = jobs.j[0];
+    if (!lanes) {
+        for (int k = 0; k < nj; ++k) {
+            const GlmJob& jb = jobs.j[k];
+            CBS_LAUNCH(k_glm_fit, grid, 128, 0, st, cnt, G, g0, g1, d_logoff, jb.yadd, jb.two_prior_over_meanlib, d_phi, d_phi_col,
+                       d_design, d_goff, jb.mode, jb.coef, jb.fitted, d_alpha_w, n_alpha, jb.alpha_out);
+        }
+        return;
+    }
+    // one shared-memory copy of the Levenberg work arrays per gene (16 genes per block)
+#define CBS_GLM_LANES(PM_) do { \
+        const size_t smem = g_tune.glm_scr ? (size_t)(128 / GLM_LANES) * lev_scratch_doubles<PM_>() * sizeof(double) : 0; \
+        t_ctx->set_func_attr((const void*)k_glm_fit_lanes<PM_>, cudaFuncAttributeMaxDynamicSharedMemorySize, \
+                             (int)((128 / GLM_LANES) * lev_scratch_doubles<PM_>() * sizeof(double))); \
+        CBS_CUDA(cudaMemsetAsync(d_nstrag, 0, 2 * sizeof(int), st)); \
+        CBS_LAUNCH(k_glm_fit_lanes<PM_>, dim3(lgrid.x, (unsigned)nj), 128, smem, st, cnt, G, g0, g1, d_logoff, jobs, d_phi, \
+                   d_phi_col, d_design, d_goff, d_alpha_w, n_alpha, g_tune.glm_scr ? 1 : 0, d_hist); \
+        if (two_pass) { \
+            const int stage = N <= 32768; \
+            const size_t wsmem = glm_wide_smem_doubles<PM_>() * sizeof(double) + (stage ? (size_t)N * sizeof(int32_t) : 0); \
+            t_ctx->set_func_attr((const void*)k_glm_fit_wide<PM_>, cudaFuncAttributeMaxDynamicSharedMemorySize, 160 * 1024); \
+            CBS_LAUNCH(k_glm_fit_wide<PM_>, dim3(64, (unsigned)nj), 128, wsmem, st, cnt, G, g0, N, d_logoff, jobs, d_phi, d_phi_col, \
+                       d_design, d_goff, d_alpha_w, n_alpha, d_hist, stage); \
+        } } while (0)
+    if (h_p <= 4) CBS_GLM_LANES(4); else if (h_p <= 8) CBS_GLM_LANES(8); else if (h_p <= 12) CBS_GLM_LANES(12); else CBS_GLM_LANES(16);
+#undef CBS_GLM_LANES
 }
 
 }  // namespace cbs

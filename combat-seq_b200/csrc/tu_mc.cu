@@ -137,7 +137,7 @@ static McPlan plan_mc_gemm(const int32_t* cnt, long G, int n, const int* d_cols,
         if (screened) {
             t_ctx->set_func_attr((const void*)k_mcg_list_screened, cudaFuncAttributeMaxDynamicSharedMemorySize, 64 * 1024);
             CBS_LAUNCH(k_mcg_list_screened, dim3((unsigned)ntiles64), 256, (size_t)NJ, st, hi, lo, sh.rows, (int)NJ,
-                       (float)MCG_PRUNE, pl.srclist, pl.count);
+                       (float)MCG_PRUNE, own, pl.srclist, pl.count);
         }
     }
     if (!screened) CBS_LAUNCH(k_mcg_list_all, dim3((unsigned)ntiles64), 128, 0, st, (int)NJ, pl.srclist, pl.count);
