@@ -187,24 +187,13 @@ k_apl_lanes(const int32_t* __restrict__ cnt, long G, long g0, long g1, const dou
                 if (cbw[l] == cbw[l] && cbw[l] > -1e7) cur = cbw[l];
                 for (int it = 0; it < 50; ++it) {
                     const double ec = exp(cur);
-                    // two accumulator pairs (alternate samples): the sums are dependent DADD chains otherwise
-                    double dl = 0, info = 0, dl1 = 0, info1 = 0;
-                    int t = t0 + ln;
-#pragma unroll 2
-                    for (; t + APLL_LANES < t1; t += 2 * APLL_LANES) {
-                        const double mu = ec * lib_s[t], inv = rcp_pos(1 + mu * phi);
-                        const double mv = ec * lib_s[t + APLL_LANES], inw = rcp_pos(1 + mv * phi);
-                        dl += (y[t] - mu) * inv;
-                        info += mu * inv;
-                        dl1 += (y[t + APLL_LANES] - mv) * inw;
-                        info1 += mv * inw;
-                    }
-                    if (t < t1) {
+                    double dl = 0, info = 0;
+#pragma unroll 4
+                    for (int t = t0 + ln; t < t1; t += APLL_LANES) {         // (independent reciprocal chains: the loop is latency-bound)
                         const double mu = ec * lib_s[t], inv = rcp_pos(1 + mu * phi);
                         dl += (y[t] - mu) * inv;
                         info += mu * inv;
                     }
-                    dl += dl1; info += info1;
                     dl = lane_sum<APLL_LANES>(dl, gm); info = lane_sum<APLL_LANES>(info, gm);
                     const double step = dl / info;                // (info may be 0 or tiny for a degenerate cell: the full division)
                     cur += step;
