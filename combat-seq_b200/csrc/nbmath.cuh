@@ -434,7 +434,7 @@ CBS_HD double nb_quantile_fast(double p, double size, double prob) {
 
 // Small counts: both distribution functions by direct summation of the pmf recurrence from 0,
 //   pmf(0) = prob^size,  pmf(j+1) = pmf(j) (j + size)/(j + 1) q,   F(k) = sum_{j<=k} pmf(j),
-// four FP64 instructions per term with the reciprocals 1/(j+1) from a table, against ~1500 for one continued fraction:
+// three FP64 instructions per term with the reciprocals 1/(j+1) from a table, against ~1500 for one continued fraction:
 // p = F_old(x - 1) costs x terms and the quantile is found by summing the NEW distribution until it reaches
 // p (1 - 64 eps) (no Cornish-Fisher start, no refinement).  Each sum carries a relative error below 1e-13 (term
 // recurrence + exp(size log prob)); whenever a decision (the |p - 1| < 1e-4 pass-through, F_new(y) >= p') is closer than
@@ -444,24 +444,29 @@ constexpr int MQ_INV_N = 1024;
 constexpr double MQ_SMALL_X = 320.0;
 CBS_HD bool match_small(double x, double old_mu, double so, double new_mu, double sn, const double* __restrict__ inv, double* out) {
     const int xi = (int)x;                                       // 2 <= x <= MQ_SMALL_X
+    if (so < 0.05 || sn < 0.05) return false;                    // (the DFMA form of the term ratio cancels for sizes near 0)
     const double qo = old_mu / (so + old_mu);
     double f = exp(-so * log1p(old_mu / so));                    // pmf_old(0) = (so / (so + mu))^so
     if (!(f > 1e-250)) return false;
+    // ratio of consecutive terms: (j + s) q / (j + 1) = q + q (s - 1) / (j + 1): one DFMA on the table entry
+    const double ao = qo * (so - 1);
     double F = f;
-    for (int j = 0; j < xi - 1; ++j) { f *= (j + so) * inv[j + 1] * qo; F += f; }      // F = P_old(X <= x - 1)
+    for (int j = 1; j < xi; ++j) { f *= fma(ao, inv[j], qo); F += f; }      // F = P_old(X <= x - 1)
     const double d1 = fabs(F - 1);
     if (fabs(d1 - 1e-4) < 1e-11 || !(F > 0)) return false;
     if (d1 < 1e-4) { *out = x; return true; }                    // helper_seq.R:54-56
     const double qn = new_mu / (sn + new_mu);
     double g = exp(-sn * log1p(new_mu / sn));
     if (!(g > 1e-250)) return false;
+    const double an = qn * (sn - 1);
     const double pp = F * (1 - 64 * DBL_EPSILON);
     double Fn = g, Fm = 0;
     int y = 0;
     while (Fn < pp) {
         if (y >= MQ_INV_N - 2) return false;
-        g *= (y + sn) * inv[y + 1] * qn;
-        ++y; Fm = Fn; Fn += g;
+        ++y;
+        g *= fma(an, inv[y], qn);
+        Fm = Fn; Fn += g;
     }
     const double tol = 1e-12 * fmax(Fn, pp);
     if (fabs(Fn - pp) <= tol || (y > 0 && fabs(Fm - pp) <= tol)) return false;

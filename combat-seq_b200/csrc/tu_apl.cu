@@ -95,8 +95,17 @@ __global__ void k_fill_apl(double* __restrict__ p, long n, double v) {
 // sum of lgamma(y + 1)) is computed once per gene.  Used when the batch's design is one-way (every within-batch design of
 // the BASELINE configs but C3b), p <= APLL_PM cells and n <= APLL_MAXN samples; anything else takes k_apl.
 constexpr int APLL_PM = 4, APLL_MAXN = 512;
+constexpr int APLL_WS = APLL_PM + 1;      // doubles per (design, gene) of the warm-start array: the cells' coefficients, sum lgamma(y + 1)
 struct AplGroups { int n; int start[APL_MAX_EVALS + 1]; };      // evaluations [start[k], start[k+1]) share one design
+// (Measured and dropped: staging the counts as int32 and converting on use, which halves the shared memory and lets 5-6 blocks
+// share an SM instead of 3, is 1-16 % slower on C5: the kernel is bound by its dependent FP64 chains, not by occupancy.)
+typedef double apl_stage_t;
 __host__ __device__ inline int apll_row_stride(int n, int lanes) { return (n + 15) / 16 * 16 + lanes; }     // = lanes mod 16: the 16 / lanes genes of a half-warp hit disjoint banks
+__device__ __forceinline__ double apl_yval(const apl_stage_t* y, int t) { return y[t]; }
+__host__ __device__ inline size_t apll_smem_bytes(int n, int lanes) {
+    const size_t rows = ((size_t)(128 / lanes) * apll_row_stride(n, lanes) * sizeof(apl_stage_t) + 15) / 16 * 16;
+    return rows + 3 * (size_t)n * sizeof(double);
+}
 
 template <int APLL_LANES>
 __global__ void __launch_bounds__(128)
@@ -105,13 +114,13 @@ k_apl_lanes(const int32_t* __restrict__ cnt, long G, long g0, long g1, const dou
             double* __restrict__ apl, const double* __restrict__ lgfact, const double* __restrict__ lgr,
             double* __restrict__ warm) {
     constexpr int APLL_GENES = 128 / APLL_LANES;
-    extern __shared__ double apl_sm[];
+    extern __shared__ __align__(16) unsigned char apl_sm[];
     const int e0 = GR.start[blockIdx.y], e1 = GR.start[blockIdx.y + 1];
     const int di = L.design[e0];
     const DesignDev d = designs[di];
     const int n = d.n, p = d.p, ns = apll_row_stride(n, APLL_LANES);
-    double* y_s = apl_sm;                       // [genes][ns]
-    double* lib_s = apl_sm + APLL_GENES * ns;   // [n] library sizes, [n] log library sizes, [n] columns (design order)
+    apl_stage_t* y_s = reinterpret_cast<apl_stage_t*>(apl_sm);                       // [genes][ns]
+    double* lib_s = reinterpret_cast<double*>(apl_sm + ((size_t)APLL_GENES * ns * sizeof(apl_stage_t) + 15) / 16 * 16);   // [n] library sizes, [n] log library sizes, [n] columns (design order)
     double* off_s = lib_s + n;
     int* col_s = reinterpret_cast<int*>(off_s + n);
     const long gbase = g0 + (long)blockIdx.x * APLL_GENES;
@@ -142,34 +151,43 @@ k_apl_lanes(const int32_t* __restrict__ cnt, long G, long g0, long g1, const dou
         for (int e = e0 + ln; e < e1; e += APLL_LANES) apl[(long)e * G + g] = 0.0;
         return;
     }
-    const double* y = y_s + gslot * ns;
-    // dispersion-independent: glm_one_group's start value per cell and sum_s lgamma(y_s + 1)
-    double start0[APLL_PM];
-    double sum_lgy1 = 0;
-#pragma unroll
-    for (int l = 0; l < APLL_PM; ++l) {
-        if (l >= p) break;
-        const int t0 = d.cell_start[l], t1 = d.cell_start[l + 1];
-        double cur = 0, nz = 0;
-        for (int t = t0 + ln; t < t1; t += APLL_LANES) {
-            const double yy = y[t];
-            if (yy > CBS_LOW_VALUE) { cur += yy / lib_s[t]; nz = 1; }
-            sum_lgy1 += (lgfact && yy < (double)LGFACT_N) ? lgfact[(int)yy] : lgamma(yy + 1);
-        }
-        cur = lane_sum<APLL_LANES>(cur, gm); nz = lane_max<APLL_LANES>(nz, gm);
-        start0[l] = nz > 0 ? log(cur / (double)(t1 - t0)) : -INFINITY;
-    }
-    sum_lgy1 = lane_sum<APLL_LANES>(sum_lgy1, gm);
-
+    const apl_stage_t* y = y_s + gslot * ns;
     // Newton start of every cell: glm_one_group's own start value for the first evaluation of a gene, afterwards the
     // coefficient the previous evaluation converged to (the previous grid point, or the previous Brent abscissa of the batch
-    // through `warm`, [design][gene][cell]).  The iteration still runs to |step| < 1e-10, so it ends at the same root
-    // (the likelihood is evaluated at a stationary point: a 1e-10 difference in the coefficient moves it by 1e-20), in 2-3
-    // steps instead of 6-9.
+    // through `warm`, [design][gene][cells, sum lgamma(y + 1)]).  The iteration still runs to |step| < 1e-10, so it ends at the
+    // same root (the likelihood is evaluated at a stationary point: a 1e-10 difference in the coefficient moves it by 1e-20),
+    // in 2-3 steps instead of 6-9.  A cell without counts has no root: its coefficient is -1e8 in `warm` as in the result.
     double cbw[APLL_PM];
-    double* wg = warm ? warm + ((long)di * G + g) * APLL_PM : nullptr;
+    double* wg = warm ? warm + ((long)di * G + g) * APLL_WS : nullptr;
 #pragma unroll
     for (int l = 0; l < APLL_PM; ++l) cbw[l] = (wg && l < p) ? wg[l] : NAN;
+    // dispersion-independent: glm_one_group's start value per cell and sum_s lgamma(y_s + 1); both are skipped from the second
+    // Brent round on (ncu: a fifth of a round's stall samples), the sum comes back from `warm`
+    double start0[APLL_PM];
+    double sum_lgy1 = wg ? wg[APLL_PM] : NAN;
+    bool cached = sum_lgy1 == sum_lgy1;
+#pragma unroll
+    for (int l = 0; l < APLL_PM; ++l) if (l < p && !(cbw[l] == cbw[l])) cached = false;
+    if (cached) {
+#pragma unroll
+        for (int l = 0; l < APLL_PM; ++l) start0[l] = cbw[l] > -1e7 ? 0.0 : -INFINITY;     // (only "has counts" matters: cbw is the start)
+    } else {
+        sum_lgy1 = 0;
+#pragma unroll
+        for (int l = 0; l < APLL_PM; ++l) {
+            if (l >= p) break;
+            const int t0 = d.cell_start[l], t1 = d.cell_start[l + 1];
+            double cur = 0, nz = 0;
+            for (int t = t0 + ln; t < t1; t += APLL_LANES) {
+                const double yy = apl_yval(y, t);
+                if (yy > CBS_LOW_VALUE) { cur += yy / lib_s[t]; nz = 1; }
+                sum_lgy1 += (lgfact && yy < (double)LGFACT_N) ? lgfact[(int)yy] : lgamma(yy + 1);
+            }
+            cur = lane_sum<APLL_LANES>(cur, gm); nz = lane_max<APLL_LANES>(nz, gm);
+            start0[l] = nz > 0 ? log(cur / (double)(t1 - t0)) : -INFINITY;
+        }
+        sum_lgy1 = lane_sum<APLL_LANES>(sum_lgy1, gm);
+    }
 
     for (int e = e0; e < e1; ++e) {
         const double phi = L.phi[e];
@@ -191,7 +209,7 @@ k_apl_lanes(const int32_t* __restrict__ cnt, long G, long g0, long g1, const dou
 #pragma unroll 4
                     for (int t = t0 + ln; t < t1; t += APLL_LANES) {         // (independent reciprocal chains: the loop is latency-bound)
                         const double mu = ec * lib_s[t], inv = rcp_pos(1 + mu * phi);
-                        dl += (y[t] - mu) * inv;
+                        dl += (apl_yval(y, t) - mu) * inv;
                         info += mu * inv;
                     }
                     dl = lane_sum<APLL_LANES>(dl, gm); info = lane_sum<APLL_LANES>(info, gm);
@@ -208,7 +226,7 @@ k_apl_lanes(const int32_t* __restrict__ cnt, long G, long g0, long g1, const dou
             for (int t = t0 + ln; t < t1; t += APLL_LANES) {
                 const double mu = ecell * lib_s[t];
                 if (mu == 0) continue;
-                const double yy = y[t], logmu = cb + off_s[t];
+                const double yy = apl_yval(y, t), logmu = cb + off_s[t];
                 if (phi > 0) {
                     const double logmur = log_pos(mu + rr);
                     const double lgyr = (lgr_e && yy < (double)LGFACT_N) ? lgr_e[(int)yy] : lgamma(yy + rr);
@@ -251,6 +269,7 @@ k_apl_lanes(const int32_t* __restrict__ cnt, long G, long g0, long g1, const dou
     if (wg && ln == 0) {
 #pragma unroll
         for (int l = 0; l < APLL_PM; ++l) if (l < p) wg[l] = cbw[l];
+        wg[APLL_PM] = sum_lgy1;
     }
 }
 
@@ -272,11 +291,11 @@ void launch_apl(const int32_t* cnt, long G, long g0, long g1, const double* logo
 #define CBS_APL_SHORT_LANES 2
 #endif
     const int lanes = nmax <= 256 ? CBS_APL_SHORT_LANES : 8, genes = 128 / lanes;          // (cells are at most as long as the batch)
-    lanes_ok = lanes_ok && ((size_t)genes * apll_row_stride(nmax, lanes) + 3 * (size_t)nmax) * sizeof(double) <= 200 * 1024;
+    lanes_ok = lanes_ok && apll_smem_bytes(nmax, lanes) <= 200 * 1024;
     if (lanes_ok) {
         double* lgfact = g_dev.get<double>("lgfact", (size_t)LGFACT_N);
         CBS_LAUNCH(k_lgfact_init, grid1(LGFACT_N, 256), 256, 0, st, lgfact);
-        const size_t smem = ((size_t)genes * apll_row_stride(nmax, lanes) + 3 * (size_t)nmax) * sizeof(double);
+        const size_t smem = apll_smem_bytes(nmax, lanes);
         t_ctx->set_func_attr((const void*)k_apl_lanes<2>, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024);
         t_ctx->set_func_attr((const void*)k_apl_lanes<4>, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024);
         t_ctx->set_func_attr((const void*)k_apl_lanes<8>, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024);
@@ -368,8 +387,8 @@ void run_common_disp(const int32_t* cnt, long G, long g0, long g1, const double*
         if (ds.h_array[b].p < ds.h_array[b].n) { br[b].init(0.0, std::pow(4.0, 0.25), 1e-5); active[b] = 1; }
     double* d_apl = g_dev.get<double>("apl_common", (size_t)nb * G);
     // Newton warm starts across the Brent rounds (k_apl_lanes): NaN = "no previous evaluation"
-    double* d_warm = g_dev.get<double>("apl_warm", (size_t)nb * G * APLL_PM);
-    CBS_CUDA(cudaMemsetAsync(d_warm, 0xff, (size_t)nb * G * APLL_PM * sizeof(double), st));
+    double* d_warm = g_dev.get<double>("apl_warm", (size_t)nb * G * APLL_WS);
+    CBS_CUDA(cudaMemsetAsync(d_warm, 0xff, (size_t)nb * G * APLL_WS * sizeof(double), st));
     int steps = 0;
     for (;;) {
         std::vector<AplJob> jobs;

@@ -2,7 +2,12 @@
 import csv, sys, re, collections
 path = sys.argv[1]; top = int(sys.argv[2]) if len(sys.argv) > 2 else 25
 rows = list(csv.reader(open(path)))
-hdr = rows[1]; body = rows[2:]
+hdr = rows[1]
+# several launches in one export: sections repeat the two header rows; keep section `sec` (third argument, default 0)
+sec = int(sys.argv[3]) if len(sys.argv) > 3 else 0
+starts = [i for i, r in enumerate(rows) if r == hdr]
+a = starts[sec]; b = starts[sec + 1] - 1 if sec + 1 < len(starts) else len(rows)
+body = rows[a + 1:b]; rows = [rows[a - 1]] + rows[a:]
 ci = {h: i for i, h in enumerate(hdr)}
 S, NI, EX = ci['Warp Stall Sampling (All Samples)'], ci['Warp Stall Sampling (Not-issued Samples)'], ci['Instructions Executed']
 tot = sum(int(r[S] or 0) for r in body); totex = sum(int(r[EX] or 0) for r in body)
