@@ -52,6 +52,7 @@ def parse_args():
     ap.add_argument("--genes", type=int, default=0, help="override the workload's gene count (debugging only)")
     ap.add_argument("--cpu-genes", type=int, default=0, help="rows of the bounded CPU sample (0 = auto)")
     ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg")
+    ap.add_argument("--tune", action="append", default=[], metavar="KEY=VALUE", help="cbs_set_tuning knob for A/B runs (development)")
     ap.add_argument("--inproc", type=int, default=0, help="single-process multi-GPU (cbs_input.n_gpus): time the host-buffer "
                                                            "call on this many devices of one process (what the R .Call reaches)")
     return ap.parse_args()
@@ -220,6 +221,8 @@ def run_native(args):
         raise SystemExit("--gpus %d but WORLD_SIZE=%d" % (args.gpus, world))
     pkg = graft.load_package()
     L = pkg._lib
+    for kv in args.tune:
+        L.set_tuning(kv.split("=")[0], float(kv.split("=")[1]))
     if pkg.device_count() < 1:
         raise SystemExit("bench.py needs a CUDA device: libcombatseq has no CPU path")
     torch.cuda.set_device(local)
@@ -451,6 +454,8 @@ def run_inproc(args):
     import torch
     pkg = graft.load_package()
     L = pkg._lib
+    for kv in args.tune:
+        L.set_tuning(kv.split("=")[0], float(kv.split("=")[1]))
     case, d = make_case(pkg, args.workload, args.genes)
     G0, N = case.counts.shape
     h_counts = torch.empty((N, G0), dtype=torch.int32, pin_memory=True)
