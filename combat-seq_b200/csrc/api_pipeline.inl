@@ -182,10 +182,11 @@ static void pipeline(const cbs_input* in, cbs_output* out, const T* h_or_d_count
     double* d_alpha = g_dev.get<double>("alpha", (size_t)G);
     double* d_coef = g_dev.get<double>("coef", (size_t)G * p);
     double* d_mu_hat = g_dev.get<double>("mu_hat", (size_t)G * N);
+    const int glm_flags = glm_class_flags(full.host[0], in->batch_idx);
     // glm_f: only its prior-count coefficients are used, through alpha_g (ComBat_seq.R:131)
-    run_glm_fit(d_cnt, G, g0, g1, N, d_logoff, lib, d_phi_hat, d_bidx, full.d_array, p, nullptr, 1e-4, nullptr, nullptr, d_aw, B, d_alpha, st, full.h_array[0].ncls > 0);
+    run_glm_fit(d_cnt, G, g0, g1, N, d_logoff, lib, d_phi_hat, d_bidx, full.d_array, p, nullptr, 1e-4, nullptr, nullptr, d_aw, B, d_alpha, st, glm_flags);
     // glm_f2: offset = log(lib) + alpha_g (ComBat_seq.R:132-134); gamma_hat = coef[,1:B], mu_hat = fitted.values
-    run_glm_fit(d_cnt, G, g0, g1, N, d_logoff, lib, d_phi_hat, d_bidx, full.d_array, p, d_alpha, 1e-4, d_coef, d_mu_hat, nullptr, 0, nullptr, st, full.h_array[0].ncls > 0);
+    run_glm_fit(d_cnt, G, g0, g1, N, d_logoff, lib, d_phi_hat, d_bidx, full.d_array, p, d_alpha, 1e-4, d_coef, d_mu_hat, nullptr, 0, nullptr, st, glm_flags);
     double* d_gamma_hat = d_coef;        // first B columns
     lap(CBS_ST_GLM);
 

@@ -61,7 +61,7 @@ int cbs_glm_fit(int64_t G, int32_t n, const int32_t* counts, const double* desig
     double* d_coef = coef ? g_dev.get<double>("coef", (size_t)G * p) : nullptr;
     double* d_fit = fitted ? g_dev.get<double>("mu_hat", (size_t)G * n) : nullptr;
     run_glm_fit(d_cnt, G, 0, G, n, d_logoff, hlib, d_phi, d_pc, ds.d_array, p, d_goff, prior_count, d_coef, d_fit,
-                nullptr, 0, nullptr, 0, ds.h_array[0].ncls > 0);
+                nullptr, 0, nullptr, 0, glm_class_flags(ds.host[0], pc.data()));
     if (coef) CBS_CUDA(cudaMemcpy(coef, d_coef, (size_t)G * p * sizeof(double), cudaMemcpyDeviceToHost));
     if (fitted) CBS_CUDA(cudaMemcpy(fitted, d_fit, (size_t)G * n * sizeof(double), cudaMemcpyDeviceToHost));
     CBS_CUDA(cudaDeviceSynchronize());

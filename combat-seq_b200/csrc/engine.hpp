@@ -92,7 +92,8 @@ void run_glm_fit(const int32_t* cnt, long G, long g0, long g1, int N, const doub
                  const std::vector<double>& h_lib, const double* d_phi, const int* d_phi_col, const DesignDev* d_design,
                  int h_p, const double* d_goff, double prior_count, double* d_coef, double* d_fitted,
                  const double* d_alpha_w, int n_alpha, double* d_alpha, cudaStream_t st,
-                 bool class_form = false);    // the design is a Levenberg design in class form (HostDesign::ncls > 0): enables the wide second pass
+                 int class_form = 0);         // bit 0: the design is a Levenberg design in class form (HostDesign::ncls > 0): enables the
+                                              // wide second pass; bit 1: every class lies inside one dispersion column (glm_class_flags)
 
 // tu_mc.cu: monte_carlo_int_NB for every batch (ComBat_seq.R:142-165); see the definition for the sharding rules
 void run_mc_stage(const int32_t* cnt, long G, int B, const std::vector<std::vector<int>>& bcols, long g0, long g1,

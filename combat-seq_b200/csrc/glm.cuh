@@ -55,6 +55,8 @@ struct RowSrc {
     const int* phi_col;    // [N] dispersion column of each sample (batch index), nullptr => column 0
     double phi_scalar;
     const int32_t* cnt_row = nullptr;   // optional: THIS gene's counts indexed by column (a shared-memory copy), instead of cnt
+    bool phi_by_class = false;          // the samples of a design class share one dispersion column (true for every fit of the
+                                        // pipeline: a class lies inside one batch): one dispersion load per class, not per sample
 };
 
 struct Row {
@@ -64,6 +66,12 @@ struct Row {
         // counts are non-negative and below 2^31: 2^52 + x is exact in the low mantissa word, one DADD instead of I2F.F64
         // (the conversion sits in every sweep of the fitters; I2F.F64 was the top stall of the GLM kernel, ncu round 1)
         const double v = __hiloint2double(0x43300000, s.cnt_row ? s.cnt_row[c] : s.cnt[g + (long)c * s.G]) - 4503599627370496.0;
+        return s.yadd ? v + s.yadd[c] : v;
+    }
+    // y(c) in two halves, so that the load can be issued one sample ahead of its use (lev_sweep)
+    __device__ __forceinline__ int yraw(int c) const { return s.cnt_row ? s.cnt_row[c] : s.cnt[g + (long)c * s.G]; }
+    __device__ __forceinline__ double ycvt(int raw, int c) const {
+        const double v = __hiloint2double(0x43300000, raw) - 4503599627370496.0;
         return s.yadd ? v + s.yadd[c] : v;
     }
     __device__ __forceinline__ double off(int c) const { return s.logoff[2 * c] + goff; }
@@ -144,6 +152,19 @@ __device__ __forceinline__ double unit_nb_deviance(double y, double mu, double p
     return 2 * (y * log_pos(y * rcp_pos(mu)) + ypr * log_pos((mu + invphi) * rcp_pos(ypr)));
 }
 
+// the same with 1 / phi handed in (invphi = rcp_pos(phi), only read when phi >= 1e-4): identical arithmetic, identical bits
+__device__ __forceinline__ double unit_nb_deviance_inv(double y, double mu, double phi, double invphi) {
+    y += CBS_MILDLY_LOW; mu += CBS_MILDLY_LOW;
+    if (phi < 1e-4) {
+        const double resid = y - mu;
+        return 2 * (y * log(y / mu) - resid - 0.5 * resid * resid * phi * (1 + phi * (0.0 * resid - y)));
+    }
+    const double product = mu * phi;
+    if (product > 1e6) return 2 * ((y - mu) / mu - log(y / mu)) * mu / (1 + product);
+    const double ypr = y + invphi;
+    return 2 * (y * log_pos(y * rcp_pos(mu)) + ypr * log_pos((mu + invphi) * rcp_pos(ypr)));
+}
+
 __device__ __forceinline__ double lin_pred(const DesignDev& d, const Row& r, int t, const double* beta) {
     double eta = r.off(d.col[t]);
     for (int k = d.rowptr[t]; k < d.rowptr[t + 1]; ++k) eta += d.cval[k] * beta[d.cidx[k]];
@@ -167,13 +188,31 @@ __device__ inline double lev_sweep(const DesignDev& d, const Row& r, const doubl
             for (int k = k0; k < k1; ++k) eta += d.cval[k] * beta[d.cidx[k]];
             const double E = exp(eta);
             double sw = 0, sz = 0;
+            if (r.s.phi_by_class) {
+                // one dispersion (and one reciprocal of it) per class; the count and the library size of the lane's next sample
+                // are requested before the current one is worked on (ncu: a quarter of the kernel's stall samples sat on the
+                // first use of these loads, and the dispersion added a third dependent load: column -> batch -> phi)
+                const double phi = r.phi(d.col[t0]);
+                const double invphi = phi >= 1e-4 ? rcp_pos(phi) : 0.0;
+                int t = t0 + ln, col = 0, yr = 0;
+                double lib = 0;
+                if (t < t1) { col = d.col[t]; lib = r.lib(col); yr = r.yraw(col); }
+                for (; t < t1; t += LANES) {
+                    const double mu = E * lib, y = r.ycvt(yr, col);
+                    if (t + LANES < t1) { col = d.col[t + LANES]; lib = r.lib(col); yr = r.yraw(col); }
+                    dev += unit_nb_deviance_inv(y, mu, phi, invphi);
+                    const double inv = rcp_pos(1 + mu * phi);
+                    sw += mu * inv; sz += (y - mu) * inv;
+                }
+            } else {
 #pragma unroll kGlmUnroll
-            for (int t = t0 + ln; t < t1; t += LANES) {
-                const int col = d.col[t];
-                const double mu = E * r.lib(col), y = r.y(col), phi = r.phi(col);
-                dev += unit_nb_deviance(y, mu, phi);
-                const double inv = rcp_pos(1 + mu * phi);
-                sw += mu * inv; sz += (y - mu) * inv;
+                for (int t = t0 + ln; t < t1; t += LANES) {
+                    const int col = d.col[t];
+                    const double mu = E * r.lib(col), y = r.y(col), phi = r.phi(col);
+                    dev += unit_nb_deviance(y, mu, phi);
+                    const double inv = rcp_pos(1 + mu * phi);
+                    sw += mu * inv; sz += (y - mu) * inv;
+                }
             }
             if (LANES > 1) { sw = lane_sum<LANES>(sw, gm); sz = lane_sum<LANES>(sz, gm); }
             for (int k = k0; k < k1; ++k) {

@@ -66,6 +66,18 @@ struct HostDesign {
     std::vector<double> start;     // p
 };
 
+// run_glm_fit's class_form argument: bit 0 = class form (ncls > 0), bit 1 = every class lies inside one dispersion column
+// (phi_col: dispersion column of each global sample column; nullptr = one column)
+inline int glm_class_flags(const HostDesign& d, const int* phi_col) {
+    if (d.ncls <= 0) return 0;
+    int flags = 3;
+    if (phi_col)
+        for (int c = 0; c < d.ncls && flags == 3; ++c)
+            for (int t = d.cell_start[c] + 1; t < d.cell_start[c + 1]; ++t)
+                if (phi_col[d.col[t]] != phi_col[d.col[d.cell_start[c]]]) { flags = 1; break; }
+    return flags;
+}
+
 // least-squares solution of X b = rhs by Householder QR (X n x p column-major, full column rank)
 inline void lstsq(const double* Xin, int n, int p, const double* rhs, double* sol) {
     std::vector<double> a(Xin, Xin + (size_t)n * p), b(rhs, rhs + n), v(n);

@@ -109,7 +109,7 @@ __global__ void __launch_bounds__(128, CBS_GLM_MINBLOCKS)
 k_glm_fit_lanes(const int32_t* __restrict__ cnt, long G, long g0, long g1, const double* __restrict__ logoff,
                 const __grid_constant__ GlmJobs jobs, const double* __restrict__ phi,
                 const int* __restrict__ phi_col, const DesignDev* __restrict__ design, const double* __restrict__ goff_in,
-                const double* __restrict__ alpha_w, int n_alpha, int use_scr, int* __restrict__ iter_hist) {
+                const double* __restrict__ alpha_w, int n_alpha, int use_scr, int phi_by_class, int* __restrict__ iter_hist) {
     const GlmJob jb = glm_pick_job(jobs);
     const double* __restrict__ yadd = jb.yadd;
     const double two_prior_over_meanlib = jb.two_prior_over_meanlib;
@@ -124,7 +124,7 @@ k_glm_fit_lanes(const int32_t* __restrict__ cnt, long G, long g0, long g1, const
     const DesignDev d = *design;
     double goff = goff_in ? goff_in[g] : 0.0;
     if (mode == 1) goff = log(exp(goff) + two_prior_over_meanlib);
-    RowSrc src{cnt, G, logoff, mode == 1 ? yadd : nullptr, phi, phi_col, 0.0};
+    RowSrc src{cnt, G, logoff, mode == 1 ? yadd : nullptr, phi, phi_col, 0.0, nullptr, phi_by_class != 0};
     Row r(src, g, goff);
     double beta[PM], cellbeta[PM];
     extern __shared__ __align__(16) double glm_scr[];       // lev_scratch_doubles<PM>() per lane group, or nothing
@@ -202,9 +202,10 @@ __device__ __forceinline__ void glm_wide_classes(const DesignDev& d, const Row& 
         for (int k = k0; k < k1; ++k) eta += d.cval[k] * bsrc[d.cidx[k]];
         const double E = exp(eta);
         double sw = 0, sz = 0, dv = 0;
+        const double phic = r.s.phi_by_class ? r.phi(d.col[t0]) : 0.0;
         for (int t = t0 + lane; t < t1; t += 32) {
             const int col = d.col[t];
-            const double mu = E * r.lib(col), y = r.y(col), phi = r.phi(col);
+            const double mu = E * r.lib(col), y = r.y(col), phi = r.s.phi_by_class ? phic : r.phi(col);
             dv += unit_nb_deviance(y, mu, phi);
             const double inv = rcp_pos(1 + mu * phi);
             sw += mu * inv; sz += (y - mu) * inv;
@@ -219,7 +220,7 @@ __global__ void __launch_bounds__(128)
 k_glm_fit_wide(const int32_t* __restrict__ cnt, long G, long g0, int N, const double* __restrict__ logoff,
                const __grid_constant__ GlmJobs jobs, const double* __restrict__ phi,
                const int* __restrict__ phi_col, const DesignDev* __restrict__ design, const double* __restrict__ goff_in,
-               const double* __restrict__ alpha_w, int n_alpha, int* __restrict__ iter_hist, int stage_counts) {
+               const double* __restrict__ alpha_w, int n_alpha, int* __restrict__ iter_hist, int stage_counts, int phi_by_class) {
     const GlmJob jb = glm_pick_job(jobs);
     const double* __restrict__ yadd = jb.yadd;
     const double two_prior_over_meanlib = jb.two_prior_over_meanlib;
@@ -257,7 +258,7 @@ k_glm_fit_wide(const int32_t* __restrict__ cnt, long G, long g0, int N, const do
         __syncthreads();
         double goff = goff_in ? goff_in[g] : 0.0;
         if (mode == 1) goff = log(exp(goff) + two_prior_over_meanlib);
-        RowSrc src{cnt, G, logoff, mode == 1 ? yadd : nullptr, phi, phi_col, 0.0, stage_counts ? xs : nullptr};
+        RowSrc src{cnt, G, logoff, mode == 1 ? yadd : nullptr, phi, phi_col, 0.0, stage_counts ? xs : nullptr, phi_by_class != 0};
         Row r(src, g, goff);
         if (warp != 0) {                                      // workers: serve sweep requests until the fit is finished
             for (;;) {
@@ -378,7 +379,7 @@ k_glm_fit_wide(const int32_t* __restrict__ cnt, long G, long g0, int N, const do
 void run_glm_fit(const int32_t* cnt, long G, long g0, long g1, int N, const double* d_logoff,
                         const std::vector<double>& h_lib, const double* d_phi, const int* d_phi_col,
                         const DesignDev* d_design, int h_p, const double* d_goff, double prior_count, double* d_coef,
-                        double* d_fitted, const double* d_alpha_w, int n_alpha, double* d_alpha, cudaStream_t st, bool class_form) {
+                        double* d_fitted, const double* d_alpha_w, int n_alpha, double* d_alpha, cudaStream_t st, int class_form) {
     if (g1 <= g0) return;
     const dim3 grid = grid1(g1 - g0, 128);
     double two_prior = 0;
@@ -397,7 +398,8 @@ void run_glm_fit(const int32_t* cnt, long G, long g0, long g1, int N, const doub
     int* d_hist = g_tune.glm_hist ? g_dev.get<int>("glm_iter_hist", 256) : nullptr;     // zeroed by cbs_get_diag("reset")
     const dim3 lgrid = grid1((g1 - g0) * GLM_LANES, 128);
     // the wide second pass needs the class form of the sweep with shared scratch (every Levenberg design of the pipeline)
-    const bool two_pass = g_tune.glm_scr && g_tune.glm_two_pass && class_form;
+    const bool two_pass = g_tune.glm_scr && g_tune.glm_two_pass && (class_form & 1);
+    const int phi_by_class = (class_form & 2) ? 1 : 0;
     int* d_strag = g_dev.get<int>("glm_strag", 2 * (size_t)(g1 - g0));
     int* d_nstrag = g_dev.get<int>("glm_nstrag", 2);
     // the fits this call asks for: the plain one (fitted values, or everything when prior_count == 0) and the predFC one
@@ -429,13 +431,13 @@ void run_glm_fit(const int32_t* cnt, long G, long g0, long g1, int N, const doub
                              (int)((128 / GLM_LANES) * lev_scratch_doubles<PM_>() * sizeof(double))); \
         CBS_CUDA(cudaMemsetAsync(d_nstrag, 0, 2 * sizeof(int), st)); \
         CBS_LAUNCH(k_glm_fit_lanes<PM_>, dim3(lgrid.x, (unsigned)nj), 128, smem, st, cnt, G, g0, g1, d_logoff, jobs, d_phi, \
-                   d_phi_col, d_design, d_goff, d_alpha_w, n_alpha, g_tune.glm_scr ? 1 : 0, d_hist); \
+                   d_phi_col, d_design, d_goff, d_alpha_w, n_alpha, g_tune.glm_scr ? 1 : 0, phi_by_class, d_hist); \
         if (two_pass) { \
             const int stage = N <= 32768; \
             const size_t wsmem = glm_wide_smem_doubles<PM_>() * sizeof(double) + (stage ? (size_t)N * sizeof(int32_t) : 0); \
             t_ctx->set_func_attr((const void*)k_glm_fit_wide<PM_>, cudaFuncAttributeMaxDynamicSharedMemorySize, 160 * 1024); \
             CBS_LAUNCH(k_glm_fit_wide<PM_>, dim3(64, (unsigned)nj), 128, wsmem, st, cnt, G, g0, N, d_logoff, jobs, d_phi, d_phi_col, \
-                       d_design, d_goff, d_alpha_w, n_alpha, d_hist, stage); \
+                       d_design, d_goff, d_alpha_w, n_alpha, d_hist, stage, phi_by_class); \
         } } while (0)
     if (h_p <= 4) CBS_GLM_LANES(4); else if (h_p <= 8) CBS_GLM_LANES(8); else if (h_p <= 12) CBS_GLM_LANES(12); else CBS_GLM_LANES(16);
 #undef CBS_GLM_LANES
