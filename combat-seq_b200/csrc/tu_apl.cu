@@ -173,9 +173,8 @@ k_apl_lanes(const int32_t* __restrict__ cnt, long G, long g0, long g1, const dou
         for (int l = 0; l < APLL_PM; ++l) start0[l] = cbw[l] > -1e7 ? 0.0 : -INFINITY;     // (only "has counts" matters: cbw is the start)
     } else {
         sum_lgy1 = 0;
-#pragma unroll
-        for (int l = 0; l < APLL_PM; ++l) {
-            if (l >= p) break;
+#pragma unroll 1
+        for (int l = 0; l < p; ++l) {
             const int t0 = d.cell_start[l], t1 = d.cell_start[l + 1];
             double cur = 0, nz = 0;
             for (int t = t0 + ln; t < t1; t += APLL_LANES) {
@@ -195,9 +194,10 @@ k_apl_lanes(const int32_t* __restrict__ cnt, long G, long g0, long g1, const dou
         const double rr = phi > 0 ? 1 / phi : 0.0, logrr = phi > 0 ? log(rr) : 0.0, lgrr = phi > 0 ? lgamma(rr) : 0.0;
         double Wc[APLL_PM];
         double ll = 0, nlive = 0, sumw = 0;
-#pragma unroll
-        for (int l = 0; l < APLL_PM; ++l) {
-            if (l >= p) break;
+        // (not unrolled: four copies of the Newton and likelihood loops with their inlined exp / log / reciprocal made the kernel
+        // 160 KB of code and a fifth of its stall samples were instruction fetches; ncu "no_instructions")
+#pragma unroll 1
+        for (int l = 0; l < p; ++l) {
             const int t0 = d.cell_start[l], t1 = d.cell_start[l + 1];
             // edgeR glm_one_group: Newton on the cell's coefficient, maxit 50, |step| < 1e-10
             double cur = start0[l];
