@@ -26,7 +26,7 @@ EXPORTS = ("cbs_version", "cbs_device_count", "cbs_last_error", "cbs_shutdown", 
            "cbs_comm_unique_id", "cbs_comm_create", "cbs_comm_destroy", "cbs_shard_range", "cbs_combat_seq", "cbs_nb_logpmf",
            "cbs_nb_cdf", "cbs_nb_quantile", "cbs_glm_fit", "cbs_apl", "cbs_common_disp", "cbs_tagwise_disp",
            "cbs_mc_int", "cbs_match_quantiles", "cbs_profile_enable", "cbs_profile_dump", "cbs_fp64_peak",
-           "cbs_fp64_mma_peak", "cbs_set_tuning", "cbs_get_diag", "cbs_tagwise_disp_prior")
+           "cbs_fp64_mma_peak", "cbs_set_tuning", "cbs_get_diag", "cbs_tagwise_disp_prior", "cbs_simulate_counts")
 
 
 class CbsInput(C.Structure):
@@ -150,6 +150,21 @@ def nb_quantile(p, size, mu): return _elementwise("cbs_nb_quantile", p, size, mu
 
 
 # ---- per-subsystem entry points ------------------------------------------------------------------------------
+def simulate_counts(base_mu, col_factor, phi_col, seed, level=None, fold=None, counts_dev_ptr=None):
+    """Synthetic NB count matrix generated on the device (cbs_simulate_counts): G x N int32, column-major."""
+    base_mu = _d(base_mu); col_factor = _d(col_factor); phi_col = _d(phi_col)
+    G, N = base_mu.size, col_factor.size
+    n_levels = 0
+    if fold is not None:
+        fold = _F(np.asarray(fold, dtype=np.float64).reshape(G, -1)); n_levels = fold.shape[1]
+        level = np.ascontiguousarray(level, dtype=np.int32)
+    out = np.empty((G, N), dtype=np.int32, order="F") if counts_dev_ptr is None else None
+    check(lib().cbs_simulate_counts(C.c_int64(G), C.c_int32(N), _p(base_mu), _p(col_factor), _p(level, i32p) if fold is not None else None,
+                                    C.c_int32(n_levels), _p(fold) if fold is not None else None, _p(phi_col), C.c_uint64(seed),
+                                    _p(out, i32p) if out is not None else None, C.c_void_p(counts_dev_ptr) if counts_dev_ptr else None))
+    return out
+
+
 def glm_fit(y, design, disp, disp_cols, lib_size, gene_offset=None, prior_count=0.0):
     y = _F(y, np.int32); G, n = y.shape
     design = _F(design); p = design.shape[1]

@@ -15,7 +15,7 @@ OUT = os.path.join(HERE, "libcombatseq.so")
 NVCC = os.environ.get("NVCC", "/usr/local/cuda/bin/nvcc")
 FLAGS = ["-gencode", "arch=compute_100a,code=sm_100a", "-lineinfo", "-O3", "-std=c++17",
          "-Xcompiler", "-fPIC", "-diag-suppress", "177"]
-UNITS = ["combatseq.cu", "tu_apl.cu", "tu_glm.cu", "tu_mq.cu", "tu_mc.cu", "tu_screen.cu"]
+UNITS = ["combatseq.cu", "tu_apl.cu", "tu_glm.cu", "tu_mq.cu", "tu_mc.cu", "tu_screen.cu", "tu_sim.cu"]
 
 
 def headers():

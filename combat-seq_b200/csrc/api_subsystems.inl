@@ -37,6 +37,28 @@ int cbs_nb_logpmf(int64_t n, const double* x, const double* size, const double* 
 int cbs_nb_cdf(int64_t n, const double* x, const double* size, const double* mu, double* out) { return nb_elementwise(1, n, x, size, mu, out); }
 int cbs_nb_quantile(int64_t n, const double* p, const double* size, const double* mu, double* out) { return nb_elementwise(2, n, p, size, mu, out); }
 
+int cbs_simulate_counts(int64_t G, int32_t N, const double* base_mu, const double* col_factor, const int32_t* level,
+                        int32_t n_levels, const double* fold, const double* phi_col, uint64_t seed, int32_t* counts,
+                        void* counts_dev) {
+    CBS_NEED_GPU();
+    if (G < 0 || N < 0 || (G > 0 && N > 0 && (!base_mu || !col_factor || !phi_col))) return fail(CBS_EINVAL, "null pointer / bad size");
+    if (!counts && !counts_dev) return fail(CBS_EINVAL, "no output buffer");
+    if (fold && (!level || n_levels < 1)) return fail(CBS_EINVAL, "fold needs level[] and n_levels >= 1");
+    if (fold) for (int s = 0; s < N; ++s) if (level[s] < 0 || level[s] >= n_levels) return fail(CBS_EINVAL, "level out of range");
+    if (G == 0 || N == 0) return CBS_OK;
+    CBS_ENTRY_BEGIN
+    double* d_base = upload(g_dev, "sim_base", base_mu, (size_t)G);
+    double* d_cf = upload(g_dev, "sim_colfac", col_factor, (size_t)N);
+    double* d_phi = upload(g_dev, "sim_phi", phi_col, (size_t)N);
+    int* d_level = fold ? upload(g_dev, "sim_level", level, (size_t)N) : nullptr;
+    double* d_fold = fold ? upload(g_dev, "sim_fold", fold, (size_t)G * n_levels) : nullptr;
+    int32_t* d_out = counts_dev ? (int32_t*)counts_dev : g_dev.get<int32_t>("sim_out", (size_t)G * N);
+    launch_simulate_counts((long)G, N, d_base, d_cf, d_level, d_fold, d_phi, seed, d_out, 0);
+    if (counts) CBS_CUDA(cudaMemcpy(counts, d_out, (size_t)G * N * sizeof(int32_t), cudaMemcpyDeviceToHost));
+    CBS_CUDA(cudaDeviceSynchronize());
+    CBS_ENTRY_END
+}
+
 int cbs_glm_fit(int64_t G, int32_t n, const int32_t* counts, const double* design, int32_t p, const double* disp,
                 int32_t n_disp_cols, const int32_t* disp_cols, const double* lib, const double* gene_offset,
                 double prior_count, double* coef, double* fitted) {

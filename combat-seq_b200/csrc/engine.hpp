@@ -108,6 +108,8 @@ void launch_match_quantiles(const int32_t* cnt, long G, long g0, long g1, const 
                             const double* phi_star, const int* keep_idx, long G0, double* out, cudaStream_t st);
 void launch_match_quantiles_plain(const int32_t* cnt, long G, int n, const double* old_mu, const double* old_phi,
                                   const double* new_mu, const double* new_phi, double* out, cudaStream_t st);
+void launch_simulate_counts(long G, int N, const double* base_mu, const double* col_factor, const int* level,
+                            const double* fold, const double* phi_col, uint64_t seed, int32_t* out, cudaStream_t st);
 void launch_nb_elementwise(int what, long n, const double* a, const double* size, const double* mu, double* out, cudaStream_t st);
 
 }  // namespace cbs

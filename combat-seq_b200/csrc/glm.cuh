@@ -172,12 +172,17 @@ __device__ __forceinline__ double lin_pred(const DesignDev& d, const Row& r, int
 }
 
 // One sweep over the samples at coefficients beta: deviance, X'WX (packed lower) and X'z.
-template <int LANES = 1>
+// SHARED: xtwx and dl are ONE shared-memory copy owned by the lane group (class form only): lane 0 of the group is the only
+// writer, and the sweep ends with a __syncwarp(gm) that publishes the result to the other lanes.
+template <int LANES = 1, bool SHARED = false>
 __device__ inline double lev_sweep(const DesignDev& d, const Row& r, const double* beta, double* xtwx, double* dl,
                                    int ln = 0, unsigned gm = 0xffffffffu) {
     const int p = d.p;
-    for (int i = 0; i < p * (p + 1) / 2; ++i) xtwx[i] = 0;
-    for (int i = 0; i < p; ++i) dl[i] = 0;
+    const bool writer = !SHARED || ln == 0;
+    if (writer) {
+        for (int i = 0; i < p * (p + 1) / 2; ++i) xtwx[i] = 0;
+        for (int i = 0; i < p; ++i) dl[i] = 0;
+    }
     double dev = 0;
     if (d.ncls > 0) {
         // Samples grouped by distinct design row: mu_s = exp(gene offset + x_c'beta) * lib.size_s needs one exp per class,
@@ -215,15 +220,16 @@ __device__ inline double lev_sweep(const DesignDev& d, const Row& r, const doubl
                 }
             }
             if (LANES > 1) { sw = lane_sum<LANES>(sw, gm); sz = lane_sum<LANES>(sz, gm); }
-            for (int k = k0; k < k1; ++k) {
-                const int ik = d.cidx[k];
-                const double vk = d.cval[k];
-                dl[ik] += vk * sz;
-                for (int k2 = k0; k2 <= k; ++k2) xtwx[tri(ik, d.cidx[k2])] += vk * d.cval[k2] * sw;
-            }
-            if (LANES > 1) __syncwarp(gm);                    // (shared scratch) the group updates X'WX as one
+            if (writer)
+                for (int k = k0; k < k1; ++k) {
+                    const int ik = d.cidx[k];
+                    const double vk = d.cval[k];
+                    dl[ik] += vk * sz;
+                    for (int k2 = k0; k2 <= k; ++k2) xtwx[tri(ik, d.cidx[k2])] += vk * d.cval[k2] * sw;
+                }
         }
         if (LANES > 1) dev = lane_sum<LANES>(dev, gm);
+        if (SHARED) __syncwarp(gm);
         return dev;
     }
     for (int t = ln; t < d.n; t += LANES) {
@@ -271,8 +277,8 @@ __device__ inline void chol_solve_packed(const double* a, int p, double* b) {
 // Levenberg trial step), or -1 when y is all zero (beta = NaN, mu = 0).
 // Work arrays of one Levenberg fit: 3 packed p x p triangles and 4 p-vectors.  One thread per gene keeps them in local
 // memory.  A lane group can share ONE copy in shared memory (SCR = true, `scr` = lev_scratch_doubles<PM>() doubles owned
-// by the group): outside the sample sweeps every lane of the group executes the same instructions on bit-identical
-// values, so the group's lanes read and write the same words in lock-step.  That needs the class form of the sweep
+// by the group): outside the sample sweeps every lane of the group follows the same control flow on bit-identical values; lane 0
+// does the small dense algebra and is the only writer, the others read after a __syncwarp.  That needs the class form of the sweep
 // (d.ncls > 0), where the lanes' partial sums are combined BEFORE X'WX is touched; the per-sample form accumulates a
 // private X'WX per lane and keeps the local arrays.
 template <int PM>
@@ -308,7 +314,12 @@ __device__ inline int fit_levenberg(const DesignDev& d, const Row& r, double* be
     if (ymax < CBS_LOW_VALUE) { for (int i = 0; i < p; ++i) beta[i] = nan(""); return -1; }
     const double c0 = log(sum_exprs / sum_weight);
     for (int i = 0; i < p; ++i) beta[i] = d.start[i] * c0;
-    double dev = lev_sweep<LANES>(d, r, beta, xtwx, dl, ln, gm);
+    // Shared work arrays (SCR): lane 0 of the group is the only writer of the shared words; every hand-over between its writes and
+    // the other lanes' reads goes through a __syncwarp(gm) (the shuffles below are such barriers too).  All lanes of the group
+    // take the same branches: the values they branch on are bit-identical.
+    const bool writer = !SCR || ln == 0;
+    const int leader = __ffs(gm) - 1;
+    double dev = lev_sweep<LANES, SCR>(d, r, beta, xtwx, dl, ln, gm);
     double max_info = -1, lambda = 0;
     int iter = 0, sweeps = 1;
     while ((++iter) <= maxit) {
@@ -318,16 +329,24 @@ __device__ inline int fit_levenberg(const DesignDev& d, const Row& r, double* be
         bool low_dev = false, failed = false;
         while (++lev) {
             do {
-                for (int i = 0; i < pt; ++i) work[i] = xtwx[i];
-                for (int i = 0; i < p; ++i) { work[tri(i, i)] += lambda; dbeta[i] = dl[i]; }
-                if (chol_packed(work, p)) break;
+                int ok = 0;
+                if (writer) {
+                    for (int i = 0; i < pt; ++i) work[i] = xtwx[i];
+                    for (int i = 0; i < p; ++i) { work[tri(i, i)] += lambda; dbeta[i] = dl[i]; }
+                    ok = chol_packed(work, p) ? 1 : 0;
+                }
+                if (SCR) ok = __shfl_sync(gm, ok, leader);
+                if (ok) break;
                 lambda *= 10;
                 if (lambda <= 0) lambda = CBS_RIDICULOUSLY_LOW;
             } while (1);
-            chol_solve_packed(work, p, dbeta);
-            for (int i = 0; i < p; ++i) beta_new[i] = beta[i] + dbeta[i];
+            if (writer) {
+                chol_solve_packed(work, p, dbeta);
+                for (int i = 0; i < p; ++i) beta_new[i] = beta[i] + dbeta[i];
+            }
+            if (SCR) __syncwarp(gm);
             if (sweeps >= max_sweeps) return -2;                   // handed to the wide second pass (tu_glm.cu): nothing is written
-            const double dev_new = lev_sweep<LANES>(d, r, beta_new, xtwx_new, dl_new, ln, gm);
+            const double dev_new = lev_sweep<LANES, SCR>(d, r, beta_new, xtwx_new, dl_new, ln, gm);
             ++sweeps;
             if (dev_new / ymax < CBS_SUPREMELY_LOW) low_dev = true;
             if (dev_new <= dev || low_dev) {
@@ -338,14 +357,19 @@ __device__ inline int fit_levenberg(const DesignDev& d, const Row& r, double* be
             lambda *= 2;
             if (lambda <= 0) lambda = CBS_RIDICULOUSLY_LOW;
             if (lambda / max_info > 1 / CBS_SUPREMELY_LOW) { failed = true; break; }
+            if (SCR) __syncwarp(gm);                              // (nothing shared is read on this path; keeps the group together)
         }
         if (failed || low_dev) break;
         double divergence = 0;
         for (int i = 0; i < p; ++i) divergence += dl[i] * dbeta[i];
         if (divergence < tolerance) break;
         if (lev == 1) lambda /= 10;
-        for (int i = 0; i < pt; ++i) xtwx[i] = xtwx_new[i];     // information at the accepted coefficients
-        for (int i = 0; i < p; ++i) dl[i] = dl_new[i];
+        if (SCR) __syncwarp(gm);                                  // every lane has read beta_new, dl, dbeta, xtwx
+        if (writer) {
+            for (int i = 0; i < pt; ++i) xtwx[i] = xtwx_new[i];     // information at the accepted coefficients
+            for (int i = 0; i < p; ++i) dl[i] = dl_new[i];
+        }
+        if (SCR) __syncwarp(gm);
     }
     return sweeps;
 }

@@ -150,6 +150,17 @@ int cbs_nb_logpmf(int64_t n, const double* x, const double* size, const double* 
 int cbs_nb_cdf(int64_t n, const double* x, const double* size, const double* mu, double* out);
 int cbs_nb_quantile(int64_t n, const double* p, const double* size, const double* mu, double* out);
 
+/* Synthetic negative-binomial count matrix, generated on the device (generator half).  Replaces
+ * the count generation of the reference's simulation study, simulations/sim_DEpipe.R:98-113
+ * (polyester::simulate_experiment(reads_per_transcript, fold_changes, size) = rnbinom(mu = reads * fold change, size)):
+ *   counts[g + s*G] ~ NB(mean = base_mu[g] * col_factor[s] * fold[g + level[s]*G], dispersion = phi_col[s])
+ * G x N column-major int32 (clamped to 2^31 - 1); fold (G x n_levels, with level[N]) may be NULL; phi_col[s] <= 0 gives
+ * Poisson.  Gamma-Poisson mixture with one Philox4x32-10 stream per element keyed by (seed, element index): the matrix
+ * depends on the seed only, not on the launch shape.  counts (host) and / or counts_dev (device pointer) receive it. */
+int cbs_simulate_counts(int64_t G, int32_t N, const double* base_mu, const double* col_factor, const int32_t* level,
+                        int32_t n_levels, const double* fold, const double* phi_col, uint64_t seed, int32_t* counts,
+                        void* counts_dev);
+
 /* edgeR glmFit.default(y, design, dispersion, offset, prior.count) as called at ComBat_seq.R:130,134.
  * counts G x n int32; design n x p; disp G x n_disp_cols with disp_cols[s] selecting the column for sample s
  * (phi_matrix of ComBat_seq.R:122-125 without materialising it); offset = log(lib[s]) + gene_offset[g]

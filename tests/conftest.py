@@ -30,6 +30,22 @@ def synth(pkg):
     return importlib.import_module("combat-seq_b200.synth")
 
 
+@pytest.fixture(scope="session")
+def hostmath_lib():
+    """tests/hostmath/libhostmath.so: the product's device math headers compiled for the host (rebuilt when a header changes)."""
+    import ctypes
+    import subprocess
+    here = os.path.dirname(os.path.abspath(__file__))
+    src = os.path.join(here, "hostmath", "hostmath.cu")
+    out = os.path.join(here, "hostmath", "libhostmath.so")
+    deps = [src] + [os.path.join(ROOT, "combat-seq_b200", "csrc", h) for h in ("nbmath.cuh", "fastmath.cuh", "rng.cuh")]
+    if not os.path.exists(out) or os.path.getmtime(out) < max(os.path.getmtime(d) for d in deps):
+        nvcc = os.environ.get("NVCC", "/usr/local/cuda/bin/nvcc")
+        subprocess.run([nvcc, "-O2", "-std=c++17", "-shared", "-Xcompiler", "-fPIC", "-Wno-deprecated-gpu-targets",
+                        "-o", out, src], check=True)
+    return ctypes.CDLL(out)
+
+
 def rel_err(a, b, rtol=1e-6, atol=1e-9):
     """max |a-b| / (rtol*|b| + atol) over the finite entries of b; NaN patterns must agree."""
     a = np.asarray(a); b = np.asarray(b)

@@ -36,3 +36,11 @@ extern "C" {
 void hm_log_pos(int64_t n, const double* x, double* out) { for (int64_t i = 0; i < n; ++i) out[i] = cbs::log_pos(x[i]); }
 void hm_rcp_pos(int64_t n, const double* x, double* out) { for (int64_t i = 0; i < n; ++i) out[i] = cbs::rcp_pos(x[i]); }
 }
+#include "../../combat-seq_b200/csrc/rng.cuh"
+extern "C" {
+// the synthetic-count sampler (rng.cuh) for elements index0 .. index0 + n - 1 of a matrix
+void hm_sample_nb(int64_t n, uint64_t seed, uint64_t index0, const double* mu, const double* phi, int32_t* out) {
+    for (int64_t i = 0; i < n; ++i) out[i] = cbs::sample_nb(seed, index0 + (uint64_t)i, mu[i], phi[i]);
+}
+void hm_philox(uint32_t* c, uint32_t k0, uint32_t k1) { cbs::philox4x32_10(c, k0, k1); }
+}

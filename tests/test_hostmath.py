@@ -14,16 +14,8 @@ f64p = C.POINTER(C.c_double)
 
 
 @pytest.fixture(scope="module")
-def hm():
-    src = os.path.join(HERE, "hostmath", "hostmath.cu")
-    out = os.path.join(HERE, "hostmath", "libhostmath.so")
-    hdr = os.path.join(HERE, "..", "combat-seq_b200", "csrc", "nbmath.cuh")
-    hdr2 = os.path.join(HERE, "..", "combat-seq_b200", "csrc", "fastmath.cuh")
-    if not os.path.exists(out) or os.path.getmtime(out) < max(os.path.getmtime(src), os.path.getmtime(hdr), os.path.getmtime(hdr2)):
-        nvcc = os.environ.get("NVCC", "/usr/local/cuda/bin/nvcc")
-        subprocess.run([nvcc, "-O2", "-std=c++17", "-shared", "-Xcompiler", "-fPIC", "-Wno-deprecated-gpu-targets",
-                        "-o", out, src], check=True)
-    lib = C.CDLL(out)
+def hm(hostmath_lib):
+    lib = hostmath_lib
 
     def call(fn, *arrs, extra=()):
         arrs = [np.ascontiguousarray(a, dtype=np.float64) for a in np.broadcast_arrays(*arrs)]

@@ -5,7 +5,7 @@ set -e
 name=$1; shift
 cd "$(dirname "$0")/.."
 out=tools/variants; obj=$out/obj_$name; mkdir -p $obj
-for u in combatseq tu_apl tu_glm tu_mq tu_mc tu_screen; do
+for u in combatseq tu_apl tu_glm tu_mq tu_mc tu_screen tu_sim; do
   /usr/local/cuda/bin/nvcc -gencode arch=compute_100a,code=sm_100a -lineinfo -O3 -std=c++17 -Xcompiler -fPIC -diag-suppress 177 "$@" -c -o $obj/$u.o combat-seq_b200/csrc/$u.cu &
 done
 wait
