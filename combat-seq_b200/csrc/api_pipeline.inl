@@ -217,6 +217,12 @@ static void pipeline(const cbs_input* in, cbs_output* out, const T* h_or_d_count
     const long r0 = (rank == 0 || g0 >= G) ? (rank == 0 ? 0 : G0) : keep_idx[g0];
     const long r1 = (g1 >= G) ? G0 : keep_idx[g1];
     out->row_begin = r0; out->row_end = r1;
+    // match_quantiles runs in up to 8 launches over the samples (in batch order); when the result goes to a host buffer, the
+    // columns of a finished launch are copied out on a second stream while the next launch computes (the D2H of the adjusted
+    // matrix, 480 MB at C5, hides behind the kernel instead of following it).
+    const bool to_host = out->adjusted && !out->adjusted_on_device;
+    cudaStream_t st2 = to_host ? t_ctx->copy_stream() : nullptr;
+    bool copied_by_columns = false;
     if (d_adj) {
         CBS_LAUNCH(k_counts_to_f64<T>, grid1(G0 * N, 256), 256, 0, st, d_in, G0 * N, d_adj);
         if (g1 > g0) {
@@ -224,8 +230,28 @@ static void pipeline(const cbs_input* in, cbs_output* out, const T* h_or_d_count
             order.reserve(N);
             for (int b = 0; b < B; ++b) order.insert(order.end(), bcols[b].begin(), bcols[b].end());
             int* d_order = upload(g_dev, "mq_order", order.data(), (size_t)N, st);
-            launch_match_quantiles(d_cnt, G, g0, g1, d_mu_hat, d_bidx, d_order, N, d_phi_hat, d_gamma_star, d_phi_star,
-                                   d_keep_idx, G0, d_adj, st);
+            const int nblk = (N + 31) / 32, nchunk = (to_host && r1 > r0) ? std::min(8, nblk) : 1;
+            std::vector<int> edge(nchunk + 1);
+            for (int c = 0; c <= nchunk; ++c) edge[c] = std::min(N, (int)((long)nblk * c / nchunk) * 32);
+            for (int c = 0; c < nchunk; ++c) {                        // all launches are enqueued before the first copy: a copy into
+                launch_match_quantiles(d_cnt, G, g0, g1, d_mu_hat, d_bidx, d_order, N, d_phi_hat, d_gamma_star, d_phi_star,   // pageable memory blocks the host
+                                       d_keep_idx, G0, d_adj, st, edge[c], edge[c + 1]);
+                if (nchunk > 1) CBS_CUDA(cudaEventRecord(t_ctx->event("mq_chunk" + std::to_string(c)), st));
+            }
+            if (nchunk > 1) {
+                copied_by_columns = true;
+                for (int c = 0; c < nchunk; ++c) {
+                    CBS_CUDA(cudaStreamWaitEvent(st2, t_ctx->event("mq_chunk" + std::to_string(c)), 0));
+                    for (int si = edge[c]; si < edge[c + 1];) {       // runs of consecutive columns go out as one 2-D copy
+                        int sj = si + 1;
+                        while (sj < edge[c + 1] && order[sj] == order[sj - 1] + 1) ++sj;
+                        const size_t off = (size_t)r0 + (size_t)order[si] * G0;
+                        CBS_CUDA(cudaMemcpy2DAsync(out->adjusted + off, (size_t)G0 * sizeof(double), d_adj + off, (size_t)G0 * sizeof(double),
+                                                   (size_t)(r1 - r0) * sizeof(double), (size_t)(sj - si), cudaMemcpyDeviceToHost, st2));
+                        si = sj;
+                    }
+                }
+            }
         }
     }
     lap(CBS_ST_MATCH_QUANTILES);
@@ -236,7 +262,7 @@ static void pipeline(const cbs_input* in, cbs_output* out, const T* h_or_d_count
         CBS_CUDA(cudaMemcpy2DAsync(host + r0, (size_t)G0 * sizeof(double), dev_G0 + r0, (size_t)G0 * sizeof(double),
                                    (size_t)(r1 - r0) * sizeof(double), (size_t)ncols, cudaMemcpyDeviceToHost, st));
     };
-    if (out->adjusted && !out->adjusted_on_device) {
+    if (to_host && !copied_by_columns) {
         if (r0 == 0 && r1 == G0) CBS_CUDA(cudaMemcpyAsync(out->adjusted, d_adj, (size_t)G0 * N * sizeof(double), cudaMemcpyDeviceToHost, st));
         else fetch_rows(out->adjusted, d_adj, N);
     }
@@ -254,6 +280,7 @@ static void pipeline(const cbs_input* in, cbs_output* out, const T* h_or_d_count
     fetch_scattered(out->gamma_star, d_gamma_star, B, "out_gamma_star");
     fetch_scattered(out->phi_star, d_phi_star_mat, B, "out_phi_star");
     fetch_scattered(out->mu_hat, d_mu_hat, N, "out_mu_hat");
+    if (copied_by_columns) CBS_CUDA(cudaStreamSynchronize(st2));
     lap(CBS_ST_D2H);
     stage[CBS_ST_TOTAL] = now_ms() - t_start;
     if (out->stage_ms) memcpy(out->stage_ms, stage, sizeof stage);

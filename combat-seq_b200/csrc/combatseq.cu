@@ -151,6 +151,7 @@ int cbs_shutdown(void) {
             kv.second->cache.release(); kv.second->pin.release();
             for (auto& e : kv.second->events) cudaEventDestroy(e.second);
             kv.second->events.clear();
+            if (kv.second->st_copy) { cudaStreamDestroy(kv.second->st_copy); kv.second->st_copy = nullptr; }
         }
         cudaSetDevice(cur);
     }

@@ -142,6 +142,11 @@ struct DevCtx {
         events[name] = e;
         return e;
     }
+    cudaStream_t st_copy = nullptr;                          // second stream: D2H of finished output columns while kernels run
+    cudaStream_t copy_stream() {
+        if (!st_copy) CBS_CUDA(cudaStreamCreateWithFlags(&st_copy, cudaStreamNonBlocking));
+        return st_copy;
+    }
     std::map<std::pair<const void*, int>, int> func_attr;    // (kernel, attribute) -> value set on this device
     void set_func_attr(const void* func, cudaFuncAttribute attr, int value) {
         auto key = std::make_pair(func, (int)attr);

@@ -105,7 +105,8 @@ double fp64_mma_peak_tflops();
 // tu_mq.cu
 void launch_match_quantiles(const int32_t* cnt, long G, long g0, long g1, const double* mu_hat, const int* batch_idx,
                             const int* order, int N, const double* phi_hat, const double* gamma_star,
-                            const double* phi_star, const int* keep_idx, long G0, double* out, cudaStream_t st);
+                            const double* phi_star, const int* keep_idx, long G0, double* out, cudaStream_t st,
+                            int si_begin = 0, int si_end = -1);      // samples [si_begin, si_end) of the batch order (-1: all)
 void launch_match_quantiles_plain(const int32_t* cnt, long G, int n, const double* old_mu, const double* old_phi,
                                   const double* new_mu, const double* new_phi, double* out, cudaStream_t st);
 void launch_simulate_counts(long G, int N, const double* base_mu, const double* col_factor, const int* level,

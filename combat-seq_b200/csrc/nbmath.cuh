@@ -321,10 +321,10 @@ CBS_HD double bfrac_fast(double a, double b, double x, double y, double lambda) 
         const double ta = alpha * an + beta * anp1, tb = alpha * bn + beta * bnp1;
         const double inv = 1. / tb, r0 = r;
         r = ta * inv;
-        if (fabs(r - r0) <= eps * r) break;
+        if (fabs(r - r0) <= eps * r) return r;
         an = anp1 * inv; bn = bnp1 * inv; anp1 = r; bnp1 = 1.;
     } while (n < 10000);
-    return r;
+    return NAN;                                               // not converged: the callers take the general bratio routine
 }
 
 // F = P(X <= k), pmf = P(X = k) for X ~ NB(size, prob), q = 1 - prob, k a non-negative integer, 0 < prob < 1
@@ -337,6 +337,7 @@ CBS_HD NbCdf nb_cdf_pmf(double k, double size, double prob, double q) {
     if (brc == 0.) { o.F = (lambda >= 0) ? 0.0 : 1.0; return o; }      // prefactor underflow: far tail
     if (lambda >= 0) o.F = brc * bfrac_fast(a, b, prob, q, lambda);
     else o.F = 0.5 - brc * bfrac_fast(b, a, q, prob, -lambda) + 0.5;
+    if (!(o.F == o.F)) o.F = pnbinom_mu(k, size, size * q / prob);      // (the fraction hit its term cap: R's bratio picks another expansion there)
     return o;
 }
 
@@ -345,6 +346,7 @@ CBS_HD NbCdf nb_cdf_pmf(double k, double size, double prob, double q) {
 // cache, and its warps diverge onto different copies (ncu, round 1: "no instruction" = 24 % of the stall cycles).
 // Same arithmetic, same results; only the call structure differs.
 static __host__ __device__ __noinline__ double bfrac_fast_ni(double a, double b, double x, double y, double lambda) { return bfrac_fast(a, b, x, y, lambda); }
+static __host__ __device__ __noinline__ double pnbinom_mu_ni(double x, double size, double mu) { return pnbinom_mu(x, size, mu); }
 static __host__ __device__ __noinline__ NbCdf nb_cdf_pmf_ni(double k, double size, double prob, double q) {
     NbCdf o;                                                  // nb_cdf_pmf with ONE copy of the continued fraction
     const double a = size, b = k + 1.;
@@ -355,9 +357,9 @@ static __host__ __device__ __noinline__ NbCdf nb_cdf_pmf_ni(double k, double siz
     const bool fwd = lambda >= 0;
     const double cf = bfrac_fast_ni(fwd ? a : b, fwd ? b : a, fwd ? prob : q, fwd ? q : prob, fwd ? lambda : -lambda);
     o.F = fwd ? brc * cf : 0.5 - brc * cf + 0.5;
+    if (!(cf == cf)) o.F = pnbinom_mu_ni(k, size, size * q / prob);     // (the fraction hit its term cap: R's bratio picks another expansion there)
     return o;
 }
-static __host__ __device__ __noinline__ double pnbinom_mu_ni(double x, double size, double mu) { return pnbinom_mu(x, size, mu); }
 static __host__ __device__ __noinline__ double qnbinom_mu_ni(double p, double size, double mu) { return qnbinom_mu(p, size, mu); }
 template <bool NI> CBS_HD NbCdf nb_cdf_pmf_t(double k, double size, double prob, double q) {
     if (NI) return nb_cdf_pmf_ni(k, size, prob, q);

@@ -23,13 +23,13 @@ k_match_quantiles_warp(const int32_t* __restrict__ cnt, long G, long g0, long g1
                        const int* __restrict__ batch_idx, const int* __restrict__ order, int N,
                        const double* __restrict__ phi_hat, const double* __restrict__ gamma_star,
                        const double* __restrict__ phi_star, const int* __restrict__ keep_idx, long G0,
-                       double* __restrict__ out) {
+                       double* __restrict__ out, int si_begin, int si_end) {
     __shared__ double inv_s[MQ_INV_N];                          // 1/j for the small-count path (nbmath.cuh match_small)
     for (int j = threadIdx.x; j < MQ_INV_N; j += blockDim.x) inv_s[j] = j ? 1.0 / (double)j : 0.0;
     __syncthreads();
     const long g = g0 + (long)blockIdx.x * 4 + (threadIdx.x >> 5);
-    const int si = blockIdx.y * 32 + (threadIdx.x & 31);
-    if (g >= g1 || si >= N) return;
+    const int si = si_begin + blockIdx.y * 32 + (threadIdx.x & 31);     // position in batch order; [si_begin, si_end): this launch's share
+    if (g >= g1 || si >= si_end) return;
     const int s = order[si], b = batch_idx[s];
     const double x = (double)cnt[g + (long)s * G];
     const double old_mu = mu_hat[g + (long)s * G];
@@ -64,10 +64,12 @@ __global__ void k_nb_elementwise(int what, long n, const double* __restrict__ a,
 
 void launch_match_quantiles(const int32_t* cnt, long G, long g0, long g1, const double* mu_hat, const int* batch_idx,
                             const int* order, int N, const double* phi_hat, const double* gamma_star,
-                            const double* phi_star, const int* keep_idx, long G0, double* out, cudaStream_t st) {
-    if (g1 <= g0) return;
-    CBS_LAUNCH(k_match_quantiles_warp, dim3((unsigned)((g1 - g0 + 3) / 4), (unsigned)((N + 31) / 32)), 128, 0, st, cnt, G,
-               g0, g1, mu_hat, batch_idx, order, N, phi_hat, gamma_star, phi_star, keep_idx, G0, out);
+                            const double* phi_star, const int* keep_idx, long G0, double* out, cudaStream_t st,
+                            int si_begin, int si_end) {
+    if (si_end < 0) si_end = N;
+    if (g1 <= g0 || si_end <= si_begin) return;
+    CBS_LAUNCH(k_match_quantiles_warp, dim3((unsigned)((g1 - g0 + 3) / 4), (unsigned)((si_end - si_begin + 31) / 32)), 128, 0, st, cnt, G,
+               g0, g1, mu_hat, batch_idx, order, N, phi_hat, gamma_star, phi_star, keep_idx, G0, out, si_begin, si_end);
 }
 
 void launch_match_quantiles_plain(const int32_t* cnt, long G, int n, const double* old_mu, const double* old_phi,

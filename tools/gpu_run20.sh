@@ -2,5 +2,4 @@
 O=gpurun_out; mkdir -p $O
 timeout 900 python -m pytest tests -m gpu -q -rs > $O/r02_pytest_gpu_20.txt 2>&1; echo "rc=$?" >> $O/r02_pytest_gpu_20.txt
 timeout 600 python bench.py --steps 3 --warmup 2 --no-cpu > $O/r02_bench_c5_20.json 2> $O/r02_bench_c5_20.err
-timeout 300 python tools/sim_time.py > $O/r02_sim_time.txt 2>&1
 exit 0
