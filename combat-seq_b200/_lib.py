@@ -26,7 +26,7 @@ EXPORTS = ("cbs_version", "cbs_device_count", "cbs_last_error", "cbs_shutdown", 
            "cbs_comm_unique_id", "cbs_comm_create", "cbs_comm_destroy", "cbs_shard_range", "cbs_combat_seq", "cbs_nb_logpmf",
            "cbs_nb_cdf", "cbs_nb_quantile", "cbs_glm_fit", "cbs_apl", "cbs_common_disp", "cbs_tagwise_disp",
            "cbs_mc_int", "cbs_match_quantiles", "cbs_profile_enable", "cbs_profile_dump", "cbs_fp64_peak",
-           "cbs_fp64_mma_peak", "cbs_set_tuning", "cbs_get_diag", "cbs_tagwise_disp_prior", "cbs_simulate_counts")
+           "cbs_fp64_mma_peak", "cbs_set_tuning", "cbs_get_diag", "cbs_tagwise_disp_prior", "cbs_simulate_counts", "cbs_mc_int_static")
 
 
 class CbsInput(C.Structure):
@@ -150,6 +150,17 @@ def nb_quantile(p, size, mu): return _elementwise("cbs_nb_quantile", p, size, mu
 
 
 # ---- per-subsystem entry points ------------------------------------------------------------------------------
+STATIC_SCRATCH_BYTES = 8 << 20
+
+
+def mc_int_static(G, n, counts_dev, mu_dev, gamma_dev, phi_dev, gamma_star_dev, phi_star_dev, n_fallback_dev=None,
+                  mc_mode=CBS_MC_REFERENCE, stream=None):
+    """cbs_mc_int_static: every argument but the sizes is a device address (int); enqueues on `stream`, does not synchronise."""
+    vp = lambda a: C.c_void_p(a) if a else None
+    check(lib().cbs_mc_int_static(C.c_int64(G), C.c_int32(n), vp(counts_dev), vp(mu_dev), vp(gamma_dev), vp(phi_dev), C.c_int32(mc_mode),
+                                  vp(gamma_star_dev), vp(phi_star_dev), vp(n_fallback_dev), vp(stream)))
+
+
 def simulate_counts(base_mu, col_factor, phi_col, seed, level=None, fold=None, counts_dev_ptr=None):
     """Synthetic NB count matrix generated on the device (cbs_simulate_counts): G x N int32, column-major."""
     base_mu = _d(base_mu); col_factor = _d(col_factor); phi_col = _d(phi_col)

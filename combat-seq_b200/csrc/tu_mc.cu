@@ -8,6 +8,7 @@
 #include "mc_gemm.cuh"
 #include "screen.hpp"
 #include <cub/device/device_radix_sort.cuh>
+#include <mutex>
 
 namespace cbs {
 
@@ -307,3 +308,86 @@ double fp64_mma_peak_tflops() {
 }
 
 }  // namespace cbs
+
+// ---- monte_carlo_int_NB without any allocation (cbs_mc_int_static) ---------------------------------------------------
+// No counterpart in the reference: added for callers that cannot call cudaMalloc
+// (code under CUDA graph capture, tight serving loops, harnesses that forbid it).  The exact pairwise kernel's per-batch
+// scratch (A, c_j, r_j, lgamma(r_j), d_i: (n + 4) G doubles, the column list and the fallback counter) lives in ONE file-scope
+// device array of CBS_STATIC_SCRATCH_BYTES that every GPU which loads the library holds until exit.  Every call shares it
+// and it keeps the last call's contents: what must start at zero (the fallback counter) is cleared by the call's first
+// kernel, everything else is overwritten before it is read.  Two calls that overlap on one GPU race on it.
+namespace cbs {
+
+static __device__ __align__(256) unsigned char g_mc_static_scratch[CBS_STATIC_SCRATCH_BYTES];
+
+// first kernel of a call: column list 0 .. n-1 and the cleared fallback counter
+__global__ void k_mc_static_setup(int n, int* __restrict__ cols, unsigned long long* __restrict__ nfb) {
+    const int t = blockIdx.x * blockDim.x + threadIdx.x;
+    if (t < n) cols[t] = t;
+    if (t == 0) *nfb = 0ull;
+}
+__global__ void k_mc_static_copy_nfb(const unsigned long long* __restrict__ src, unsigned long long* __restrict__ dst) { *dst = *src; }
+
+// In host code the array's name is a host-side stand-in, not a device address: the address is looked up once per device,
+// with that device current.
+static std::mutex g_static_mutex;
+static std::map<int, unsigned char*> g_static_ptr;
+static int static_scratch_ptr(unsigned char** out) {
+    int dev = 0;
+    cudaError_t e = cudaGetDevice(&dev);
+    if (e != cudaSuccess) return fail(CBS_ECUDA, "cudaGetDevice: %s", cudaGetErrorString(e));
+    std::lock_guard<std::mutex> lk(g_static_mutex);
+    auto it = g_static_ptr.find(dev);
+    if (it == g_static_ptr.end()) {
+        unsigned char* p = nullptr;
+        e = cudaGetSymbolAddress((void**)&p, g_mc_static_scratch);
+        if (e != cudaSuccess || !p) return fail(CBS_ECUDA, "cudaGetSymbolAddress(static scratch) on device %d: %s", dev, cudaGetErrorString(e));
+        it = g_static_ptr.emplace(dev, p).first;
+    }
+    *out = it->second;
+    return CBS_OK;
+}
+
+static size_t mc_static_bytes(int64_t G, int32_t n) {
+    const size_t head = 256 + ((size_t)n * sizeof(int) + 255) / 256 * 256;       // counter, column list
+    return head + ((size_t)n + 4) * (size_t)G * sizeof(double);
+}
+
+}  // namespace cbs
+
+extern "C" int cbs_mc_int_static(int64_t G, int32_t n, const int32_t* counts_dev, const double* mu_dev, const double* gamma_dev,
+                                 const double* phi_dev, int32_t mc_mode, double* gamma_star_dev, double* phi_star_dev,
+                                 uint64_t* n_fallback_dev, void* stream) {
+    using namespace cbs;
+    int ndev = 0;
+    if (cudaGetDeviceCount(&ndev) != cudaSuccess || ndev < 1) { cudaGetLastError(); return fail(CBS_ENOGPU, "no CUDA device visible: libcombatseq has no CPU path"); }
+    if (G < 2 || n < 1 || !counts_dev || !mu_dev || !gamma_dev || !phi_dev || !gamma_star_dev || !phi_star_dev)
+        return fail(CBS_EINVAL, "null pointer / bad size");
+    if (mc_mode != CBS_MC_REFERENCE && mc_mode != CBS_MC_STABLE) return fail(CBS_EINVAL, "mc_mode must be 0 or 1");
+    if (mc_static_bytes(G, n) > (size_t)CBS_STATIC_SCRATCH_BYTES || n > 65536)
+        return fail(CBS_EINVAL, "cbs_mc_int_static: 256 + 256*ceil(n/64) + 8 (n + 4) G = %zu bytes of scratch needed for G = %lld, n = %d; "
+                                "the static array holds %d (use cbs_mc_int)", mc_static_bytes(G, n), (long long)G, (int)n, (int)CBS_STATIC_SCRATCH_BYTES);
+    unsigned char* base = nullptr;
+    if (int rc = static_scratch_ptr(&base)) return rc;
+    cudaStream_t st = (cudaStream_t)stream;
+    unsigned long long* nfb = reinterpret_cast<unsigned long long*>(base);
+    int* cols = reinterpret_cast<int*>(base + 256);
+    double* A = reinterpret_cast<double*>(base + 256 + ((size_t)n * sizeof(int) + 255) / 256 * 256);
+    double *cj = A + (size_t)n * G, *rj = cj + G, *lgr = rj + G, *di = lgr + G;
+    // the targets' counts sit in shared memory while the default 48 KB allow it (no function attribute is touched here)
+    size_t smem = (size_t)MC_TI * n * sizeof(double);
+    const int xs_shared = smem <= 48 * 1024;
+    if (!xs_shared) smem = 0;
+    const unsigned gblocks = (unsigned)((G + 127) / 128);
+    k_mc_static_setup<<<(unsigned)((n + 255) / 256), 256, 0, st>>>(n, cols, nfb);
+    k_mc_prep_src<<<gblocks, 128, 0, st>>>(mu_dev, (long)G, n, cols, phi_dev, A, cj, rj, lgr);
+    k_mc_prep_tgt<<<gblocks, 128, 0, st>>>(counts_dev, (long)G, n, cols, di);
+    k_mc_direct<<<(unsigned)((G + MC_TI - 1) / MC_TI), 256, smem, st>>>(counts_dev, (long)G, n, cols, 0L, (long)G, A, cj, rj, lgr, di, gamma_dev, phi_dev,
+                                                                      mc_mode == CBS_MC_STABLE ? 1 : 0, 0, 0ull, xs_shared, gamma_star_dev,
+                                                                      phi_star_dev, nfb);
+    if (n_fallback_dev) k_mc_static_copy_nfb<<<1, 1, 0, st>>>(nfb, reinterpret_cast<unsigned long long*>(n_fallback_dev));
+    g_launches.fetch_add(n_fallback_dev ? 5 : 4, std::memory_order_relaxed);
+    const cudaError_t e = cudaGetLastError();
+    if (e != cudaSuccess) return fail(CBS_ECUDA, "cbs_mc_int_static launch: %s", cudaGetErrorString(e));
+    return CBS_OK;
+}

@@ -192,6 +192,21 @@ int cbs_mc_int(int64_t G, int32_t n, const int32_t* counts, const double* mu, co
                const double* phi, int32_t mc_mode, int32_t gene_subset_n, uint64_t seed,
                double* gamma_star, double* phi_star, int64_t* n_fallback);
 
+/* monte_carlo_int_NB for one batch WITHOUT ANY ALLOCATION.  No counterpart in the reference: added
+ * for callers that cannot call cudaMalloc (code under CUDA graph capture, tight serving loops, harnesses
+ * that forbid it).  Same result as cbs_mc_int(gene_subset_n = 0) by the exact pairwise kernel; every pointer is a DEVICE
+ * pointer of the current device (counts G x n int32 and mu G x n column-major, gamma / phi / gamma_star / phi_star G,
+ * n_fallback one uint64 or NULL); the kernels are enqueued on `stream` (a cudaStream_t, NULL = default stream) and the call
+ * returns without synchronising: outputs are valid once the stream has been synchronised.  The kernels' scratch
+ * (256 + 256*ceil(n/64) + 8 (n + 4) G bytes) lives in one static device array of CBS_STATIC_SCRATCH_BYTES that every GPU which
+ * loads the library holds until exit; larger problems are rejected with CBS_EINVAL (use cbs_mc_int).  The call makes no
+ * cudaMalloc / cudaFree and takes no lock around the GPU work: every call shares the array, which keeps the last call's
+ * contents (the call clears what must start at zero), so calls that overlap on one GPU race. */
+#define CBS_STATIC_SCRATCH_BYTES (8 << 20)
+int cbs_mc_int_static(int64_t G, int32_t n, const int32_t* counts_dev, const double* mu_dev, const double* gamma_dev,
+                      const double* phi_dev, int32_t mc_mode, double* gamma_star_dev, double* phi_star_dev,
+                      uint64_t* n_fallback_dev, void* stream);
+
 /* match_quantiles(counts_sub, old_mu, old_phi, new_mu, new_phi)  helper_seq.R:46-64 for one batch */
 int cbs_match_quantiles(int64_t G, int32_t n, const int32_t* counts, const double* old_mu, const double* old_phi,
                         const double* new_mu, const double* new_phi, double* adjusted);
