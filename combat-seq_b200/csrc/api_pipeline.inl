@@ -49,6 +49,9 @@ __global__ void k_unshard_counts(const T* __restrict__ recv, long G0, int N, lon
     const long rk = g / per;
     dst[g + (long)s * G0] = recv[((long)rk * N + s) * per + (g - rk * per)];
 }
+// a big PAGEABLE caller buffer goes through the pinned staging of host_bridge.hpp
+static bool bridge_wanted(const void* host, size_t bytes) { return bytes >= ((size_t)16 << 20) && is_pageable(host); }
+
 template <class T>
 static const T* upload_counts_sharded(const T* h_counts, long G0, int N, cbs_comm* comm, cudaStream_t st) {
     const int world = comm->world, rank = comm->rank;
@@ -58,8 +61,12 @@ static const T* upload_counts_sharded(const T* h_counts, long G0, int N, cbs_com
     T* recv = g_dev.get<T>("counts_recv", (size_t)per * N * world);
     T* dst = g_dev.get<T>("counts_in", (size_t)G0 * N);
     if (b > a)
-        CBS_CUDA(cudaMemcpy2DAsync(send, (size_t)per * sizeof(T), h_counts + a, (size_t)G0 * sizeof(T), (size_t)(b - a) * sizeof(T),
-                                   (size_t)N, cudaMemcpyHostToDevice, st));
+        if (bridge_wanted(h_counts, (size_t)(b - a) * N * sizeof(T)))
+            bridge_run(t_ctx, {BridgeJob{(char*)(h_counts + a), (size_t)G0 * sizeof(T), (char*)send, (size_t)per * sizeof(T),
+                                         (size_t)(b - a) * sizeof(T), (size_t)N, nullptr}}, true);
+        else
+            CBS_CUDA(cudaMemcpy2DAsync(send, (size_t)per * sizeof(T), h_counts + a, (size_t)G0 * sizeof(T), (size_t)(b - a) * sizeof(T),
+                                       (size_t)N, cudaMemcpyHostToDevice, st));
     CBS_NCCL(nccl_api()->AllGather(send, recv, (size_t)per * N * sizeof(T), NCCL_INT8, comm->nccl, st));
     CBS_LAUNCH(k_unshard_counts<T>, dim3((unsigned)((G0 + 255) / 256), (unsigned)N), 256, 0, st, (const T*)recv, G0, N, per, dst);
     return dst;
@@ -89,7 +96,12 @@ static void pipeline(const cbs_input* in, cbs_output* out, const T* h_or_d_count
     const T* d_in;
     if (in->counts_on_device) d_in = h_or_d_counts;
     else if (world > 1) d_in = upload_counts_sharded<T>(h_or_d_counts, G0, N, comm, st);
-    else d_in = upload(g_dev, "counts_in", h_or_d_counts, (size_t)G0 * N, st);
+    else if (bridge_wanted(h_or_d_counts, (size_t)G0 * N * sizeof(T))) {      // pageable caller buffer (an R matrix): staged by worker threads
+        T* d = g_dev.get<T>("counts_in", (size_t)G0 * N);
+        bridge_run(t_ctx, {BridgeJob{(char*)h_or_d_counts, (size_t)G0 * sizeof(T), (char*)d, (size_t)G0 * sizeof(T), (size_t)G0 * sizeof(T),
+                                     (size_t)N, nullptr}}, true);
+        d_in = d;
+    } else d_in = upload(g_dev, "counts_in", h_or_d_counts, (size_t)G0 * N, st);
     int* d_bidx = upload(g_dev, "batch_idx", in->batch_idx, (size_t)N, st);
     lap(CBS_ST_H2D);
 
@@ -240,17 +252,25 @@ static void pipeline(const cbs_input* in, cbs_output* out, const T* h_or_d_count
             }
             if (nchunk > 1) {
                 copied_by_columns = true;
+                const bool bridge = bridge_wanted(out->adjusted, (size_t)(r1 - r0) * N * sizeof(double));
+                std::vector<BridgeJob> jobs;
                 for (int c = 0; c < nchunk; ++c) {
-                    CBS_CUDA(cudaStreamWaitEvent(st2, t_ctx->event("mq_chunk" + std::to_string(c)), 0));
+                    cudaEvent_t done = t_ctx->event("mq_chunk" + std::to_string(c));
+                    if (!bridge) CBS_CUDA(cudaStreamWaitEvent(st2, done, 0));
                     for (int si = edge[c]; si < edge[c + 1];) {       // runs of consecutive columns go out as one 2-D copy
                         int sj = si + 1;
                         while (sj < edge[c + 1] && order[sj] == order[sj - 1] + 1) ++sj;
                         const size_t off = (size_t)r0 + (size_t)order[si] * G0;
-                        CBS_CUDA(cudaMemcpy2DAsync(out->adjusted + off, (size_t)G0 * sizeof(double), d_adj + off, (size_t)G0 * sizeof(double),
-                                                   (size_t)(r1 - r0) * sizeof(double), (size_t)(sj - si), cudaMemcpyDeviceToHost, st2));
+                        if (bridge)
+                            jobs.push_back({(char*)(out->adjusted + off), (size_t)G0 * sizeof(double), (char*)(d_adj + off), (size_t)G0 * sizeof(double),
+                                            (size_t)(r1 - r0) * sizeof(double), (size_t)(sj - si), done});
+                        else
+                            CBS_CUDA(cudaMemcpy2DAsync(out->adjusted + off, (size_t)G0 * sizeof(double), d_adj + off, (size_t)G0 * sizeof(double),
+                                                       (size_t)(r1 - r0) * sizeof(double), (size_t)(sj - si), cudaMemcpyDeviceToHost, st2));
                         si = sj;
                     }
                 }
+                if (bridge) bridge_run(t_ctx, jobs, false);           // pageable caller buffer: staged by worker threads
             }
         }
     }

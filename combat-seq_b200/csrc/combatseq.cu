@@ -5,6 +5,7 @@
 // CUDA device every compute entry returns CBS_ENOGPU.
 #include "engine.hpp"
 #include "prep_kernels.cuh"
+#include "host_bridge.hpp"
 #include <dlfcn.h>
 #include <chrono>
 #include <mutex>

@@ -213,3 +213,22 @@ def test_glm_wide_second_pass_agrees_with_the_single_pass(pkg, synth):
     assert np.array_equal(two["adjusted"], one["adjusted"])
     same = np.all((two["gamma_hat"] == one["gamma_hat"]) | np.isnan(one["gamma_hat"]), axis=1)
     assert same.mean() > 0.99
+
+
+def test_pageable_buffers_take_the_staged_copies_and_give_the_same_matrix(pkg, synth):
+    """Caller buffers of 16 MB and more in pageable memory (an R matrix) are copied by worker threads through pinned staging
+    (host_bridge.hpp), pinned ones directly: same bits either way."""
+    torch = pytest.importorskip("torch")
+    L = pkg._lib
+    case = synth.CASES["C5"](G=2200, n=100, B=10)                       # 2200 x 1000 doubles = 17.6 MB in, 17.6 MB out
+    d = pkg.design.build_design(case.counts.shape[1], case.batch, case.group, case.covar_mod, case.full_mod)
+    G0, N = case.counts.shape
+    page_in = np.asfortranarray(case.counts.astype(np.float64))
+    page_out = np.full((G0, N), -1.0, order="F")
+    L.combat_seq_into(page_in, d.batch_idx, d.mod, page_out, shrink=False, shrink_disp=False)
+    pin_in = torch.empty((N, G0), dtype=torch.float64, pin_memory=True)
+    pin_in.numpy()[:] = case.counts.T
+    pin_out = torch.full((N, G0), -1.0, dtype=torch.float64, pin_memory=True)
+    L.combat_seq_into(pin_in.numpy().T, d.batch_idx, d.mod, pin_out.numpy().T, shrink=False, shrink_disp=False)
+    assert np.array_equal(page_out, pin_out.numpy().T)
+    assert page_out.min() >= 0 and not np.array_equal(page_out, page_in)
