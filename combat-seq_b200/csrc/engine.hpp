@@ -16,6 +16,7 @@ struct Tuning {
     int mc_band = 1;             // 1 = abundance-sorted sources + screened source-tile lists for the contraction, 0 = all tiles
     int glm_scr = 1;             // 1 = Levenberg work arrays of the lane-group GLM kernel in shared memory (one copy per gene)
     int apl_fast = 1;            // 1 = lgamma tables + hoisted invariants in the APL kernel (same bits), 0 = per-sample calls
+    int mq_bins = 1;             // 1 = match_quantiles over elements binned by count (uniform work per warp), 0 = lane = sample
     int apl_lanes = 1;           // 1 = lane-group APL kernel with the batch row staged in shared memory (one-way designs), 0 = k_apl
     int glm_two_pass = 1;        // 1 = fits that need more than 9 sweeps are redone by a warp per gene (k_glm_fit_wide)
     int glm_hist = 0;            // 1 = histogram of Levenberg iterations per gene (diagnostics; cbs_get_diag "glm_iter_*")

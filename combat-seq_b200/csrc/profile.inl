@@ -69,6 +69,7 @@ int cbs_set_tuning(const char* key, double value) {
     if (!strcmp(key, "mc_band")) { g_tune.mc_band = value != 0; return CBS_OK; }
     if (!strcmp(key, "mc_tail_tol")) { g_tune.mc_tail_tol = value; return CBS_OK; }
     if (!strcmp(key, "apl_fast")) { g_tune.apl_fast = value != 0; return CBS_OK; }
+    if (!strcmp(key, "mq_bins")) { g_tune.mq_bins = value != 0; return CBS_OK; }
     if (!strcmp(key, "apl_lanes")) { g_tune.apl_lanes = value != 0; return CBS_OK; }
     if (!strcmp(key, "glm_hist")) {
         g_tune.glm_hist = value != 0;

@@ -37,6 +37,97 @@ k_match_quantiles_warp(const int32_t* __restrict__ cnt, long G, long g0, long g1
     out[(keep_idx ? (long)keep_idx[g] : g) + (long)s * G0] = match_one_fast<true>(x, old_mu, phi_hat[g + (long)b * G], new_mu, phi_star[g], inv_s);
 }
 
+// ---- binned form: a warp's 32 lanes get elements with the same amount of work ------------------------------------------
+// The cost of an element is its count: the small-count path sums x terms of the old and about x * new_mu / old_mu terms of
+// the new distribution, the continued fractions need O(sqrt x) terms.  With lane = sample the 32 counts of a warp are NB draws
+// around the gene's mean: the longest lane ran about twice the average (ncu, round 2: half of the lanes active on average).
+// Here the elements with x >= 2 (the others are pass-throughs, already in the pre-filled output) are put into 256 bins by a
+// counting sort on the device (histogram, scan, scatter of element indices: two streaming passes over the counts), the key
+// being the quarter-octave of x (1 + new_mu / old_mu), small-count and continued-fraction elements in separate halves, and
+// k_match_quantiles_binned gives consecutive index entries to consecutive lanes.  One thread per element and the same
+// routine as before: the results are the same bits (test_kernel_variants_give_the_same_bits, "mq_bins").
+constexpr int MQ_BINS = 256;
+__device__ __forceinline__ int mq_bin_key(double x, double gamma_star) {
+    double ratio = exp(-gamma_star);                                   // new_mu / old_mu  (ComBat_seq.R:176)
+    ratio = fmin(fmax(ratio, 0.0), 64.0);                              // (NaN -> 64)
+    const double w = x * (1.0 + ratio);                                // >= 2
+    int k = ((__double2hiint(w) >> 18) & 0x1FFF) - (1023 << 2);        // exponent and the top two mantissa bits
+    k = min(max(k, 0), MQ_BINS / 2 - 1);
+    return k + (x > MQ_SMALL_X ? MQ_BINS / 2 : 0);
+}
+
+// grid (ceil(ng / 256), nsi), block 256.  pass 0: hist[key]++.  pass 1: ids[cursor[key]++] = element index
+// (gene - g0) + (sample position - si_begin) * ng, the block reserving one range per bin.
+template <int PASS>
+__global__ void __launch_bounds__(256)
+k_mq_bin(const int32_t* __restrict__ cnt, long G, long g0, long g1, const int* __restrict__ batch_idx,
+         const int* __restrict__ order, int si_begin, const double* __restrict__ gamma_star, int* __restrict__ hist,
+         int* __restrict__ cursor, int* __restrict__ ids) {
+    __shared__ int cnt_s[MQ_BINS], base_s[MQ_BINS];
+    cnt_s[threadIdx.x] = 0;
+    __syncthreads();
+    const long ng = g1 - g0, gl = (long)blockIdx.x * 256 + threadIdx.x;
+    const int sl = blockIdx.y, s = order[si_begin + sl];
+    int key = -1, rank = 0;
+    if (gl < ng) {
+        const long g = g0 + gl;
+        const int x = cnt[g + (long)s * G];
+        if (x >= 2) {
+            key = mq_bin_key((double)x, gamma_star[g + (long)batch_idx[s] * G]);
+            rank = atomicAdd(&cnt_s[key], 1);
+        }
+    }
+    __syncthreads();
+    const int c = cnt_s[threadIdx.x];
+    if (PASS == 0) { if (c) atomicAdd(&hist[threadIdx.x], c); return; }
+    base_s[threadIdx.x] = c ? atomicAdd(&cursor[threadIdx.x], c) : 0;
+    __syncthreads();
+    if (key >= 0) ids[base_s[key] + rank] = (int)(gl + (long)sl * ng);
+}
+// cursor = exclusive scan of hist; cursor[MQ_BINS] = number of elements
+__global__ void __launch_bounds__(MQ_BINS) k_mq_bin_scan(const int* __restrict__ hist, int* __restrict__ cursor) {
+    __shared__ int sc[MQ_BINS];
+    const int v = hist[threadIdx.x];
+    sc[threadIdx.x] = v;
+    __syncthreads();
+    for (int o = 1; o < MQ_BINS; o <<= 1) {
+        const int a = (int)threadIdx.x >= o ? sc[threadIdx.x - o] : 0;
+        __syncthreads();
+        sc[threadIdx.x] += a;
+        __syncthreads();
+    }
+    cursor[threadIdx.x] = sc[threadIdx.x] - v;
+    if (threadIdx.x == MQ_BINS - 1) cursor[MQ_BINS] = sc[threadIdx.x];
+}
+
+__global__ void __launch_bounds__(128, CBS_MQ_MINBLOCKS)
+k_match_quantiles_binned(const int32_t* __restrict__ cnt, long G, long g0, long ng, const double* __restrict__ mu_hat,
+                         const int* __restrict__ batch_idx, const int* __restrict__ order, int si_begin,
+                         const double* __restrict__ phi_hat, const double* __restrict__ gamma_star,
+                         const double* __restrict__ phi_star, const int* __restrict__ keep_idx, long G0,
+                         double* __restrict__ out, const int* __restrict__ ids, const int* __restrict__ total,
+                         const double* __restrict__ inv_tab) {
+    __shared__ double inv_s[MQ_INV_N];
+    const long k0 = (long)blockIdx.x * blockDim.x;
+    const int n_el = *total;
+    if (k0 >= n_el) return;                                     // (the grid covers the chunk; the list is shorter)
+    for (int j = threadIdx.x; j < MQ_INV_N; j += blockDim.x) inv_s[j] = inv_tab[j];
+    __syncthreads();
+    const long k = k0 + threadIdx.x;
+    if (k >= n_el) return;
+    const int e = ids[k];
+    const long g = g0 + e % ng;
+    const int s = order[si_begin + (int)(e / ng)], b = batch_idx[s];
+    const double x = (double)cnt[g + (long)s * G];
+    const double old_mu = mu_hat[g + (long)s * G];
+    const double new_mu = exp(log(old_mu) - gamma_star[g + (long)b * G]);     // ComBat_seq.R:176
+    out[(keep_idx ? (long)keep_idx[g] : g) + (long)s * G0] = match_one_fast<true>(x, old_mu, phi_hat[g + (long)b * G], new_mu, phi_star[g], inv_s);
+}
+__global__ void k_mq_inv_table(double* __restrict__ t) {
+    const int j = blockIdx.x * blockDim.x + threadIdx.x;
+    if (j < MQ_INV_N) t[j] = j ? 1.0 / (double)j : 0.0;
+}
+
 // generic per-batch form used by cbs_match_quantiles (explicit new_mu)
 __global__ void __launch_bounds__(128)
 k_match_quantiles_plain(const int32_t* __restrict__ cnt, long G, int n, const double* __restrict__ old_mu,
@@ -68,6 +159,26 @@ void launch_match_quantiles(const int32_t* cnt, long G, long g0, long g1, const 
                             int si_begin, int si_end) {
     if (si_end < 0) si_end = N;
     if (g1 <= g0 || si_end <= si_begin) return;
+    const long ng = g1 - g0, nsi = si_end - si_begin;
+    // binned form: needs the pre-filled output for the pass-through elements (the pipeline's k_counts_to_f64) and element
+    // indices that fit an int
+    if (g_tune.mq_bins && ng * nsi < 2000000000L && nsi <= 65535) {
+        int* hist = g_dev.get<int>("mq_hist", 2 * MQ_BINS + 2);
+        int* cursor = hist + MQ_BINS;
+        int* ids = g_dev.get<int>("mq_ids", (size_t)(ng * nsi));
+        double* inv_tab = g_dev.get<double>("mq_inv", MQ_INV_N);
+        CBS_CUDA(cudaMemsetAsync(hist, 0, (2 * MQ_BINS + 2) * sizeof(int), st));
+        CBS_LAUNCH(k_mq_inv_table, dim3(MQ_INV_N / 256), 256, 0, st, inv_tab);
+        const dim3 bgrid((unsigned)((ng + 255) / 256), (unsigned)nsi);
+        CBS_LAUNCH(k_mq_bin<0>, bgrid, 256, 0, st, cnt, G, g0, g1, batch_idx, order, si_begin, gamma_star, hist, cursor, ids);
+        CBS_LAUNCH(k_mq_bin_scan, dim3(1), MQ_BINS, 0, st, (const int*)hist, cursor);
+        CBS_LAUNCH(k_mq_bin<1>, bgrid, 256, 0, st, cnt, G, g0, g1, batch_idx, order, si_begin, gamma_star, hist, cursor, ids);
+        // after the scatter cursor[k] is the END of bin k: cursor[MQ_BINS - 1] = cursor[MQ_BINS] = number of elements
+        CBS_LAUNCH(k_match_quantiles_binned, dim3((unsigned)((ng * nsi + 127) / 128)), 128, 0, st, cnt, G, g0, ng, mu_hat, batch_idx,
+                   order, si_begin, phi_hat, gamma_star, phi_star, keep_idx, G0, out, (const int*)ids, (const int*)(cursor + MQ_BINS),
+                   (const double*)inv_tab);
+        return;
+    }
     CBS_LAUNCH(k_match_quantiles_warp, dim3((unsigned)((g1 - g0 + 3) / 4), (unsigned)((si_end - si_begin + 31) / 32)), 128, 0, st, cnt, G,
                g0, g1, mu_hat, batch_idx, order, N, phi_hat, gamma_star, phi_star, keep_idx, G0, out, si_begin, si_end);
 }

@@ -81,6 +81,8 @@ int         cbs_fp64_mma_peak(double* tflops);   /* same for the FP64 tensor pip
  *                  exceeds it is redone with the direct kernel when mc_algo = 0
  *   "apl_fast"     1 (default) = lgamma tables, hoisted log/lgamma of 1/phi and product-form mu in the APL kernel
  *                  (last-place differences); 0 = one call per sample
+ *   "mq_bins"      1 (default) = match_quantiles visits the elements binned by count, so that the lanes of a warp have the same
+ *                  amount of work; 0 = one warp per gene, lane = sample (same bits)
  *   "glm_scr"      1 (default) = Levenberg work arrays of the lane-group GLM kernel in shared memory; 0 = local memory
  *                  (same bits)
  * cbs_get_diag keys: "mc_tail" (largest tail estimate since the last reset), "mc_terms" (Chebyshev terms of the

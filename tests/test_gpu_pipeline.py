@@ -145,8 +145,8 @@ def test_int32_and_float_inputs_agree(pkg, synth):
 
 
 def test_kernel_variants_give_the_same_bits(pkg, synth):
-    """The restructured GLM kernel keeps every result bit for bit: Levenberg work arrays shared by a gene's lane group vs
-    per-lane local copies ("glm_scr").  A design crossed inside the batches (Levenberg path, class sweeps) and a one-way one."""
+    """The restructured kernels keep every result bit for bit: Levenberg work arrays shared by a gene's lane group vs
+    per-lane local copies ("glm_scr"); match_quantiles over elements binned by count vs one warp per gene ("mq_bins").  A design crossed inside the batches (Levenberg path, class sweeps) and a one-way one."""
     L = pkg._lib
     for case in (synth.c3(G=1500, crossed=True), synth.c5(G=1200, n=12, B=3)):
         d = pkg.design.build_design(case.counts.shape[1], case.batch, case.group, case.covar_mod, case.full_mod)
@@ -157,8 +157,11 @@ def test_kernel_variants_give_the_same_bits(pkg, synth):
             for glm_scr in (1, 0):
                 L.set_tuning("glm_scr", glm_scr)
                 outs.append(L.combat_seq_raw(case.counts, d.batch_idx, d.mod, shrink=case.shrink, shrink_disp=case.shrink_disp, want=want))
+            L.set_tuning("glm_scr", 1)
+            L.set_tuning("mq_bins", 0)               # match_quantiles: lane = sample instead of elements binned by count
+            outs.append(L.combat_seq_raw(case.counts, d.batch_idx, d.mod, shrink=case.shrink, shrink_disp=case.shrink_disp, want=want))
         finally:
-            L.set_tuning("glm_scr", 1); L.set_tuning("glm_two_pass", 1)
+            L.set_tuning("glm_scr", 1); L.set_tuning("glm_two_pass", 1); L.set_tuning("mq_bins", 1)
         for o in outs[1:]:
             for k in want:
                 assert np.array_equal(outs[0][k], o[k], equal_nan=True), k
