@@ -47,42 +47,54 @@ k_match_quantiles_warp(const int32_t* __restrict__ cnt, long G, long g0, long g1
 // k_match_quantiles_binned gives consecutive index entries to consecutive lanes.  One thread per element and the same
 // routine as before: the results are the same bits (test_kernel_variants_give_the_same_bits, "mq_bins").
 constexpr int MQ_BINS = 256;
-__device__ __forceinline__ int mq_bin_key(double x, double gamma_star) {
-    double ratio = exp(-gamma_star);                                   // new_mu / old_mu  (ComBat_seq.R:176)
-    ratio = fmin(fmax(ratio, 0.0), 64.0);                              // (NaN -> 64)
-    const double w = x * (1.0 + ratio);                                // >= 2
-    int k = ((__double2hiint(w) >> 18) & 0x1FFF) - (1023 << 2);        // exponent and the top two mantissa bits
+__device__ __forceinline__ int mq_bin_key(int x, double gamma_star) {
+    // (single precision: the key only balances the work; both passes compute it with the same instructions)
+    float ratio = __expf(-(float)gamma_star);                          // new_mu / old_mu  (ComBat_seq.R:176)
+    ratio = fminf(fmaxf(ratio, 0.f), 64.f);                            // (NaN -> 64)
+    const float w = (float)x * (1.f + ratio);                          // >= 2
+    int k = ((__float_as_int(w) >> 21) & 0x3FF) - (127 << 2);          // exponent and the top two mantissa bits
     k = min(max(k, 0), MQ_BINS / 2 - 1);
-    return k + (x > MQ_SMALL_X ? MQ_BINS / 2 : 0);
+    return k + (x > (int)MQ_SMALL_X ? MQ_BINS / 2 : 0);
 }
 
-// grid (ceil(ng / 256), nsi), block 256.  pass 0: hist[key]++.  pass 1: ids[cursor[key]++] = element index
-// (gene - g0) + (sample position - si_begin) * ng, the block reserving one range per bin.
+// grid (ceil(ng / 256), ceil(nsi / MQ_BIN_SPB)), block 256: a block takes 256 genes x MQ_BIN_SPB sample positions (one sample
+// per block made the two passes block-turnover bound: 235 000 blocks of a microsecond each per pass on C5).
+// pass 0: hist[key] += count.  pass 1: ids[cursor[key]++] = element index (gene - g0) + (sample position - si_begin) * ng,
+// the block reserving one range per bin.
+constexpr int MQ_BIN_SPB = 8;
 template <int PASS>
 __global__ void __launch_bounds__(256)
 k_mq_bin(const int32_t* __restrict__ cnt, long G, long g0, long g1, const int* __restrict__ batch_idx,
-         const int* __restrict__ order, int si_begin, const double* __restrict__ gamma_star, int* __restrict__ hist,
+         const int* __restrict__ order, int si_begin, int nsi, const double* __restrict__ gamma_star, int* __restrict__ hist,
          int* __restrict__ cursor, int* __restrict__ ids) {
-    __shared__ int cnt_s[MQ_BINS], base_s[MQ_BINS];
+    __shared__ int cnt_s[MQ_BINS];
     cnt_s[threadIdx.x] = 0;
     __syncthreads();
     const long ng = g1 - g0, gl = (long)blockIdx.x * 256 + threadIdx.x;
-    const int sl = blockIdx.y, s = order[si_begin + sl];
-    int key = -1, rank = 0;
-    if (gl < ng) {
-        const long g = g0 + gl;
-        const int x = cnt[g + (long)s * G];
-        if (x >= 2) {
-            key = mq_bin_key((double)x, gamma_star[g + (long)batch_idx[s] * G]);
-            rank = atomicAdd(&cnt_s[key], 1);
+    const int sl0 = blockIdx.y * MQ_BIN_SPB, sl1 = min(nsi, sl0 + MQ_BIN_SPB);
+    int keys[MQ_BIN_SPB];
+#pragma unroll
+    for (int u = 0; u < MQ_BIN_SPB; ++u) {
+        keys[u] = -1;
+        if (gl < ng && sl0 + u < sl1) {
+            const int s = order[si_begin + sl0 + u];
+            const long g = g0 + gl;
+            const int x = cnt[g + (long)s * G];
+            if (x >= 2) {
+                keys[u] = mq_bin_key(x, gamma_star[g + (long)batch_idx[s] * G]);
+                atomicAdd(&cnt_s[keys[u]], 1);
+            }
         }
     }
     __syncthreads();
     const int c = cnt_s[threadIdx.x];
     if (PASS == 0) { if (c) atomicAdd(&hist[threadIdx.x], c); return; }
-    base_s[threadIdx.x] = c ? atomicAdd(&cursor[threadIdx.x], c) : 0;
     __syncthreads();
-    if (key >= 0) ids[base_s[key] + rank] = (int)(gl + (long)sl * ng);
+    cnt_s[threadIdx.x] = c ? atomicAdd(&cursor[threadIdx.x], c) : 0;       // now the block's write position in every bin
+    __syncthreads();
+#pragma unroll
+    for (int u = 0; u < MQ_BIN_SPB; ++u)
+        if (keys[u] >= 0) ids[atomicAdd(&cnt_s[keys[u]], 1)] = (int)(gl + (long)(sl0 + u) * ng);
 }
 // cursor = exclusive scan of hist; cursor[MQ_BINS] = number of elements
 __global__ void __launch_bounds__(MQ_BINS) k_mq_bin_scan(const int* __restrict__ hist, int* __restrict__ cursor) {
@@ -169,10 +181,10 @@ void launch_match_quantiles(const int32_t* cnt, long G, long g0, long g1, const 
         double* inv_tab = g_dev.get<double>("mq_inv", MQ_INV_N);
         CBS_CUDA(cudaMemsetAsync(hist, 0, (2 * MQ_BINS + 2) * sizeof(int), st));
         CBS_LAUNCH(k_mq_inv_table, dim3(MQ_INV_N / 256), 256, 0, st, inv_tab);
-        const dim3 bgrid((unsigned)((ng + 255) / 256), (unsigned)nsi);
-        CBS_LAUNCH(k_mq_bin<0>, bgrid, 256, 0, st, cnt, G, g0, g1, batch_idx, order, si_begin, gamma_star, hist, cursor, ids);
+        const dim3 bgrid((unsigned)((ng + 255) / 256), (unsigned)((nsi + MQ_BIN_SPB - 1) / MQ_BIN_SPB));
+        CBS_LAUNCH(k_mq_bin<0>, bgrid, 256, 0, st, cnt, G, g0, g1, batch_idx, order, si_begin, (int)nsi, gamma_star, hist, cursor, ids);
         CBS_LAUNCH(k_mq_bin_scan, dim3(1), MQ_BINS, 0, st, (const int*)hist, cursor);
-        CBS_LAUNCH(k_mq_bin<1>, bgrid, 256, 0, st, cnt, G, g0, g1, batch_idx, order, si_begin, gamma_star, hist, cursor, ids);
+        CBS_LAUNCH(k_mq_bin<1>, bgrid, 256, 0, st, cnt, G, g0, g1, batch_idx, order, si_begin, (int)nsi, gamma_star, hist, cursor, ids);
         // after the scatter cursor[k] is the END of bin k: cursor[MQ_BINS - 1] = cursor[MQ_BINS] = number of elements
         CBS_LAUNCH(k_match_quantiles_binned, dim3((unsigned)((ng * nsi + 127) / 128)), 128, 0, st, cnt, G, g0, ng, mu_hat, batch_idx,
                    order, si_begin, phi_hat, gamma_star, phi_star, keep_idx, G0, out, (const int*)ids, (const int*)(cursor + MQ_BINS),
