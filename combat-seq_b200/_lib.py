@@ -11,6 +11,26 @@ import numpy as np
 HERE = os.path.dirname(os.path.abspath(__file__))
 LIB_PATH = os.environ.get("COMBATSEQ_LIB") or os.path.join(HERE, "libcombatseq.so")   # (override: development builds)
 
+
+def _prefer_bundled_nccl():
+    """If this Python has the NCCL wheel PyTorch uses (nvidia/nccl/lib/libnccl.so.2), let the library dlopen that one
+    (COMBATSEQ_NCCL) instead of an older system NCCL: whichever libnccl.so.2 is mapped first also serves a later `import torch`."""
+    if os.environ.get("COMBATSEQ_NCCL"):
+        return
+    try:
+        import importlib.util
+        spec = importlib.util.find_spec("nvidia.nccl")
+        for root in (spec.submodule_search_locations if spec else []):
+            cand = os.path.join(root, "lib", "libnccl.so.2")
+            if os.path.exists(cand):
+                os.environ["COMBATSEQ_NCCL"] = cand
+                return
+    except (ImportError, ValueError, AttributeError):
+        pass
+
+
+_prefer_bundled_nccl()
+
 f64p = C.POINTER(C.c_double)
 i32p = C.POINTER(C.c_int32)
 i64p = C.POINTER(C.c_int64)

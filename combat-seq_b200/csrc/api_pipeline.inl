@@ -109,7 +109,11 @@ static void pipeline(const cbs_input* in, cbs_output* out, const T* h_or_d_count
     unsigned char* d_keep = g_dev.get<unsigned char>("keep", (size_t)G0);
     int* d_bad = g_dev.get<int>("bad_counts", 1);
     CBS_CUDA(cudaMemsetAsync(d_bad, 0, sizeof(int), st));
-    CBS_LAUNCH(k_keep_mask<T>, grid1(G0, 128), 128, 0, st, d_in, G0, N, d_bidx, B, d_keep, d_bad);
+    unsigned long long* d_seen = g_dev.get<unsigned long long>("keep_seen", (size_t)2 * G0);
+    CBS_CUDA(cudaMemsetAsync(d_seen, 0, (size_t)2 * G0 * sizeof(unsigned long long), st));
+    CBS_LAUNCH(k_keep_mask<T>, dim3((unsigned)((G0 + 127) / 128), (unsigned)std::max(1, std::min(16, N / 32))), 128, 0, st, d_in, G0, N,
+               d_bidx, d_seen, d_bad);
+    CBS_LAUNCH(k_keep_finish, grid1(G0, 256), 256, 0, st, (const unsigned long long*)d_seen, G0, B, d_keep);
     std::vector<unsigned char> keep(G0);
     int bad = 0;
     CBS_CUDA(cudaMemcpyAsync(keep.data(), d_keep, (size_t)G0, cudaMemcpyDeviceToHost, st));

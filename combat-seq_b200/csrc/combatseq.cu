@@ -49,8 +49,11 @@ NcclApi* nccl_api() {
     if (api.handle) return &api;
     if (tried) return nullptr;
     tried = true;
-    const char* names[] = {"libnccl.so.2", "libnccl.so"};
-    for (const char* n : names) { api.handle = dlopen(n, RTLD_NOW | RTLD_GLOBAL); if (api.handle) break; }
+    // COMBATSEQ_NCCL names the library to load first.  It matters when the process maps another libnccl.so.2 LATER (PyTorch
+    // bundles its own, newer one): the dynamic loader resolves that later request to whatever libnccl.so.2 is already mapped,
+    // so loading an older system NCCL here first makes a subsequent `import torch` fail on a missing symbol.
+    const char* names[] = {getenv("COMBATSEQ_NCCL"), "libnccl.so.2", "libnccl.so"};
+    for (const char* n : names) { if (!n || !*n) continue; api.handle = dlopen(n, RTLD_NOW | RTLD_GLOBAL); if (api.handle) break; }
     if (!api.handle) { fail(CBS_ENCCL, "cannot dlopen libnccl.so.2: %s", dlerror()); return nullptr; }
     auto sym = [&](const char* s) { return dlsym(api.handle, s); };
     api.GetUniqueId = (int (*)(void*))sym("ncclGetUniqueId");

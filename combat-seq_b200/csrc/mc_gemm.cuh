@@ -92,42 +92,88 @@ k_mcg_phi_range(const double* __restrict__ phi, long G, double* __restrict__ out
 // Row j of P and Q is gene perm[j] (the batch's abundance order, see k_mcg_sort_key): genes with similar expression sit
 // in neighbouring rows, so the pairs that carry weight form a band around the diagonal.
 // Rows j >= G are padding: zeros with c_j = MC_LOG_ZERO, so their weight is exactly 0.
+// Two kernels.  k_mcg_prep_src: grid (rows / 128, KTP / 8), one thread per (row, k-chunk): the thread computes the chunk's eight
+// columns and writes them as one 64-byte piece (consecutive threads = consecutive rows: whole lines); the chunks of the sample
+// part also leave their partial sums of r l_s (for c_j) and of A_s^2 (for the screening bound) in part[].  One thread per row
+// walking all KTP columns (round 1) gave 469 blocks of serial, 8-byte-strided stores per batch: a fifth of a wave, as long at
+// 8 GPUs as at one.  k_mcg_prep_src_fin: one thread per row adds the partials in chunk order (a fixed order: the same bits for
+// every GPU count), writes c_j and the row's summary for the screening pass, qsum[j] = (sqrt(sum A^2), max_v |lg_v|, |c_j|).
+__device__ __forceinline__ double mcg_src_tail_col(int k, int n, int Kc, int KT, double r, double tt) {
+    // column k >= n of row j, except c_j: Chebyshev T_{k-n}(tt), then lgamma(v + r) - lgamma(v + 1) for v < MCG_SHIFT, then zeros
+    if (k < n + Kc) {
+        double t0 = 1.0, t1 = tt;
+        for (int i = 0; i < k - n; ++i) { const double t2 = 2.0 * tt * t1 - t0; t0 = t1; t1 = t2; }
+        return t0;
+    }
+    if (k < n + Kc + MCG_SHIFT) { const int v = k - n - Kc; return lgamma(v + r) - lgamma(v + 1.0); }
+    return 0.0;                                              // c_j (k = KT - 1) is written by k_mcg_prep_src_fin; padding
+}
 __global__ void __launch_bounds__(128)
 k_mcg_prep_src(const double* __restrict__ mu_hat, long G, const int* __restrict__ cols, const double* __restrict__ phi,
-               const int* __restrict__ perm, McgShape sh, double* __restrict__ Q) {
+               const int* __restrict__ perm, McgShape sh, double* __restrict__ Q, double2* __restrict__ part) {
     const long j = (long)blockIdx.x * blockDim.x + threadIdx.x;
+    const int kc = blockIdx.y;
     if (j >= sh.rows) return;
     const int n = sh.n, Kc = sh.Kc;
+    double v[MCG_KC];
+    double csum = 0, s2 = 0;
     if (j >= G) {
-        for (int k = 0; k < sh.KTP; ++k) Q[mcg_index(sh.rows, j, k)] = (k == sh.KT - 1) ? MC_LOG_ZERO : 0.0;
+#pragma unroll
+        for (int e = 0; e < MCG_KC; ++e) v[e] = 0.0;
+    } else {
+        const long gj = perm[j];
+        const double r = 1.0 / phi[gj];
+        double tt = 0.0;
+        if (kc * MCG_KC + MCG_KC > n) {
+            const double u = log(r + (double)MCG_SHIFT);
+            tt = (sh.uhi > sh.ulo) ? (2.0 * u - (sh.ulo + sh.uhi)) / (sh.uhi - sh.ulo) : 0.0;
+            tt = fmin(1.0, fmax(-1.0, tt));
+        }
+        double mu[MCG_KC];
+#pragma unroll
+        for (int e = 0; e < MCG_KC; ++e) { const int t = kc * MCG_KC + e; mu[e] = t < n ? mu_hat[gj + (long)cols[t] * G] : 1.0; }
+#pragma unroll
+        for (int e = 0; e < MCG_KC; ++e) {
+            const int k = kc * MCG_KC + e;
+            if (k < n) {
+                double a, l;
+                if (mu[e] == 0) { a = MC_LOG_ZERO; l = 0; }
+                else {
+                    a = (mu[e] < r) ? log(mu[e] / (r + mu[e])) : log1p(-r / (r + mu[e]));
+                    l = (r < mu[e]) ? log(r / (r + mu[e])) : log1p(-mu[e] / (r + mu[e]));
+                }
+                v[e] = a;
+                csum += r * l;
+                s2 += a * a;
+            } else v[e] = mcg_src_tail_col(k, n, Kc, sh.KT, r, tt);
+        }
+    }
+    // the chunk's 64 bytes: column kk of the chunk sits at (kk ^ swz), swz as in mcg_index
+    const int swz = (int)((j >> 1) & 1) << 2;
+    static_assert(MCG_KC == 8, "chunk layout");
+    double2* dst = reinterpret_cast<double2*>(Q + ((size_t)kc * sh.rows + j) * MCG_KC);
+    const double2 a0 = make_double2(v[0], v[1]), a1 = make_double2(v[2], v[3]), b0 = make_double2(v[4], v[5]), b1 = make_double2(v[6], v[7]);
+    dst[0] = swz ? b0 : a0; dst[1] = swz ? b1 : a1; dst[2] = swz ? a0 : b0; dst[3] = swz ? a1 : b1;
+    if (kc * MCG_KC < n) part[(size_t)kc * sh.rows + j] = make_double2(csum, s2);
+}
+__global__ void __launch_bounds__(128)
+k_mcg_prep_src_fin(long G, const double* __restrict__ phi, const int* __restrict__ perm, McgShape sh,
+                   const double2* __restrict__ part, double* __restrict__ Q, float4* __restrict__ qsum) {
+    const long j = (long)blockIdx.x * blockDim.x + threadIdx.x;
+    if (j >= sh.rows) return;
+    if (j >= G) {
+        Q[mcg_index(sh.rows, j, sh.KT - 1)] = MC_LOG_ZERO;
+        qsum[j] = make_float4(0.f, 0.f, -1.f, 0.f);          // (z < 0: an impossible source, left out of the tile maxima)
         return;
     }
-    const long gj = perm[j];
-    const double r = 1.0 / phi[gj];
-    double c = 0;
-    for (int t = 0; t < n; ++t) {
-        const double mu = mu_hat[gj + (long)cols[t] * G];
-        double a, l;
-        if (mu == 0) { a = MC_LOG_ZERO; l = 0; }
-        else {
-            a = (mu < r) ? log(mu / (r + mu)) : log1p(-r / (r + mu));
-            l = (r < mu) ? log(r / (r + mu)) : log1p(-mu / (r + mu));
-        }
-        Q[mcg_index(sh.rows, j, t)] = a;
-        c += r * l;
-    }
-    const double u = log(r + (double)MCG_SHIFT);
-    double tt = (sh.uhi > sh.ulo) ? (2.0 * u - (sh.ulo + sh.uhi)) / (sh.uhi - sh.ulo) : 0.0;
-    tt = fmin(1.0, fmax(-1.0, tt));
-    double t0 = 1.0, t1 = tt;
-    for (int k = 0; k < Kc; ++k) {
-        Q[mcg_index(sh.rows, j, n + k)] = t0;
-        const double t2 = 2.0 * tt * t1 - t0;
-        t0 = t1; t1 = t2;
-    }
-    for (int v = 0; v < MCG_SHIFT; ++v) Q[mcg_index(sh.rows, j, n + Kc + v)] = lgamma(v + r) - lgamma(v + 1.0);
-    Q[mcg_index(sh.rows, j, sh.KT - 1)] = c - n * lgamma(r);
-    for (int k = sh.KT; k < sh.KTP; ++k) Q[mcg_index(sh.rows, j, k)] = 0.0;
+    const double r = 1.0 / phi[perm[j]];
+    double c = 0, s2 = 0;
+    for (int kc = 0; kc * MCG_KC < sh.n; ++kc) { const double2 p = part[(size_t)kc * sh.rows + j]; c += p.x; s2 += p.y; }
+    const double cj = c - sh.n * lgamma(r);
+    Q[mcg_index(sh.rows, j, sh.KT - 1)] = cj;
+    double mx = 0;
+    for (int v = 0; v < MCG_SHIFT; ++v) mx = fmax(mx, fabs(lgamma(v + r) - lgamma(v + 1.0)));
+    qsum[j] = make_float4((float)sqrt(s2), (float)mx, fabsf((float)cj), 0.f);
 }
 
 // ---- target side, step 0: the batch's counts of this rank's target rows in abundance order, xs[t * own_rows + local row] ----
@@ -555,9 +601,13 @@ k_mcg_sort_key(const double* __restrict__ mu_hat, long G, int n, const int* __re
                int* __restrict__ idx) {
     const long g = (long)blockIdx.x * blockDim.x + threadIdx.x;
     if (g >= G) return;
-    double s = 0;
-    for (int t = 0; t < n; ++t) s += log(fmax(mu_hat[g + (long)cols[t] * G], 1e-300));
-    key[g] = (float)(s / n);
+    // single precision and independent loads: the key only orders the genes (any fixed order gives the same sums up to
+    // rounding, and the same bits for every GPU count); in double precision with one dependent log per load this kernel was
+    // as long as the whole operand preparation of a shard at 8 GPUs
+    float s = 0.f;
+#pragma unroll 8
+    for (int t = 0; t < n; ++t) s += __log2f(fmaxf((float)mu_hat[g + (long)cols[t] * G], 1e-37f));
+    key[g] = s / (float)n;
     idx[g] = (int)g;
 }
 __global__ void k_mcg_iota(int* __restrict__ idx, long G) {

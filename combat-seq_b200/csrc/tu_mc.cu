@@ -114,7 +114,11 @@ static McPlan plan_mc_gemm(const int32_t* cnt, long G, int n, const int* d_cols,
     pl.gp = (double2*)g_dev.get<double>(sl("mcg_gp", slot), (size_t)2 * sh.rows);
     unsigned long long* d_tail = g_dev.get<unsigned long long>(sl("mcg_tail", slot), 1);
     CBS_CUDA(cudaMemsetAsync(d_tail, 0, sizeof(unsigned long long), st));
-    CBS_LAUNCH(k_mcg_prep_src, grid1(sh.rows, 128), 128, 0, st, d_mu_hat, G, d_cols, d_phi, pl.perm, sh, pl.Q);
+    double2* d_part = (double2*)g_dev.get<double>(sl("mcg_srcpart", slot), (size_t)2 * ((n + MCG_KC - 1) / MCG_KC) * sh.rows);
+    float4* d_qsum = (float4*)g_dev.get<float>(sl("mcg_qsum", slot), (size_t)4 * sh.rows);
+    CBS_LAUNCH(k_mcg_prep_src, dim3((unsigned)(sh.rows / 128), (unsigned)(sh.KTP / MCG_KC)), 128, 0, st, d_mu_hat, G, d_cols, d_phi, pl.perm, sh,
+               pl.Q, d_part);
+    CBS_LAUNCH(k_mcg_prep_src_fin, grid1(sh.rows, 128), 128, 0, st, G, d_phi, (const int*)pl.perm, sh, (const double2*)d_part, pl.Q, d_qsum);
     CBS_LAUNCH(k_mcg_pack_gp, grid1(sh.rows, 256), 256, 0, st, d_gamma, d_phi, pl.perm, G, sh.rows, pl.gp);
     if (own_rows > 0) {                     // P is only needed for this rank's target blocks (Q for all sources)
         int32_t* xs = g_dev.get<int32_t>(sl("mcg_xs", slot), (size_t)own_rows * n);
@@ -134,7 +138,7 @@ static McPlan plan_mc_gemm(const int32_t* cnt, long G, int n, const int* d_cols,
     if (g_tune.mc_band && own_rows > 0) {
         float* hi = g_dev.get<float>(sl("mcs_hi", slot), (size_t)NJ * sh.rows);
         float* lo = g_dev.get<float>(sl("mcs_lo", slot), (size_t)NJ * sh.rows);
-        screened = mc_screen(pl.P, pl.Q, sh, own, slot, hi, lo, st);
+        screened = mc_screen(pl.P, pl.Q, d_qsum, sh, own, slot, hi, lo, st);
         if (screened) {
             t_ctx->set_func_attr((const void*)k_mcg_list_screened, cudaFuncAttributeMaxDynamicSharedMemorySize, 64 * 1024);
             CBS_LAUNCH(k_mcg_list_screened, dim3((unsigned)ntiles64), 256, (size_t)NJ, st, hi, lo, sh.rows, (int)NJ,

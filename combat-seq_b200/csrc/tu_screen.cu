@@ -70,7 +70,7 @@ struct ScrShape {
 // |A_j|, max_v |lg_jv| and |c_j|, kept as the bit patterns of non-negative floats (atomicMax on ints; zero on entry).
 __global__ void __launch_bounds__(256)
 k_scr_convert(const double* __restrict__ X, McgShape sh, ScrShape ss, int is_q, McgOwn own, long n_rows,
-              __nv_bfloat16* __restrict__ out, float4* __restrict__ pvec, int* __restrict__ qtile) {
+              __nv_bfloat16* __restrict__ out, float4* __restrict__ pvec, int* __restrict__ qtile, const float4* __restrict__ qsum) {
     const long t = (long)blockIdx.x * blockDim.x + threadIdx.x;
     const int chunks_per_row = ss.nk * 8;
     const long lr = t / chunks_per_row;
@@ -116,21 +116,18 @@ k_scr_convert(const double* __restrict__ X, McgShape sh, ScrShape ss, int is_q, 
     char* dst = reinterpret_cast<char*>(out) + blk * SCR_TILE_BYTES + rr * 128 + ((c8 ^ (rr & 7)) << 4);
     *reinterpret_cast<uint4*>(dst) = *reinterpret_cast<const uint4*>(v);
     if (ch == 0 && !pad_row) {
-        double s2 = 0;
-        for (int k = 0; k < ss.n; ++k) { const double x = X[mcg_index(sh.rows, r, k)]; s2 += x * x; }
         if (!is_q) {
-            double s1 = 0, hot = 0;
+            double s2 = 0, s1 = 0, hot = 0;
+            for (int k = 0; k < ss.n; ++k) { const double x = X[mcg_index(sh.rows, r, k)]; s2 += x * x; }
             for (int k = ss.n + 1; k < ss.n + sh.Kc; ++k) s1 += fabs(X[mcg_index(sh.rows, r, k)]);
             for (int k = ss.n + sh.Kc; k < sh.KT - 1; ++k) hot += X[mcg_index(sh.rows, r, k)];
             pvec[r] = make_float4(SCR_EPS * (float)sqrt(s2), SCR_EPS * (float)s1, SCR_EPS * (float)hot, 0.f);
         } else {
-            double mx = 0;
-            for (int k = ss.n + sh.Kc; k < sh.KT - 1; ++k) mx = fmax(mx, fabs(X[mcg_index(sh.rows, r, k)]));
-            const float cj = fabsf((float)X[mcg_index(sh.rows, r, sh.KT - 1)]);
+            const float4 q = qsum[r];                              // row summary left by k_mcg_prep_src_fin
             int* q3 = qtile + 4 * (r / MCG_TILE);
-            atomicMax(q3 + 0, __float_as_int(fminf((float)sqrt(s2) * 1.000001f, 3e38f)));
-            atomicMax(q3 + 1, __float_as_int((float)mx * 1.000001f));
-            if (cj < 1e29f) atomicMax(q3 + 2, __float_as_int(cj));             // (c_j = -1e30 marks an impossible source)
+            atomicMax(q3 + 0, __float_as_int(fminf(q.x * 1.000001f, 3e38f)));
+            atomicMax(q3 + 1, __float_as_int(q.y * 1.000001f));
+            if (q.z >= 0.f && q.z < 1e29f) atomicMax(q3 + 2, __float_as_int(q.z));     // (c_j = -1e30 marks an impossible source)
         }
     }
 }
@@ -363,7 +360,7 @@ __global__ void k_scr_items(McgOwn own, long rows, int NJ2, int nchunk, int3* __
     }
 }
 
-bool mc_screen(const double* P, const double* Q, const McgShape& sh, McgOwn own, int slot, float* hi, float* lo,
+bool mc_screen(const double* P, const double* Q, const float4* qsum, const McgShape& sh, McgOwn own, int slot, float* hi, float* lo,
                cudaStream_t st) {
     ScrShape ss;
     ss.n = sh.n;
@@ -389,8 +386,8 @@ bool mc_screen(const double* P, const double* Q, const McgShape& sh, McgOwn own,
     int* qtile = g_dev.get<int>("mcs_qtile" + sfx, (size_t)4 * (ss.nrb + 1));
     CBS_CUDA(cudaMemsetAsync(qtile, 0, (size_t)4 * (ss.nrb + 1) * sizeof(int), st));
     const int cpr = ss.nk * 8;
-    CBS_LAUNCH(k_scr_convert, grid1(own_blocks * SCR_BM * cpr, 256), 256, 0, st, P, sh, ss, 0, own, own_blocks * SCR_BM, Pt, pvec, (int*)nullptr);
-    CBS_LAUNCH(k_scr_convert, grid1((sh.rows + SCR_BM) * cpr, 256), 256, 0, st, Q, sh, ss, 1, own, sh.rows + SCR_BM, Qt, (float4*)nullptr, qtile);
+    CBS_LAUNCH(k_scr_convert, grid1(own_blocks * SCR_BM * cpr, 256), 256, 0, st, P, sh, ss, 0, own, own_blocks * SCR_BM, Pt, pvec, (int*)nullptr, (const float4*)nullptr);
+    CBS_LAUNCH(k_scr_convert, grid1((sh.rows + SCR_BM) * cpr, 256), 256, 0, st, Q, sh, ss, 1, own, sh.rows + SCR_BM, Qt, (float4*)nullptr, qtile, qsum);
     int sms = 148;
     cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
     // about 8 waves of CTAs and at least 4 ranges; every CTA re-loads its 128-row A operand once, so ranges should not be
