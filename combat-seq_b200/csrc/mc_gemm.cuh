@@ -225,42 +225,64 @@ k_mcg_prep_nodes(const int32_t* __restrict__ xs, long G, McgShape sh, McgOwn own
 // ---- target side, step 2: row i of P (counts, Chebyshev coefficients by DCT, one-hot counts, 1) ------------
 // dct is the Kc x Kc table dct[k*Kc + m] = (k ? 2 : 1)/Kc * cos(pi k (m + 1/2)/Kc).  tail_bits: atomicMax of the
 // bit pattern of |C_{Kc-1}| + |C_{Kc-2}| (non-negative doubles order like their bit patterns).
+// grid (own_rows / 128, KTP / 8): one thread per (row, k-chunk), the chunk written as one 64-byte piece (see k_mcg_prep_src).
 __global__ void __launch_bounds__(128)
 k_mcg_prep_tgt(const int32_t* __restrict__ xs, long G, McgShape sh, McgOwn own, long own_rows,
                const double* __restrict__ Fnode, const double* __restrict__ dct,
                double* __restrict__ P, unsigned long long* __restrict__ tail_bits) {
     const long lr = (long)blockIdx.x * blockDim.x + threadIdx.x;
+    const int kc = blockIdx.y;
     if (lr >= own_rows) return;
     const long i = own.row(lr);
     if (i >= sh.rows) return;
-    const int n = sh.n, Kc = sh.Kc;
-    if (i >= G) {
-        for (int k = 0; k < sh.KTP; ++k) P[mcg_index(sh.rows, i, k)] = 0.0;
-        return;
-    }
-    int hot[MCG_SHIFT];
+    const int n = sh.n, Kc = sh.Kc, k0 = kc * MCG_KC;
+    double v[MCG_KC];
 #pragma unroll
-    for (int v = 0; v < MCG_SHIFT; ++v) hot[v] = 0;
-    for (int t = 0; t < n; ++t) {
-        const int x = xs[(long)t * own_rows + lr];
-        P[mcg_index(sh.rows, i, t)] = (double)x;
+    for (int e = 0; e < MCG_KC; ++e) v[e] = 0.0;
+    if (i < G) {
 #pragma unroll
-        for (int v = 0; v < MCG_SHIFT; ++v) hot[v] += (x == v);
-    }
-    double f[MCG_MAX_KC];
-    for (int m = 0; m < Kc; ++m) f[m] = Fnode[(long)m * G + i];
-    double tail = 0;
-    for (int k = 0; k < Kc; ++k) {
-        double c = 0;
-        for (int m = 0; m < Kc; ++m) c += dct[k * Kc + m] * f[m];
-        P[mcg_index(sh.rows, i, n + k)] = c;
-        if (Kc >= 4 && k >= Kc - 2) tail += fabs(c);
-    }
+        for (int e = 0; e < MCG_KC; ++e) if (k0 + e < n) v[e] = (double)xs[(long)(k0 + e) * own_rows + lr];
+        if (k0 + MCG_KC > n && k0 < n + Kc) {                    // Chebyshev coefficients c_k = sum_m dct[k][m] f[m]
+            double f[MCG_MAX_KC];
+            for (int m = 0; m < Kc; ++m) f[m] = Fnode[(long)m * G + i];
 #pragma unroll
-    for (int v = 0; v < MCG_SHIFT; ++v) P[mcg_index(sh.rows, i, n + Kc + v)] = (double)hot[v];
-    P[mcg_index(sh.rows, i, sh.KT - 1)] = 1.0;
-    for (int k = sh.KT; k < sh.KTP; ++k) P[mcg_index(sh.rows, i, k)] = 0.0;
-    if (tail > 0) atomicMax(tail_bits, (unsigned long long)__double_as_longlong(tail));
+            for (int e = 0; e < MCG_KC; ++e) {
+                const int k = k0 + e - n;
+                if (k < 0 || k >= Kc) continue;
+                double c = 0;
+                for (int m = 0; m < Kc; ++m) c += dct[k * Kc + m] * f[m];
+                v[e] = c;
+            }
+            if (Kc >= 4 && k0 <= n + Kc - 1 && n + Kc - 1 < k0 + MCG_KC) {       // the thread that holds the last coefficient
+                double c2 = 0;
+                for (int m = 0; m < Kc; ++m) c2 += dct[(Kc - 2) * Kc + m] * f[m];
+                double c1 = 0;
+                for (int m = 0; m < Kc; ++m) c1 += dct[(Kc - 1) * Kc + m] * f[m];
+                const double tail = fabs(c2) + fabs(c1);
+                if (tail > 0) atomicMax(tail_bits, (unsigned long long)__double_as_longlong(tail));
+            }
+        }
+        if (k0 + MCG_KC > n + Kc && k0 < n + Kc + MCG_SHIFT) {   // one-hot counts: how many samples have x == v
+            int hot[MCG_SHIFT];
+#pragma unroll
+            for (int q = 0; q < MCG_SHIFT; ++q) hot[q] = 0;
+            for (int t = 0; t < n; ++t) {
+                const int x = xs[(long)t * own_rows + lr];
+#pragma unroll
+                for (int q = 0; q < MCG_SHIFT; ++q) hot[q] += (x == q);
+            }
+#pragma unroll
+            for (int e = 0; e < MCG_KC; ++e)
+#pragma unroll
+                for (int q = 0; q < MCG_SHIFT; ++q) if (k0 + e == n + Kc + q) v[e] = (double)hot[q];
+        }
+#pragma unroll
+        for (int e = 0; e < MCG_KC; ++e) if (k0 + e == sh.KT - 1) v[e] = 1.0;
+    }
+    const int swz = (int)((i >> 1) & 1) << 2;
+    double2* dst = reinterpret_cast<double2*>(P + ((size_t)kc * sh.rows + i) * MCG_KC);
+    const double2 a0 = make_double2(v[0], v[1]), a1 = make_double2(v[2], v[3]), b0 = make_double2(v[4], v[5]), b1 = make_double2(v[6], v[7]);
+    dst[0] = swz ? b0 : a0; dst[1] = swz ? b1 : a1; dst[2] = swz ? a0 : b0; dst[3] = swz ? a1 : b1;
 }
 
 // ---- PTX helpers: mbarrier + 1-D TMA bulk copy (global -> shared) and the FP64 tensor-core MMA ---------------

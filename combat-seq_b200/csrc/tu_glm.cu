@@ -138,8 +138,8 @@ k_glm_fit_lanes(const int32_t* __restrict__ cnt, long G, long g0, long g1, const
     glm_store<GLM_LANES, PM>(d, r, g, G, ln, beta, cellbeta, coef, fitted, alpha_w, n_alpha, alpha_out);
 }
 
-// Second pass: one BLOCK (4 warps) per abandoned gene.  The gene's counts are staged in shared memory (the sweeps then run
-// at shared-memory instead of DRAM latency); a sweep is split over the design's classes (warp w takes classes w, w + 4, ...:
+// Second pass: one BLOCK (GLM_WIDE_WARPS warps) per abandoned gene.  The gene's counts are staged in shared memory (the sweeps then run
+// at shared-memory instead of DRAM latency); a sweep is split over the design's classes (warp w takes classes w, w + GLM_WIDE_WARPS, ...:
 // one exp per class, the class's samples over the 32 lanes, butterfly sums), the class sums are left in shared memory and
 // warp 0 assembles deviance, X'WX and X'z from them in class order.  Warp 0 runs edgeR's Levenberg iteration exactly as
 // fit_levenberg does (same lambda schedule, acceptance and stopping rules); the other warps wait for its sweep requests at
@@ -191,12 +191,16 @@ __device__ __forceinline__ void chol_solve_packed_warp(const double* a, int p, d
         __syncwarp();
     }
 }
-__device__ __forceinline__ void glm_wide_bar() { asm volatile("bar.sync 1, 128;" ::: "memory"); }
+#ifndef CBS_GLM_WIDE_WARPS
+#define CBS_GLM_WIDE_WARPS 16     // warps per abandoned gene: the classes of a sweep are dealt out over them (C5: 20 classes)
+#endif
+constexpr int GLM_WIDE_WARPS = CBS_GLM_WIDE_WARPS, GLM_WIDE_THREADS = 32 * GLM_WIDE_WARPS;
+__device__ __forceinline__ void glm_wide_bar() { asm volatile("bar.sync 1, %0;" ::"n"(GLM_WIDE_THREADS) : "memory"); }
 
 // class sums of one sweep at the coefficients bsrc for the classes of this warp: cls[c], cls[32+c], cls[64+c] = sum W, sum z, deviance
 __device__ __forceinline__ void glm_wide_classes(const DesignDev& d, const Row& r, const double* bsrc, int warp, int lane,
                                                  double* cls) {
-    for (int c = warp; c < d.ncls; c += 4) {
+    for (int c = warp; c < d.ncls; c += GLM_WIDE_WARPS) {
         const int t0 = d.cell_start[c], t1 = d.cell_start[c + 1], k0 = d.rowptr[t0], k1 = d.rowptr[t0 + 1];
         double eta = r.goff;
         for (int k = k0; k < k1; ++k) eta += d.cval[k] * bsrc[d.cidx[k]];
@@ -216,7 +220,7 @@ __device__ __forceinline__ void glm_wide_classes(const DesignDev& d, const Row& 
 }
 
 template <int PM>
-__global__ void __launch_bounds__(128)
+__global__ void __launch_bounds__(GLM_WIDE_THREADS)
 k_glm_fit_wide(const int32_t* __restrict__ cnt, long G, long g0, int N, const double* __restrict__ logoff,
                const __grid_constant__ GlmJobs jobs, const double* __restrict__ phi,
                const int* __restrict__ phi_col, const DesignDev* __restrict__ design, const double* __restrict__ goff_in,
@@ -436,7 +440,7 @@ void run_glm_fit(const int32_t* cnt, long G, long g0, long g1, int N, const doub
             const int stage = N <= 32768; \
             const size_t wsmem = glm_wide_smem_doubles<PM_>() * sizeof(double) + (stage ? (size_t)N * sizeof(int32_t) : 0); \
             t_ctx->set_func_attr((const void*)k_glm_fit_wide<PM_>, cudaFuncAttributeMaxDynamicSharedMemorySize, 160 * 1024); \
-            CBS_LAUNCH(k_glm_fit_wide<PM_>, dim3(64, (unsigned)nj), 128, wsmem, st, cnt, G, g0, N, d_logoff, jobs, d_phi, d_phi_col, \
+            CBS_LAUNCH(k_glm_fit_wide<PM_>, dim3(64, (unsigned)nj), GLM_WIDE_THREADS, wsmem, st, cnt, G, g0, N, d_logoff, jobs, d_phi, d_phi_col, \
                        d_design, d_goff, d_alpha_w, n_alpha, d_hist, stage, phi_by_class); \
         } } while (0)
     if (h_p <= 4) CBS_GLM_LANES(4); else if (h_p <= 8) CBS_GLM_LANES(8); else if (h_p <= 12) CBS_GLM_LANES(12); else CBS_GLM_LANES(16);

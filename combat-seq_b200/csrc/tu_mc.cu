@@ -126,7 +126,7 @@ static McPlan plan_mc_gemm(const int32_t* cnt, long G, int n, const int* d_cols,
         double* d_lgtab = g_dev.get<double>(sl("mcg_lgtab", slot), (size_t)sh.Kc * MCG_LGTAB);
         CBS_LAUNCH(k_mcg_node_table, dim3(MCG_LGTAB / 256, (unsigned)sh.Kc), 256, 0, st, sh, d_lgtab);
         CBS_LAUNCH(k_mcg_prep_nodes, dim3((unsigned)(own_rows / 128), (unsigned)sh.Kc), 128, 0, st, xs, G, sh, own, own_rows, d_lgtab, Fn);
-        CBS_LAUNCH(k_mcg_prep_tgt, grid1(own_rows, 128), 128, 0, st, xs, G, sh, own, own_rows, Fn, d_dct, pl.P, d_tail);
+        CBS_LAUNCH(k_mcg_prep_tgt, dim3((unsigned)((own_rows + 127) / 128), (unsigned)(sh.KTP / MCG_KC)), 128, 0, st, xs, G, sh, own, own_rows, Fn, d_dct, pl.P, d_tail);
     }
     // the series' tail is judged over ALL targets, so that every rank takes the decision a single GPU would
     if (comm && comm->world > 1) CBS_NCCL(nccl_api()->AllReduce(d_tail, d_tail, 1, NCCL_UINT64, NCCL_MAX, comm->nccl, st));
