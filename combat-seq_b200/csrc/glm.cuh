@@ -187,14 +187,6 @@ __device__ inline double lev_sweep(const DesignDev& d, const Row& r, const doubl
     if (d.ncls > 0) {
         // Samples grouped by distinct design row: mu_s = exp(gene offset + x_c'beta) * lib.size_s needs one exp per class,
         // and X'WX, X'z only need the class sums of W and z (the packed matrix is touched once per class, not per sample).
-        // (phi_by_class) dispersion of the next class and the lane's first sample of it, requested one class ahead
-        int ncol = 0, nyr = 0;
-        double nlib = 0, nphi = 0;
-        if (r.s.phi_by_class) {
-            const int u0 = d.cell_start[0], u1 = d.cell_start[1];
-            nphi = r.phi(d.col[u0]);
-            if (u0 + ln < u1) { ncol = d.col[u0 + ln]; nlib = r.lib(ncol); nyr = r.yraw(ncol); }
-        }
         for (int c = 0; c < d.ncls; ++c) {
             const int t0 = d.cell_start[c], t1 = d.cell_start[c + 1], k0 = d.rowptr[t0], k1 = d.rowptr[t0 + 1];
             double eta = r.goff;
@@ -203,18 +195,13 @@ __device__ inline double lev_sweep(const DesignDev& d, const Row& r, const doubl
             double sw = 0, sz = 0;
             if (r.s.phi_by_class) {
                 // one dispersion (and one reciprocal of it) per class; the count and the library size of the lane's next sample
-                // are requested before the current one is worked on, across class boundaries too (ncu: a quarter of the kernel's
-                // stall samples sat on the first use of these loads, and the dispersion added a third dependent load:
-                // column -> batch -> phi)
-                const double phi = nphi;
+                // are requested before the current one is worked on (ncu: a quarter of the kernel's stall samples sat on the
+                // first use of these loads, and the dispersion added a third dependent load: column -> batch -> phi)
+                const double phi = r.phi(d.col[t0]);
                 const double invphi = phi >= 1e-4 ? rcp_pos(phi) : 0.0;
-                int t = t0 + ln, col = ncol, yr = nyr;
-                double lib = nlib;
-                if (c + 1 < d.ncls) {
-                    const int u1 = d.cell_start[c + 2];
-                    nphi = r.phi(d.col[t1]);
-                    if (t1 + ln < u1) { ncol = d.col[t1 + ln]; nlib = r.lib(ncol); nyr = r.yraw(ncol); }
-                }
+                int t = t0 + ln, col = 0, yr = 0;
+                double lib = 0;
+                if (t < t1) { col = d.col[t]; lib = r.lib(col); yr = r.yraw(col); }
                 for (; t < t1; t += LANES) {
                     const double mu = E * lib, y = r.ycvt(yr, col);
                     if (t + LANES < t1) { col = d.col[t + LANES]; lib = r.lib(col); yr = r.yraw(col); }
