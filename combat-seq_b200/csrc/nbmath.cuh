@@ -447,6 +447,9 @@ constexpr double MQ_SMALL_X = 320.0;
 CBS_HD bool match_small(double x, double old_mu, double so, double new_mu, double sn, const double* __restrict__ inv, double* out) {
     const int xi = (int)x;                                       // 2 <= x <= MQ_SMALL_X
     if (so < 0.05 || sn < 0.05) return false;                    // (the DFMA form of the term ratio cancels for sizes near 0)
+    // prob = size / (size + mu) rounds to 1 for dispersions below ~1e-16 mu^-1 (what Brent's lower end gives on Poisson-like
+    // data): R 3.5's qnbinom returns 0 there ("if (prob == 1 || size == 0) return 0"), and so do the general routines below
+    if (!(sn / (sn + new_mu) < 1)) return false;
     const double qo = old_mu / (so + old_mu);
     double f = exp(-so * log1p(old_mu / so));                    // pmf_old(0) = (so / (so + mu))^so
     if (!(f > 1e-250)) return false;

@@ -106,3 +106,22 @@ def test_fast_log_for_positive_normal_arguments(hm):
     m = ref != 0
     assert err[m].max() <= 2.0, err[m].max()
     assert np.all(got[~m] == 0)
+
+
+def test_vanishing_dispersion_follows_r35_qnbinom(hm):
+    """Dispersions of 1e-20 (the lower end of Brent's bracket on Poisson-like data) make prob = size / (size + mu) round to 1:
+    R 3.5's qnbinom returns 0 there (nmath/qnbinom.c: "if (prob == 1 || size == 0) return 0"), so match_quantiles maps every count
+    above 1 that is not passed through to 1.  The fast routines (small-count sums included) must do what the plain ones do."""
+    rng = np.random.default_rng(0)
+    mu = np.exp(rng.normal(3, 1.5, 3000))
+    x = rng.poisson(mu).astype(float)
+    nmu = mu * np.exp(rng.normal(0, 0.3, 3000))
+    for phi in (1e-20, 1e-300):
+        plain = hm("hm_match_quantiles", x, mu, phi, nmu, phi, extra=(C.c_int(0),))
+        fast = hm("hm_match_quantiles", x, mu, phi, nmu, phi, extra=(C.c_int(2),))
+        assert np.array_equal(plain, fast)
+        assert set(np.unique(plain[x > 1])) <= {1.0} | set(np.unique(x))
+    for phi in (1e-8, 1e-12):                          # still a proper negative binomial, indistinguishable from Poisson
+        plain = hm("hm_match_quantiles", x, mu, phi, nmu, phi, extra=(C.c_int(0),))
+        fast = hm("hm_match_quantiles", x, mu, phi, nmu, phi, extra=(C.c_int(2),))
+        assert np.array_equal(plain, fast)
