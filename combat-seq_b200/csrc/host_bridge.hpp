@@ -2,7 +2,7 @@
 //
 // An R numeric matrix (the caller the drop-in is for, /root/reference/ComBat_seq.R:22) lives in pageable memory.  A plain
 // cudaMemcpy from or to such a buffer is staged by the driver on the calling thread at 10-13 GB/s; for C5 that is 480 MB in
-// and 480 MB out, a quarter of the whole call.  Here BRIDGE_WORKERS threads each copy their share of the rows through two
+// and 480 MB out, a quarter of the whole call.  Here up to BRIDGE_WORKERS threads (half the host's cores at most) each copy their share of the rows through two
 // pinned staging buffers and their own stream, so the host memcpy of one piece overlaps the DMA of another and several cores
 // share the memcpy.  Pinned (or registered) caller buffers do not come here: they are copied directly and asynchronously.
 #pragma once
@@ -13,7 +13,10 @@
 
 namespace cbs {
 
-constexpr int BRIDGE_WORKERS = 4;
+#ifndef CBS_BRIDGE_WORKERS
+#define CBS_BRIDGE_WORKERS 8      // measured on a 16-core B200 host, C5 from pageable buffers: 2 -> 201.6, 4 -> 194.5, 8 -> 181.0, 16 -> 181.0 ms per call
+#endif
+constexpr int BRIDGE_WORKERS = CBS_BRIDGE_WORKERS;
 constexpr size_t BRIDGE_PIECE = 8u << 20;      // bytes per staging buffer
 
 inline bool is_pageable(const void* p) {
@@ -45,7 +48,8 @@ inline void bridge_run(DevCtx* ctx, const std::vector<BridgeJob>& jobs, bool to_
         for (size_t l = 0; l < j.height; l += per) units.push_back({&j, l, std::min(per, j.height - l)});
     }
     if (units.empty()) return;
-    const int nw = (int)std::min<size_t>(BRIDGE_WORKERS, units.size());
+    const unsigned hw = std::thread::hardware_concurrency();
+    const int nw = (int)std::min<size_t>(std::max(1u, std::min((unsigned)BRIDGE_WORKERS, hw ? hw / 2 : 2u)), units.size());
     std::vector<char*> stage(2 * nw);
     for (int i = 0; i < 2 * nw; ++i) stage[i] = (char*)ctx->pin.get("bridge" + std::to_string(i), BRIDGE_PIECE);
     const int device = ctx->device;
