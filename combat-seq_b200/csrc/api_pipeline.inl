@@ -63,7 +63,7 @@ static const T* upload_counts_sharded(const T* h_counts, long G0, int N, cbs_com
     if (b > a)
         if (bridge_wanted(h_counts, (size_t)(b - a) * N * sizeof(T)))
             bridge_run(t_ctx, {BridgeJob{(char*)(h_counts + a), (size_t)G0 * sizeof(T), (char*)send, (size_t)per * sizeof(T),
-                                         (size_t)(b - a) * sizeof(T), (size_t)N, nullptr}}, true);
+                                         (size_t)(b - a) * sizeof(T), (size_t)N, nullptr}}, true, comm->world);
         else
             CBS_CUDA(cudaMemcpy2DAsync(send, (size_t)per * sizeof(T), h_counts + a, (size_t)G0 * sizeof(T), (size_t)(b - a) * sizeof(T),
                                        (size_t)N, cudaMemcpyHostToDevice, st));
@@ -274,7 +274,7 @@ static void pipeline(const cbs_input* in, cbs_output* out, const T* h_or_d_count
                         si = sj;
                     }
                 }
-                if (bridge) bridge_run(t_ctx, jobs, false);           // pageable caller buffer: staged by worker threads
+                if (bridge) bridge_run(t_ctx, jobs, false, world);           // pageable caller buffer: staged by worker threads
             }
         }
     }

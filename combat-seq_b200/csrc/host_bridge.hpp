@@ -36,7 +36,7 @@ struct BridgeJob {
 
 // Runs the jobs (all host-to-device or all device-to-host) and returns when every byte has arrived.  Must be called by the
 // thread that owns the device context `ctx` (its pinned cache provides the staging buffers).
-inline void bridge_run(DevCtx* ctx, const std::vector<BridgeJob>& jobs, bool to_device) {
+inline void bridge_run(DevCtx* ctx, const std::vector<BridgeJob>& jobs, bool to_device, int share = 1) {
     struct Unit { const BridgeJob* j; size_t line0, lines; };
     std::vector<BridgeJob> cut;                                   // lines longer than a staging buffer are cut into column strips
     for (const BridgeJob& j : jobs)
@@ -49,7 +49,9 @@ inline void bridge_run(DevCtx* ctx, const std::vector<BridgeJob>& jobs, bool to_
     }
     if (units.empty()) return;
     const unsigned hw = std::thread::hardware_concurrency();
-    const int nw = (int)std::min<size_t>(std::max(1u, std::min((unsigned)BRIDGE_WORKERS, hw ? hw / 2 : 2u)), units.size());
+    // `share` = devices (ranks or threads of one call) staging through this host at the same time: they divide the cores
+    const unsigned budget = (hw ? hw / 2 : 2u) / (unsigned)std::max(1, share);
+    const int nw = (int)std::min<size_t>(std::max(1u, std::min((unsigned)BRIDGE_WORKERS, budget)), units.size());
     std::vector<char*> stage(2 * nw);
     for (int i = 0; i < 2 * nw; ++i) stage[i] = (char*)ctx->pin.get("bridge" + std::to_string(i), BRIDGE_PIECE);
     const int device = ctx->device;

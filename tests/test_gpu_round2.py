@@ -172,6 +172,17 @@ def test_single_process_multi_gpu_is_bit_identical(pkg, synth):
             for k in want + ("keep", "lib_size", "disp_common", "n_mc_fallback"):
                 assert np.array_equal(one[k], many[k], equal_nan=True), "%s differs at n_gpus=%d (%s)" % (k, n, case.name)
             assert (many["row_begin"], many["row_end"]) == (0, case.counts.shape[0])
+    # big pageable float64 buffers (what R hands over): every device thread stages its rows through pinned memory
+    # (host_bridge.hpp), in and out; 4 600 x 1000 doubles = 36.8 MB, 18 MB per device at n_gpus = 2
+    case = synth.c5(G=4600, n=100, B=10)
+    d = pkg.design.build_design(case.counts.shape[1], case.batch, case.group, case.covar_mod, case.full_mod)
+    page_in = np.asfortranarray(case.counts.astype(np.float64))
+    outs = []
+    for n in (1, 2):
+        page_out = np.full(case.counts.shape, -1.0, order="F")
+        L.combat_seq_into(page_in, d.batch_idx, d.mod, page_out, shrink=False, shrink_disp=False, n_gpus=n)
+        outs.append(page_out)
+    assert np.array_equal(outs[0], outs[1]) and outs[0].min() >= 0
 
 
 def test_tagwise_prior_df_moderation(pkg, oracle, synth):
