@@ -424,7 +424,7 @@ def rooflines(L, prof, G, G0, N, nb, world, steps, diag):
                           "(screened band); pairs_equiv = all G^2 pairs / time" % (ktp, n_b, kc, tiles_done, tiles_all),
                      pairs_equiv_per_s=float(G) / world * G / avg_s)
         elif name.startswith("k_scr_mma"):
-            chunks = (int(n_b) + 15) // 16 + (int(kc) - 1 + 4 + 15) // 16
+            chunks = (int(n_b) + int(kc) - 1 + 4 + 3 + 15) // 16       # sample columns, Chebyshev orders >= 1, one-hot, 3 pieces of c_j
             rows = (G + 127) // 128 * 128
             flops = 2.0 * 128 * 256 * 16 * 3 * chunks * (rows / 128.0 / world) * ((rows / 128 + 1) // 2)
             ach = flops / avg_s / 1e12

@@ -52,8 +52,8 @@ static_assert(SCR_BM == MCG_TILE && SCR_BN == 2 * MCG_TILE, "screening tiles are
 
 struct ScrShape {
     int n, KS;       // samples; KS - n series columns (Chebyshev orders 1.., one-hot; no order-0 term, no c_j)
-    int nxc, ncc;    // 16-column chunks of the sample part and of the series part
-    int nk;          // k-tiles per operand row = ceil((nxc + ncc) / 2)
+    int nch;         // 16-column chunks: the n sample columns, then the series columns and the three pieces of c_j, back to back
+    int nk;          // k-tiles per operand row = ceil(nch / 2)
     int stages;      // ring of B stages (2 blocks each)
     long rows;       // rows of P / Q (multiple of 128)
     long nrb;        // 128-row blocks; the operands hold one more (zero) block so that the last pair can be read whole
@@ -87,9 +87,10 @@ k_scr_convert(const double* __restrict__ X, McgShape sh, ScrShape ss, int is_q, 
         float f = 0.f;
         if (!pad_row) {
             int k = -1, cpart = -1;                               // MC column to convert, or piece of c_j
-            if (c < ss.nxc) { const int kk = c * 16 + half * 8 + e; if (kk < ss.n) k = kk; }
+            const int q = c * 16 + half * 8 + e;                  // column of the packed screening row
+            if (q < ss.n) k = q;
             else {
-                const int kk = ser0 + (c - ss.nxc) * 16 + half * 8 + e;
+                const int kk = ser0 + (q - ss.n);
                 if (kk < ser1) k = kk; else if (kk < ser1 + 3) cpart = kk - ser1;
             }
             if (k >= 0) {
@@ -105,9 +106,9 @@ k_scr_convert(const double* __restrict__ X, McgShape sh, ScrShape ss, int is_q, 
                     f = cpart == 0 ? h : cpart == 1 ? m : (float)(x - (double)h - (double)m);
                 }
             }
-        } else if (is_q && !lo_part && c >= ss.nxc) {             // padding sources: c_j = -1e30, never kept
-            const int kk = ser0 + (c - ss.nxc) * 16 + half * 8 + e;
-            if (kk == ser1) f = -1e30f;
+        } else if (is_q && !lo_part) {                            // padding sources: c_j = -1e30, never kept
+            const int q = c * 16 + half * 8 + e;
+            if (q >= ss.n && ser0 + (q - ss.n) == ser1) f = -1e30f;
         }
         v[e] = __float2bfloat16_rn(f);
     }
@@ -270,7 +271,7 @@ k_scr_mma(const __nv_bfloat16* __restrict__ Pt, const __nv_bfloat16* __restrict_
             sbar_wait(a_full, 0);
             tc_fence_after();
             const uint32_t a_addr = s_u32(a_s), b_addr = s_u32(b_s);
-            const int nchunks = ss.nxc + ss.ncc;
+            const int nchunks = ss.nch;
             int st = 0; uint32_t ph = 0;
             for (int jj = 0; jj < nj; ++jj) {
                 const int as = jj & 1;
@@ -365,9 +366,8 @@ bool mc_screen(const double* P, const double* Q, const float4* qsum, const McgSh
     ScrShape ss;
     ss.n = sh.n;
     ss.KS = sh.KT - 2;
-    ss.nxc = (sh.n + 15) / 16;
-    ss.ncc = (ss.KS - sh.n + 3 + 15) / 16;                       // + the three columns of c_j
-    ss.nk = (ss.nxc + ss.ncc + 1) / 2;
+    ss.nch = (ss.KS + 3 + 15) / 16;                              // KS columns + the three columns of c_j
+    ss.nk = (ss.nch + 1) / 2;
     ss.rows = sh.rows;
     ss.nrb = sh.rows / SCR_BM;
     ss.NJ2 = (int)((ss.nrb + 1) / 2);
