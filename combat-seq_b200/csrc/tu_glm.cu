@@ -58,7 +58,7 @@ k_glm_fit(const int32_t* __restrict__ cnt, long G, long g0, long g1, const doubl
 constexpr int GLM_LANES = CBS_GLM_LANES_N;
 constexpr int GLM_LANES_PMAX = 16;
 #ifndef CBS_GLM_MINBLOCKS
-#define CBS_GLM_MINBLOCKS 5
+#define CBS_GLM_MINBLOCKS 6      // measured on C5: 4 -> 23.4, 5 -> 21.6, 6 -> 21.35 ms per step
 #endif
 // what a fit leaves behind: coefficients, alpha_g (ComBat_seq.R:131), fitted values; LANES lanes of the gene share the stores
 template <int LANES, int PM>
@@ -90,7 +90,11 @@ __device__ __forceinline__ void glm_store(const DesignDev& d, const Row& r, long
 // it with a whole warp and the gene's counts in shared memory.  On 8 lanes such a fit is a serial chain ten times longer
 // than its neighbours': it alone set the duration of a launch once the genes were spread over 8 GPUs (7 ms per launch
 // whatever the shard).  The decision depends on the gene only, so it is the same for every sharding.
-constexpr int GLM_SWEEP_CAP = 9;
+#ifndef CBS_GLM_SWEEP_CAP
+#define CBS_GLM_SWEEP_CAP 8      // measured on C5 (lanes kernel, ms per step): 12 -> 22.4, 9 -> 21.6, 8 -> 21.3, 7 -> 21.0, and 6 sends
+                                 // the bulk of the genes to the second pass (65 ms): the cap must stay above the usual 5-7 sweeps
+#endif
+constexpr int GLM_SWEEP_CAP = CBS_GLM_SWEEP_CAP;
 // One launch can carry two independent fits of the same genes (blockIdx.y picks the job): the plain fit and the predFC fit
 // of a glmFit(prior.count > 0) call read the same counts and do not depend on each other, and once the genes are spread
 // over several GPUs a launch is a fraction of a wave whose duration is the latency of one fit, not its throughput.
@@ -195,6 +199,8 @@ __device__ __forceinline__ void chol_solve_packed_warp(const double* a, int p, d
 #define CBS_GLM_WIDE_WARPS 16     // warps per abandoned gene: the classes of a sweep are dealt out over them (C5: 20 classes)
 #endif
 constexpr int GLM_WIDE_WARPS = CBS_GLM_WIDE_WARPS, GLM_WIDE_THREADS = 32 * GLM_WIDE_WARPS;
+constexpr int GLM_WIDE_BLOCKS = 592;      // blocks stride over the list; the usual list is a few dozen genes, but data whose fits need more
+                                          // sweeps than the cap must not queue behind 64 blocks (blocks beyond the list leave at once)
 __device__ __forceinline__ void glm_wide_bar() { asm volatile("bar.sync 1, %0;" ::"n"(GLM_WIDE_THREADS) : "memory"); }
 
 // class sums of one sweep at the coefficients bsrc for the classes of this warp: cls[c], cls[32+c], cls[64+c] = sum W, sum z, deviance
@@ -249,6 +255,7 @@ k_glm_fit_wide(const int32_t* __restrict__ cnt, long G, long g0, int N, const do
     const DesignDev d = *design;
     const int p = d.p, pt = p * (p + 1) / 2;
     const int count = *n_strag;
+    if ((int)blockIdx.x >= count) return;                     // (block-uniform) nothing for this block
     for (int k = threadIdx.x; k < 32 * PM; k += blockDim.x) Xc[k] = 0;
     __syncthreads();
     for (int c = threadIdx.x; c < d.ncls; c += blockDim.x) {
@@ -440,7 +447,7 @@ void run_glm_fit(const int32_t* cnt, long G, long g0, long g1, int N, const doub
             const int stage = N <= 32768; \
             const size_t wsmem = glm_wide_smem_doubles<PM_>() * sizeof(double) + (stage ? (size_t)N * sizeof(int32_t) : 0); \
             t_ctx->set_func_attr((const void*)k_glm_fit_wide<PM_>, cudaFuncAttributeMaxDynamicSharedMemorySize, 160 * 1024); \
-            CBS_LAUNCH(k_glm_fit_wide<PM_>, dim3(64, (unsigned)nj), GLM_WIDE_THREADS, wsmem, st, cnt, G, g0, N, d_logoff, jobs, d_phi, d_phi_col, \
+            CBS_LAUNCH(k_glm_fit_wide<PM_>, dim3(GLM_WIDE_BLOCKS, (unsigned)nj), GLM_WIDE_THREADS, wsmem, st, cnt, G, g0, N, d_logoff, jobs, d_phi, d_phi_col, \
                        d_design, d_goff, d_alpha_w, n_alpha, d_hist, stage, phi_by_class); \
         } } while (0)
     if (h_p <= 4) CBS_GLM_LANES(4); else if (h_p <= 8) CBS_GLM_LANES(8); else if (h_p <= 12) CBS_GLM_LANES(12); else CBS_GLM_LANES(16);

@@ -16,7 +16,7 @@ namespace cbs {
 // out is G0-row column-major; row of kept gene i is keep_idx[i] (or i when keep_idx == nullptr).
 // grid: (ceil((g1-g0)/4), ceil(N/32)), block 128.
 #ifndef CBS_MQ_MINBLOCKS
-#define CBS_MQ_MINBLOCKS 6      // 80 registers: measured 25.3 -> 23.4 ms on C5 against 5 blocks of 96 registers
+#define CBS_MQ_MINBLOCKS 8      // 64 registers; binned kernel on C5 (ms per step): 5 -> 9.75, 6 -> 8.9, 8 -> 8.15, 10 -> 8.13, 12 -> 8.33
 #endif
 __global__ void __launch_bounds__(128, CBS_MQ_MINBLOCKS)
 k_match_quantiles_warp(const int32_t* __restrict__ cnt, long G, long g0, long g1, const double* __restrict__ mu_hat,
