@@ -394,7 +394,10 @@ static_assert(MCG_THREADS == MCG_CONSUMER_WARPS * 32, "consumer thread count");
 // source-tile list srclist[t*NJ ..] (count[t] entries, ascending; built by the screening pass, or all NJ tiles).  The
 // decomposition depends on the lists only, never on the number of GPUs, and the partials of a target tile are merged in
 // segment order (k_mcg_finalize): results are bit-identical for every sharding.
-constexpr int MCG_SEG = 8;           // source tiles per work item
+#ifndef CBS_MCG_SEG
+#define CBS_MCG_SEG 8
+#endif
+constexpr int MCG_SEG = CBS_MCG_SEG;           // source tiles per work item
 template <int STABLE>
 __global__ void __launch_bounds__(MCG_BLOCK, MCG_CTAS)
 k_mc_gemm(const double* __restrict__ P, const double* __restrict__ Q, const double2* __restrict__ gp, McgShape sh,

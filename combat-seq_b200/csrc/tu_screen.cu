@@ -39,6 +39,9 @@
 
 namespace cbs {
 
+#ifndef CBS_SCR_WAVES
+#define CBS_SCR_WAVES 8
+#endif
 constexpr int SCR_BM = 128;                 // target rows per CTA (UMMA M)
 constexpr int SCR_BN = 256;                 // source rows per MMA (UMMA N): two source tiles of the contraction
 constexpr int SCR_KTILE = 64;               // bf16 per operand row and k-tile: 128 bytes, the swizzle span
@@ -392,7 +395,7 @@ bool mc_screen(const double* P, const double* Q, const float4* qsum, const McgSh
     cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
     // about 8 waves of CTAs and at least 4 ranges; every CTA re-loads its 128-row A operand once, so ranges should not be
     // too short either
-    int nchunk = (int)std::min<long>(std::max<long>(4, (8L * sms + own_blocks - 1) / std::max<long>(own_blocks, 1)), std::max(1, ss.NJ2 / 4));
+    int nchunk = (int)std::min<long>(std::max<long>(4, ((long)CBS_SCR_WAVES * sms + own_blocks - 1) / std::max<long>(own_blocks, 1)), std::max(1, ss.NJ2 / 4));
     int3* items = (int3*)g_dev.get<int>("mcs_items" + sfx, (size_t)3 * own_blocks * nchunk + 3);
     CBS_LAUNCH(k_scr_items, grid1(own_blocks, 128), 128, 0, st, own, sh.rows, ss.NJ2, nchunk, items);
     t_ctx->set_func_attr((const void*)k_scr_mma, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)ScrSmem::total);
