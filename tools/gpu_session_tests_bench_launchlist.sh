@@ -1,8 +1,7 @@
 #!/bin/bash
-# 1 GPU: tests, the default bench line, the ncu launch list of the same command
+# 1 GPU: a short bench line, then the ncu launch list (gpu__time_duration.sum per launch) of the same command
 O=gpurun_out; mkdir -p $O
-timeout 900 python -m pytest tests -m gpu -x -q -rs > $O/r02_pytest_gpu_16.txt 2>&1; echo "rc=$?" >> $O/r02_pytest_gpu_16.txt
-timeout 900 python bench.py > $O/r02_bench_c5_default_16.json 2> $O/r02_bench_c5_default_16.err; echo "rc=$?" >> $O/r02_bench_c5_default_16.err
-timeout 600 python bench.py --steps 2 --warmup 1 --no-cpu > $O/r02_bench_c5_short_16.json 2> $O/r02_bench_c5_short_16.err; echo "rc=$?" >> $O/r02_bench_c5_short_16.err
-timeout 900 ncu --metrics gpu__time_duration.sum --clock-control none -c 4000 --csv --log-file $O/r02_ncu_launches_16.csv python bench.py --steps 2 --warmup 1 --no-cpu > $O/r02_ncu_launches_16.log 2>&1; echo "rc=$?" >> $O/r02_ncu_launches_16.log
+CMD="python bench.py --steps 2 --warmup 1 --no-cpu"
+timeout 600 $CMD > $O/r02_bench_c5_short_final.json 2> $O/r02_bench_c5_short_final.err; echo "rc=$?" >> $O/r02_bench_c5_short_final.err
+timeout 900 ncu --metrics gpu__time_duration.sum --clock-control none -c 6000 --csv --log-file $O/r02_ncu_launches_final.csv $CMD > $O/r02_ncu_launches_final.log 2>&1; echo "rc=$?" >> $O/r02_ncu_launches_final.log
 exit 0
