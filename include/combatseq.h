@@ -85,9 +85,16 @@ int         cbs_fp64_mma_peak(double* tflops);   /* same for the FP64 tensor pip
  *                  amount of work; 0 = one warp per gene, lane = sample (same bits)
  *   "glm_scr"      1 (default) = Levenberg work arrays of the lane-group GLM kernel in shared memory; 0 = local memory
  *                  (same bits)
+ *   "glm_two_pass" 1 (default) = a Levenberg fit that needs more than 8 sweeps over the samples is abandoned by the lane-group
+ *                  kernel and redone by a block per gene (its sums associate differently: last-place differences for those
+ *                  genes); 0 = every fit finishes in the lane-group kernel
+ *   "apl_lanes"    1 (default) = lane-group APL kernel with the batch's row staged in shared memory (one-way designs);
+ *                  0 = one thread per (gene, evaluation)
+ *   "glm_hist"     1 = collect the histogram of sweeps per fit (cbs_get_diag "glm_iter_<k>"); default 0
  * cbs_get_diag keys: "mc_tail" (largest tail estimate since the last reset), "mc_terms" (Chebyshev terms of the
  * last contraction launch), "mc_tiles_done" / "mc_tiles_all" (source tiles visited / available, summed over the target
- * tiles of rank 0 since the last reset); cbs_get_diag("reset", &x) clears them. */
+ * tiles of rank 0 since the last reset), "glm_iter_<k>" (fits that took k sweeps, with "glm_hist"); cbs_get_diag("reset", &x)
+ * clears them. */
 int         cbs_set_tuning(const char* key, double value);
 int         cbs_get_diag(const char* key, double* value);
 
